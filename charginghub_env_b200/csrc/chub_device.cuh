@@ -1,0 +1,266 @@
+// chub_device.cuh -- device-side building blocks of the hub step kernel (sm_100a).
+//
+// Everything here is arithmetic the reference performs per pile / per hub; the citations give
+// the reference lines whose RESULTS each function reproduces.  The code is written for the GPU,
+// not transcribed: polynomials are fp64 Horner chains with explicit fma(), pow() never appears,
+// logf/expf with integer arguments come from host-built tables, and the libstdc++ polar normal
+// is re-derived on top of a 32-bit minstd state.  The translation unit is compiled with
+// -fmad=false so that every operation NOT written as fma() rounds exactly like the reference's
+// separate multiply/add (x86-64 SSE2, no contraction); fp64 results then narrow to fp32 at the
+// same points the reference's `float` returns do.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/chub.h"
+#include "../../include/chub_rng.h"
+
+// ---------------------------------------------------------------------------------------------
+// constant-memory tables, filled by the host (chub_engine.cu) with this machine's glibc
+struct ChubConst {
+    float renege[16];      // (float)(0.1 * logf(i + 1))            CHS.hpp:1287
+    float balk[64];        // expf((float)-(0.01 * k))               CHS.hpp:1299
+    double price[96];      // price_after_MAD_96                     Aggregator_Simple.py:9-15
+    double time_sin[96];   // sin(2 pi t / 96)                       evcssp_manager.py:319-320
+    double price_mean, price_std;
+    // curve constants that the reference evaluates with libm at run time
+    float fast_aa1_c;      // (float)((0.7194/0.053) * exp(0))       CHS.hpp:693
+    float fast_aa2_c;      // aa_part2_c                             CHS.hpp:698-700
+    float fast_scale;      // 100 / aa_part2(51.2f)  (fp32 division) CHS.hpp:652
+    float slow_c2_end;     // c_part2((float)3.67)                   CHS.hpp:576
+    double slow_stt1_a;    // -4.276 * pow(10,-5)                    CHS.hpp:581
+    double slow_stt2_a;    //  4.742 * pow(10,-6)                    CHS.hpp:585
+    // J2601 lookup (hydro_sys.py:232-233)
+    double j_x[10], j_y[10];
+    double j_slope[8];     // (y[2+a]-y[1+a])/(x[2+a]-x[1+a])
+    double topoff_time;    // (87.4 - 69) / 7.2                      hydro_sys.py:311
+    double fcev_cap;       // 6.3 * 1000                             hydro_sys.py:221
+};
+
+// per hub-class constants (derived on the host from chub_hub_class; hydro_sys.py:9-158)
+struct ChubClass {
+    int n[2];
+    int type[2];
+    int constant;
+    float perm_f;          // (float) fcev_permeate, as Boost.Python would narrow it
+    float possible_in_f;   // (float) 0.3
+    float transformer[2];  // CHS.hpp:1153-1154 / 1463-1464
+    double half[2];        // transformer / 2 (evcssp_manager.py:377)
+    double v_h_max, v_M, cap_mass, cap_floor /* cap_mass*0.1 */, floor_01 /* 0.1*cap_mass */;
+    double init_soc, init_mass, loss, fc_cells, cpr_w12;
+    double el_cells;       // integer valued
+    double el_den;         // v_M * 1000 * 60
+};
+
+#ifdef CHUB_KERNEL_TU  // device code below is compiled only into chub_kernels.cu
+__constant__ ChubConst kC;
+
+// ---------------------------------------------------------------------------------------------
+// per-hub random streams (include/chub_rng.h)
+struct HubRng {
+    uint32_t k0, k1, uctr, lcg;
+};
+
+__device__ __forceinline__ int rng_u1000(HubRng &r) {  // rand() % 1000, CHS.hpp:41
+    return (int) (chub_rand31(r.k0, r.k1, r.uctr++) % 1000u);
+}
+__device__ __forceinline__ float rng_u01(HubRng &r) {  // uniform_rand(0,1): tr*(1-0)+0
+    float tr = (float) rng_u1000(r) / 999.0f;
+    return tr * 1.0f + 0.0f;
+}
+__device__ __forceinline__ uint32_t rng_e(HubRng &r) {
+    r.lcg = chub_minstd_next(r.lcg);
+    return r.lcg;
+}
+
+// libstdc++ generate_canonical<double,53> over minstd_rand0: two draws (bits/random.tcc:3349-3381)
+__device__ __forceinline__ double rng_canon_d(HubRng &r) {
+    double a = (double) (rng_e(r) - 1u);
+    double b = (double) (rng_e(r) - 1u);
+    double sum = a + b * 2147483646.0;
+    double ret = sum / 4611686009837453316.0;  // (2^31-2)^2 rounded to double = 2^62 - 2^33
+    if (ret >= 1.0) ret = 0.99999999999999988898;
+    return ret;
+}
+// generate_canonical<float,24>: one draw, divisor float(2147483646) = 2^31
+__device__ __forceinline__ float rng_canon_f(HubRng &r) {
+    float a = (float) (rng_e(r) - 1u);
+    float ret = a * 4.656612873077392578125e-10f;  // exact: division by 2^31
+    if (ret >= 1.0f) ret = 0.99999994f;
+    return ret;
+}
+
+// std::normal_distribution<double>(mean, sd)(e) on a FRESH distribution object (CHS.hpp:805-806):
+// Marsaglia polar, second variate discarded (bits/random.tcc:1811-1844).
+__device__ __forceinline__ double rng_normal_d(HubRng &r, double mean, double sd) {
+    double x, y, r2;
+    do {
+        x = 2.0 * rng_canon_d(r) - 1.0;
+        y = 2.0 * rng_canon_d(r) - 1.0;
+        r2 = x * x + y * y;
+    } while (r2 > 1.0 || r2 == 0.0);
+    double mult = sqrt(-2.0 * log(r2) / r2);
+    return (y * mult) * sd + mean;
+}
+// float flavour (CHS.hpp:819-820, 833-834).  logf is taken as the correctly rounded fp32 log
+// (fp64 log narrowed), which is what glibc's logf returns except on rare hard cases.
+__device__ __forceinline__ float rng_normal_f(HubRng &r, float mean, float sd) {
+    float x, y, r2;
+    do {
+        x = 2.0f * rng_canon_f(r) - 1.0f;
+        y = 2.0f * rng_canon_f(r) - 1.0f;
+        r2 = x * x + y * y;
+    } while (r2 > 1.0f || r2 == 0.0f);
+    float lg = (float) log((double) r2);
+    float mult = sqrtf(-2.0f * lg / r2);
+    float ret = y * mult;
+    return ret * sd + mean;
+}
+
+__device__ __forceinline__ float rng_mk_soc(HubRng &r) {  // CHS.hpp:804-814
+    float de = (float) rng_normal_d(r, 7.0, 3.0);
+    de = fminf(fmaxf(de, 1.0f), 10.0f);
+    return (float) (75.0 - 5.0 * (double) de);
+}
+__device__ __forceinline__ int rng_late_time(HubRng &r) {  // CHS.hpp:816-830 ("slow" for both pile types)
+    int d = (int) roundf(rng_normal_f(r, 2.0f, 2.0f));
+    return d > 0 ? d : 0;
+}
+__device__ __forceinline__ int rng_init_cars(HubRng &r, int mu) {  // CHS.hpp:832-842, theta 3
+    int t = (int) roundf(rng_normal_f(r, (float) mu, 1.0f));
+    return min(max(t, mu - 3), mu + 3);
+}
+
+// ---------------------------------------------------------------------------------------------
+// charging curves.  Time unit = one 15-minute step.  fp32 in/out, fp64 inside.
+
+// --- slow charger (CHS.hpp:495-588) ---
+__device__ __forceinline__ float slow_s2t(float s) {
+    if (s < 0.0f) return 0.0f;
+    double d = (double) s;
+    if (d <= 73.89239629561729) return (float) (d * fma(kC.slow_stt1_a, d, 0.1295));
+    if (d <= 100.0) {
+        double p = fma(fma(fma(fma(kC.slow_stt2_a, d, -0.001529), d, 0.1871), d, -10.15), d, 213.1);
+        float q = (float) (p + 0.1787983924863248);
+        return (float) ((double) q + (0.2012016075138625 * (d - 73.89239629561729)) / 26.10760370438271);
+    }
+    return 14.68f;
+}
+// time -> (soc, power) in one go: car_step needs both at the same time (CHS.hpp:901-905)
+__device__ __forceinline__ void slow_step(float t, float &soc, float &power) {
+    double y = (double) (t * 0.25f);  // charge_time / 4 is exact in fp32
+    double td = (double) t;
+    float ch;
+    if (td <= 0.0) {
+        ch = 0.0f;
+    } else if (td <= 2.33 * 4) {
+        ch = (float) (y * fma(fma(fma(fma(-0.0004112, y, 0.0023025), y, 0.03562 / 3), y, 0.011895), y, 6.007));
+    } else if (td <= 3.67 * 4) {
+        ch = (float) (-4.041 * y + 19.140115 * log(fabs(y - 0.485)) + 11.943306312699628);
+    } else {
+        ch = kC.slow_c2_end;
+    }
+    soc = (float) ((double) (100.0f * ch) / 19.285746346634653);
+    if (td < 2.33 * 4) {
+        power = (float) fma(fma(fma(fma(-0.002056, y, 0.00921), y, 0.03562), y, 0.02379), y, 6.007);
+    } else if (td < 3.67 * 4) {
+        power = (float) ((-4.041 * y + 21.1) / (y - 0.485));
+    } else {
+        power = 0.0f;
+    }
+}
+__device__ __forceinline__ float slow_t2p(float t) {
+    double y = (double) (t * 0.25f), td = (double) t;
+    if (td < 2.33 * 4) return (float) fma(fma(fma(fma(-0.002056, y, 0.00921), y, 0.03562), y, 0.02379), y, 6.007);
+    if (td < 3.67 * 4) return (float) ((-4.041 * y + 21.1) / (y - 0.485));
+    return 0.0f;
+}
+
+// --- fast charger (CHS.hpp:621-725) ---
+__device__ __forceinline__ float fast_s2t(float s) {
+    if (s <= 0.0f) return 0.0f;
+    if (s >= 100.0f) return (float) (51.2 / 15);
+    float zf = (s - 61.43f) / 31.48f;  // norm_soc: fp32 arithmetic
+    double z = (double) zf, z2 = z * z;
+    // p4*x and q3*x are fp32 products in the reference (float locals times a float argument)
+    double p4z = (double) (-62.97f * zf), q3z = (double) (-50.12f * zf);
+    double num = fma(fma((double) -18.18f, z, (double) 9.559f), z, (double) 48.99f) * z2 + p4z + (double) 29.09f;
+    double den = fma(fma(z, 1.0, (double) -23.9f), z, (double) 56.48f) * z2 + q3z + (double) 18.96f;
+    return (float) (num / den);
+}
+__device__ __forceinline__ float fast_aa2(double x) {
+    double p = x * fma(fma(fma(fma(0.0002253 / 5, x, -(0.03572 / 4)), x, 2.016 / 3), x, -(48.76 / 2)), x, 457.7);
+    return (float) (p + (double) kC.fast_aa2_c);
+}
+__device__ __forceinline__ void fast_step(float t, float &soc, float &power) {
+    float xf = t * 15.0f;
+    double x = (double) xf, td = (double) t;
+    double ex = 0.0;
+    if (td > 0.0 && td <= 28.7 / 15) ex = exp(0.053 * x);
+    if (td <= 0.0) {
+        soc = 0.0f;
+    } else if (td <= 28.7 / 15) {
+        float a1 = (float) ((0.7194 / 0.053) * ex + 50.15 * x - (double) kC.fast_aa1_c);
+        soc = a1 * kC.fast_scale;
+    } else if (td <= 51.2 / 15) {
+        soc = fast_aa2(x) * kC.fast_scale;
+    } else {
+        soc = 100.0f;
+    }
+    if (td >= 0.0 && td < 28.7 / 15) {
+        if (td <= 0.0) ex = exp(0.053 * x);
+        power = (float) (0.7194 * ex + 47.78);
+    } else if (td >= 0.0 && td < 51.2 / 15) {
+        power = (float) fma(fma(fma(fma(0.0002253, x, -0.03572), x, 2.016), x, -48.76), x, 457.7);
+    } else {
+        power = 0.0f;
+    }
+}
+__device__ __forceinline__ float fast_t2p(float t) {
+    double x = (double) (t * 15.0f), td = (double) t;
+    if (td >= 0.0 && td < 28.7 / 15) return (float) (0.7194 * exp(0.053 * x) + 47.78);
+    if (td >= 0.0 && td < 51.2 / 15) return (float) fma(fma(fma(fma(0.0002253, x, -0.03572), x, 2.016), x, -48.76), x, 457.7);
+    return 0.0f;
+}
+
+// --- constant-power variants (CHS.hpp:496-501, 514-521, 528-535, 622-627, 640-647, 662-669) ---
+__device__ __forceinline__ float const_s2t(float s, double tmax) {
+    if (s <= 0.0f) return 0.0f;
+    if (s >= 100.0f) return (float) tmax;
+    return (float) (tmax * (double) s / 100.0);
+}
+__device__ __forceinline__ void const_step(float t, double tmax, float pconst, float &soc, float &power) {
+    if (t <= 0.0f) soc = 0.0f;
+    else if ((double) t >= tmax) soc = 100.0f;
+    else soc = (float) ((double) (100.0f * t) / tmax);
+    power = (tmax >= (double) t && t >= 0.0f) ? pconst : 0.0f;
+}
+
+#define CHUB_SLOW_TMAX 14.68
+#define CHUB_FAST_TMAX 3.4133333333333336
+#define CHUB_SLOW_PCONST ((float) 5.254973139368931)
+#define CHUB_FAST_PCONST ((float) 36.44764034125146)
+
+// dispatch on (station type, constant_charging); both are uniform across a homogeneous batch
+__device__ __forceinline__ float curve_s2t(int type, int cp, float s) {
+    if (cp) return const_s2t(s, type == CHUB_SLOW ? CHUB_SLOW_TMAX : CHUB_FAST_TMAX);
+    return type == CHUB_SLOW ? slow_s2t(s) : fast_s2t(s);
+}
+__device__ __forceinline__ void curve_step(int type, int cp, float t, float &soc, float &power) {
+    if (cp) {
+        const_step(t, type == CHUB_SLOW ? CHUB_SLOW_TMAX : CHUB_FAST_TMAX,
+                   type == CHUB_SLOW ? CHUB_SLOW_PCONST : CHUB_FAST_PCONST, soc, power);
+    } else if (type == CHUB_SLOW) {
+        slow_step(t, soc, power);
+    } else {
+        fast_step(t, soc, power);
+    }
+}
+__device__ __forceinline__ float curve_t2p(int type, int cp, float t) {
+    if (cp) {
+        double tmax = type == CHUB_SLOW ? CHUB_SLOW_TMAX : CHUB_FAST_TMAX;
+        return (tmax >= (double) t && t >= 0.0f) ? (type == CHUB_SLOW ? CHUB_SLOW_PCONST : CHUB_FAST_PCONST) : 0.0f;
+    }
+    return type == CHUB_SLOW ? slow_t2p(t) : fast_t2p(t);
+}
+#endif  // CHUB_KERNEL_TU

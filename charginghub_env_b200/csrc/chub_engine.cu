@@ -1,0 +1,709 @@
+// chub_engine.cu -- host side of libchub.so: the C ABI of include/chub.h over the sm_100a kernels.
+//
+// Owns all device memory of one engine (one shard of hubs on one GPU), derives the per-class
+// constants and lookup tables on the host with this machine's libm (so table entries equal what
+// the reference computes at run time), launches the step / reset kernels stream-ordered, and
+// exposes outputs as raw device pointers and DLPack tensors.  No CPU stepping path exists here:
+// if CUDA is unavailable every entry point fails with CHUB_ERR_CUDA.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "chub_kernels.cuh"
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string &msg) {
+    g_err = msg;
+    return code;
+}
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(CHUB_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));        \
+    } while (0)
+
+struct chub_engine {
+    chub_config cfg;
+    int H = 0, Hpad = 0, S0 = 0, S1 = 0;
+    int refcount = 1;  // engine handle + live DLPack views
+    bool destroyed = false;
+    std::vector<ChubClass> classes;
+    std::vector<double> el_tables;
+    std::vector<int32_t> hub_class;
+    ChubParams P;
+    // device
+    uint4 *pile = nullptr; float *arrive = nullptr; uint4 *hubA = nullptr; double *store = nullptr;
+    uint2 *keys = nullptr; int *cls = nullptr; float4 *stats = nullptr, *last_stats = nullptr;
+    uint32_t *err = nullptr; float *qsoc = nullptr; ChubClass *d_classes = nullptr; double *d_el = nullptr;
+    uint16_t *lut = nullptr; double *pv = nullptr, *wd = nullptr, *price_tr = nullptr;
+    float *obs = nullptr, *reward = nullptr; uint8_t *done = nullptr; double *diag = nullptr; float *st_power = nullptr;
+    long long *step_index = nullptr;
+    float *actions_stage = nullptr;  // device copy target of chub_step_host
+    int trace_len = 0, trace_per_hub = 0;
+    bool have_tables = false, have_classes = false, have_traces = false, have_seed = false;
+    long long launches = 0;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t graph_exec = nullptr;
+    int graph_steps = 0;
+};
+
+extern "C" const char *chub_last_error(void) { return g_err.c_str(); }
+extern "C" int chub_version(void) { return 100; }
+
+static void engine_free(chub_engine *e) {
+    cudaSetDevice(e->cfg.device);
+    if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
+    if (e->graph) cudaGraphDestroy(e->graph);
+    void *ptrs[] = {e->pile, e->arrive, e->hubA, e->store, e->keys, e->cls, e->stats, e->last_stats, e->err, e->qsoc,
+                    e->d_classes, e->d_el, e->lut, e->pv, e->wd, e->price_tr, e->obs, e->reward, e->done, e->diag,
+                    e->st_power, e->step_index, e->actions_stage};
+    for (void *p : ptrs)
+        if (p) cudaFree(p);
+    delete e;
+}
+static void engine_unref(chub_engine *e) {
+    if (--e->refcount == 0) engine_free(e);
+}
+
+template <class T>
+static cudaError_t dalloc(T **p, size_t n) {
+    cudaError_t r = cudaMalloc((void **) p, n * sizeof(T));
+    if (r == cudaSuccess) r = cudaMemset(*p, 0, n * sizeof(T));
+    return r;
+}
+
+extern "C" int chub_create(const chub_config *cfg, chub_engine **out) {
+    if (!cfg || !out) return fail(CHUB_ERR_ARG, "chub_create: null argument");
+    if (cfg->n_hubs <= 0) return fail(CHUB_ERR_ARG, "chub_create: n_hubs must be positive");
+    if (cfg->action_stride < 3) return fail(CHUB_ERR_ARG, "chub_create: action_stride too small");
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev == 0)
+        return fail(CHUB_ERR_CUDA, "chub_create: no CUDA device (this engine has no CPU path)");
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(CHUB_ERR_ARG, "chub_create: bad device ordinal");
+    CK(cudaSetDevice(cfg->device));
+    chub_engine *e = new chub_engine();
+    e->cfg = *cfg;
+    e->H = cfg->n_hubs;
+    e->Hpad = (cfg->n_hubs + 31) / 32 * 32;
+    const size_t Hp = (size_t) e->Hpad;
+    cudaError_t r = cudaSuccess;
+    auto A = [&](cudaError_t x) { if (r == cudaSuccess) r = x; };
+    A(dalloc(&e->hubA, Hp)); A(dalloc(&e->store, Hp)); A(dalloc(&e->keys, Hp));
+    A(dalloc(&e->stats, Hp)); A(dalloc(&e->last_stats, Hp)); A(dalloc(&e->err, Hp));
+    A(dalloc(&e->qsoc, Hp * CHUB_FCEV_QCAP)); A(dalloc(&e->lut, (size_t) 96 * 1000));
+    A(dalloc(&e->obs, Hp * CHUB_OBS_DIM)); A(dalloc(&e->reward, Hp)); A(dalloc(&e->done, Hp));
+    A(dalloc(&e->step_index, 1)); A(dalloc(&e->actions_stage, Hp * (size_t) cfg->action_stride));
+    if (cfg->diagnostics) { A(dalloc(&e->diag, Hp * CHUB_D_COUNT)); A(dalloc(&e->st_power, Hp * 6)); }
+    if (r != cudaSuccess) {
+        engine_free(e);
+        return fail(CHUB_ERR_CUDA, std::string("chub_create: allocation failed: ") + cudaGetErrorString(r));
+    }
+    *out = e;
+    return CHUB_OK;
+}
+
+extern "C" int chub_destroy(chub_engine *e) {
+    if (!e) return CHUB_OK;
+    if (e->destroyed) return fail(CHUB_ERR_STATE, "chub_destroy: already destroyed");
+    e->destroyed = true;
+    cudaSetDevice(e->cfg.device);
+    cudaDeviceSynchronize();
+    engine_unref(e);
+    return CHUB_OK;
+}
+
+// ---- per-class constants (hydro_sys.py:9-36, 57-72, 91-102, 133-158; CHS.hpp:1153-1154, 1463-1464) ----
+static double host_el_power(const ChubClass &c, double m) {
+    if (c.el_cells == 0.0) return 0.0;
+    double per_cell = m / c.el_cells;
+    double mol = per_cell / 2.02;
+    double litres = mol * c.v_M;
+    double ml_min = litres * 1000 * 60;
+    double cur = ml_min * 2 * 96487 / c.el_den;
+    double w = std::pow(cur, 2) * 0.326 + cur * 1.476;
+    return c.el_cells * w / 1000;
+}
+static void derive_class(const chub_hub_class &in, ChubClass &c, double *table) {
+    memset(&c, 0, sizeof c);
+    for (int k = 0; k < 2; ++k) {
+        c.n[k] = in.n_piles[k];
+        c.type[k] = in.station_type[k];
+        float unit = (in.station_type[k] == CHUB_SLOW) ? (float) 5.254973139368931 : (float) 36.44764034125146;
+        c.transformer[k] = unit * (float) in.n_piles[k];
+        c.half[k] = (double) c.transformer[k] / 2;
+    }
+    c.constant = in.constant_charging ? 1 : 0;
+    c.perm_f = (float) in.fcev_permeate;
+    c.possible_in_f = (float) 0.3;
+    const double prod = in.hydro_prod_rate > 0 ? in.hydro_prod_rate : 430.0;
+    c.v_h_max = 0.089 * prod * 1000 / 3600;
+    c.v_M = 0.082 * (273 + 25) / 1;
+    c.el_den = c.v_M * 1000 * 60;
+    {   // one reference cell produces 10 mL/min (hydro_sys.py:22-24)
+        double litres_s = (10.0 / 1000) / 60;
+        double grams_s = (litres_s / c.v_M) * 2.02;
+        c.el_cells = std::ceil(c.v_h_max / grams_s);
+    }
+    {   // two-stage adiabatic compression 1 -> sqrt(200) -> 200 bar (hydro_sys.py:57-77)
+        const double alpha = 1.4, R = 0.082, T = 273 + 25;
+        const double p_mid = std::sqrt(1.0 * 200.0);
+        const double k1 = alpha / (alpha - 1), k2 = k1 * R * T, k3 = (alpha - 1) / alpha;
+        c.cpr_w12 = k2 * (-1 + std::pow(p_mid / 1.0, k3)) + k2 * (-1 + std::pow(200.0 / p_mid, k3));
+    }
+    const double vol = in.hydro_store_vlt > 0 ? in.hydro_store_vlt : 5000.0;
+    c.cap_mass = (0.089 * (200 / 1)) * (vol * 1000);
+    c.cap_floor = c.cap_mass * 0.1;
+    c.floor_01 = 0.1 * c.cap_mass;
+    c.init_soc = in.init_soc;
+    c.init_mass = in.init_soc * c.cap_mass;
+    c.loss = in.hydro_loss;
+    c.fc_cells = in.fc_max_power < 0 ? 100.0 : in.fc_max_power;
+    if (in.el_table) {
+        memcpy(table, in.el_table, sizeof(double) * CHUB_EL_TABLE);
+    } else {  // hy_step(0.01*i) on an unclipped store (hydro_sys.py:153-157, 172-186)
+        for (int i = 0; i < 101; ++i) {
+            double flow = (0.01 * i * c.v_h_max * (15 * 60)) / (15 * 60);
+            if (c.v_h_max < flow) flow = c.v_h_max;
+            double n = flow / 2.02;
+            table[i] = host_el_power(c, flow) + (n * c.cpr_w12 / 0.8) / 1000;
+        }
+        table[101] = table[100];
+    }
+}
+
+extern "C" int chub_set_hub_classes(chub_engine *e, const chub_hub_class *classes, int32_t n_classes,
+                                    const int32_t *hub_class) {
+    if (!e || !classes || n_classes < 1) return fail(CHUB_ERR_ARG, "chub_set_hub_classes: bad argument");
+    if (n_classes > 1 && !hub_class) return fail(CHUB_ERR_ARG, "chub_set_hub_classes: hub_class required");
+    CK(cudaSetDevice(e->cfg.device));
+    int S0 = 0, S1 = 0;
+    e->classes.assign(n_classes, ChubClass());
+    e->el_tables.assign((size_t) n_classes * CHUB_EL_TABLE, 0.0);
+    for (int k = 0; k < n_classes; ++k) {
+        const chub_hub_class &in = classes[k];
+        for (int s = 0; s < 2; ++s) {
+            if (in.n_piles[s] < 0 || in.n_piles[s] > CHUB_MAX_PILES)
+                return fail(CHUB_ERR_ARG, "chub_set_hub_classes: piles per station must be in [0, 32]");
+            if (in.station_type[s] != CHUB_FAST && in.station_type[s] != CHUB_SLOW)
+                return fail(CHUB_ERR_ARG, "chub_set_hub_classes: station type must be CHUB_FAST or CHUB_SLOW");
+        }
+        if (in.n_piles[0] + in.n_piles[1] < 1)
+            return fail(CHUB_ERR_ARG, "chub_set_hub_classes: a hub needs at least one pile");  // evcssp_manager.py:336
+        if (in.n_piles[0] + in.n_piles[1] + 2 > e->cfg.action_stride)
+            return fail(CHUB_ERR_ARG, "chub_set_hub_classes: action_stride smaller than n0+n1+2");
+        if (!(in.init_soc >= 0.1 && in.init_soc <= 1.0))
+            return fail(CHUB_ERR_ARG, "chub_set_hub_classes: init_soc must be in [0.1, 1]");  // hydro_sys.py:137
+        derive_class(in, e->classes[k], &e->el_tables[(size_t) k * CHUB_EL_TABLE]);
+        S0 = std::max(S0, in.n_piles[0]);
+        S1 = std::max(S1, in.n_piles[1]);
+    }
+    if (hub_class)
+        for (int h = 0; h < e->H; ++h)
+            if (hub_class[h] < 0 || hub_class[h] >= n_classes)
+                return fail(CHUB_ERR_ARG, "chub_set_hub_classes: class index out of range");
+    if (e->pile) { cudaFree(e->pile); e->pile = nullptr; }
+    if (e->arrive) { cudaFree(e->arrive); e->arrive = nullptr; }
+    if (e->d_classes) { cudaFree(e->d_classes); e->d_classes = nullptr; }
+    if (e->d_el) { cudaFree(e->d_el); e->d_el = nullptr; }
+    if (e->cls) { cudaFree(e->cls); e->cls = nullptr; }
+    e->S0 = S0; e->S1 = S1;
+    const size_t slots = (size_t) (S0 + S1) * e->Hpad;
+    CK(dalloc(&e->pile, slots));
+    CK(dalloc(&e->arrive, slots));
+    CK(dalloc(&e->d_classes, (size_t) n_classes));
+    CK(dalloc(&e->d_el, (size_t) n_classes * CHUB_EL_TABLE));
+    CK(cudaMemcpy(e->d_classes, e->classes.data(), sizeof(ChubClass) * n_classes, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(e->d_el, e->el_tables.data(), sizeof(double) * e->el_tables.size(), cudaMemcpyHostToDevice));
+    e->hub_class.assign(e->H, 0);
+    if (n_classes > 1) {
+        e->hub_class.assign(hub_class, hub_class + e->H);
+        CK(dalloc(&e->cls, (size_t) e->Hpad));
+        CK(cudaMemcpy(e->cls, hub_class, sizeof(int32_t) * e->H, cudaMemcpyHostToDevice));
+    }
+    e->cfg.n_classes = n_classes;
+    e->have_classes = true;
+    return CHUB_OK;
+}
+
+extern "C" int chub_get_class_table(chub_engine *e, int32_t k, double *out) {
+    if (!e || !out || !e->have_classes || k < 0 || k >= (int) e->classes.size())
+        return fail(CHUB_ERR_ARG, "chub_get_class_table: bad argument");
+    memcpy(out, &e->el_tables[(size_t) k * CHUB_EL_TABLE], sizeof(double) * CHUB_EL_TABLE);
+    return CHUB_OK;
+}
+
+extern "C" int64_t chub_algorithmic_bytes(chub_engine *e, int32_t k) {
+    if (!e || !e->have_classes || k < 0 || k >= (int) e->classes.size()) return -1;
+    const int64_t n = e->classes[k].n[0] + e->classes[k].n[1];
+    return 2 * (16 * n + 80) + 4 * (n + 2) + 57;
+}
+
+// ---- static tables ----
+static float h_fast_aa1(float x, float c1) { return (float) ((0.7194 / 0.053) * std::exp(0.053 * x) + 50.15 * x - c1); }
+static double h_fast_anti(double x) {  // antiderivative of the quartic power fit, libm pow like the reference
+    return (0.0002253 / 5) * std::pow(x, 5) - (0.03572 / 4) * std::pow(x, 4) + (2.016 / 3) * std::pow(x, 3) -
+           (48.76 / 2) * std::pow(x, 2) + 457.7 * x;
+}
+
+extern "C" int chub_set_tables(chub_engine *e, const chub_tables *t) {
+    if (!e || !t || !t->arrival_cdf || !t->price || !t->time_sin) return fail(CHUB_ERR_ARG, "chub_set_tables: null argument");
+    CK(cudaSetDevice(e->cfg.device));
+    ChubConst c;
+    memset(&c, 0, sizeof c);
+    for (int i = 0; i < 16; ++i) c.renege[i] = (float) (0.1 * logf((float) (i + 1)));
+    for (int k = 0; k < 64; ++k) c.balk[k] = expf((float) -(0.01 * k));
+    memcpy(c.price, t->price, sizeof c.price);
+    memcpy(c.time_sin, t->time_sin, sizeof c.time_sin);
+    c.price_mean = t->price_mean;
+    c.price_std = t->price_std;
+    c.fast_aa1_c = (float) ((0.7194 / 0.053) * std::exp(0));
+    c.fast_aa2_c = (float) (h_fast_aa1((float) 28.7, c.fast_aa1_c) - h_fast_anti(28.7));
+    {
+        float x = (float) 51.2;
+        float full = (float) ((0.0002253 / 5) * std::pow(x, 5) - (0.03572 / 4) * std::pow(x, 4) +
+                              (2.016 / 3) * std::pow(x, 3) - (48.76 / 2) * std::pow(x, 2) + 457.7 * x + c.fast_aa2_c);
+        c.fast_scale = 100 / full;
+    }
+    {
+        float x = (float) 3.67;
+        c.slow_c2_end = (float) (-4.041 * x + 19.140115 * std::log(std::fabs(x - 0.485)) + 11.943306312699628);
+    }
+    c.slow_stt1_a = -4.276 * std::pow(10, -5);
+    c.slow_stt2_a = 4.742 * std::pow(10, -6);
+    const double jx[10] = {0.50, 5.00, 10.0, 15.0, 20.0, 30.0, 40.0, 50.0, 60.0, 70.0};
+    const double jy[10] = {87.4, 81.0, 86.8, 86.1, 85.4, 83.8, 82.2, 80.4, 78.5, 76.1};
+    for (int i = 0; i < 10; ++i) { c.j_x[i] = jx[i]; c.j_y[i] = jy[i]; }
+    for (int a = 0; a < 8; ++a) c.j_slope[a] = (jy[2 + a] - jy[1 + a]) / (jx[2 + a] - jx[1 + a]);
+    c.topoff_time = (87.4 - 69) / 7.2;
+    c.fcev_cap = 6.3 * 1000;
+    CK(chub_upload_const(c));
+    // traffic-count LUT: for every possible U value r/999.f the first column whose CDF entry is >= it
+    std::vector<uint16_t> lut((size_t) 96 * 1000);
+    for (int tt = 0; tt < 96; ++tt) {
+        const double *row = t->arrival_cdf + (size_t) tt * 301;
+        for (int r = 0; r < 1000; ++r) {
+            float u = (float) r / 999.0f;
+            u = u * (1.0f - 0.0f) + 0.0f;
+            int j = 0;
+            while (j < 301 && !(row[j] >= (double) u)) ++j;
+            lut[(size_t) tt * 1000 + r] = (uint16_t) (j < 301 ? j : 300);
+        }
+    }
+    CK(cudaMemcpy(e->lut, lut.data(), lut.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
+    e->have_tables = true;
+    return CHUB_OK;
+}
+
+extern "C" int chub_set_traces(chub_engine *e, const double *pv, const double *wd, const double *price, int32_t length,
+                               int32_t per_hub) {
+    if (!e || !pv || !wd || !price || length < 1) return fail(CHUB_ERR_ARG, "chub_set_traces: bad argument");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    for (double **p : {&e->pv, &e->wd, &e->price_tr})
+        if (*p) { cudaFree(*p); *p = nullptr; }
+    const size_t row = per_hub ? (size_t) e->Hpad : 1;
+    const size_t n = (size_t) length * row;
+    const double *src[3] = {pv, wd, price};
+    double **dst[3] = {&e->pv, &e->wd, &e->price_tr};
+    for (int a = 0; a < 3; ++a) {
+        CK(dalloc(dst[a], n));
+        if (per_hub)
+            CK(cudaMemcpy2D(*dst[a], row * sizeof(double), src[a], (size_t) e->H * sizeof(double),
+                            (size_t) e->H * sizeof(double), length, cudaMemcpyHostToDevice));
+        else
+            CK(cudaMemcpy(*dst[a], src[a], n * sizeof(double), cudaMemcpyHostToDevice));
+    }
+    e->trace_len = length;
+    e->trace_per_hub = per_hub ? 1 : 0;
+    e->have_traces = true;
+    return CHUB_OK;
+}
+
+static int upload_streams(chub_engine *e, const std::vector<uint2> &keys, const std::vector<uint4> &hubA) {
+    CK(cudaMemcpy(e->keys, keys.data(), sizeof(uint2) * e->H, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(e->hubA, hubA.data(), sizeof(uint4) * e->H, cudaMemcpyHostToDevice));
+    e->have_seed = true;
+    return CHUB_OK;
+}
+
+extern "C" int chub_seed(chub_engine *e, uint64_t base_seed) {
+    if (!e) return fail(CHUB_ERR_ARG, "chub_seed: null engine");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    std::vector<uint2> keys(e->H);
+    std::vector<uint4> hubA(e->H);
+    for (int h = 0; h < e->H; ++h) {
+        uint32_t k0, k1, e0;
+        chub_hub_streams(base_seed, (uint64_t) e->cfg.hub_id_base + (uint64_t) h, &k0, &k1, &e0);
+        keys[h] = make_uint2(k0, k1);
+        hubA[h] = make_uint4(e0, 0u, 0u, 128u | (128u << 8));
+    }
+    return upload_streams(e, keys, hubA);
+}
+
+extern "C" int chub_seed_explicit(chub_engine *e, const uint32_t *key0, const uint32_t *key1, const uint32_t *uctr,
+                                  const uint32_t *lcg) {
+    if (!e || !key0 || !key1 || !lcg) return fail(CHUB_ERR_ARG, "chub_seed_explicit: null argument");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    std::vector<uint2> keys(e->H);
+    std::vector<uint4> hubA(e->H);
+    for (int h = 0; h < e->H; ++h) {
+        if (lcg[h] < 1u || lcg[h] > 2147483646u) return fail(CHUB_ERR_ARG, "chub_seed_explicit: minstd state out of range");
+        keys[h] = make_uint2(key0[h], key1[h]);
+        hubA[h] = make_uint4(lcg[h], uctr ? uctr[h] : 0u, 0u, 128u | (128u << 8));
+    }
+    return upload_streams(e, keys, hubA);
+}
+
+// ---- launches ----
+static int fill_params(chub_engine *e, ChubParams &P) {
+    if (!e->have_classes) return fail(CHUB_ERR_STATE, "call chub_set_hub_classes first");
+    if (!e->have_tables) return fail(CHUB_ERR_STATE, "call chub_set_tables first");
+    if (!e->have_traces) return fail(CHUB_ERR_STATE, "call chub_set_traces first");
+    if (!e->have_seed) return fail(CHUB_ERR_STATE, "call chub_seed first");
+    memset(&P, 0, sizeof P);
+    P.H = e->H; P.Hpad = e->Hpad; P.S0 = e->S0; P.S1 = e->S1;
+    P.n_classes = (int) e->classes.size(); P.action_stride = e->cfg.action_stride;
+    P.auto_reset = e->cfg.auto_reset; P.diagnostics = e->cfg.diagnostics;
+    P.trace_len = e->trace_len; P.trace_per_hub = e->trace_per_hub;
+    P.step_offset = 0; P.step_index = e->step_index;
+    P.pile = e->pile; P.arrive = e->arrive; P.hubA = e->hubA; P.store = e->store; P.keys = e->keys; P.cls = e->cls;
+    P.stats = e->stats; P.last_stats = e->last_stats; P.err = e->err; P.qsoc = e->qsoc;
+    P.classes = e->d_classes; P.el_table = e->d_el; P.lut = e->lut;
+    P.pv = e->pv; P.wd = e->wd; P.price_tr = e->price_tr;
+    P.actions = nullptr; P.obs = e->obs; P.reward = e->reward; P.done = e->done;
+    P.diag = e->diag; P.st_power = e->st_power; P.reset_mask = nullptr;
+    return CHUB_OK;
+}
+
+extern "C" int chub_reset(chub_engine *e, const uint8_t *mask_dev, int64_t step_index, void *stream) {
+    if (!e) return fail(CHUB_ERR_ARG, "chub_reset: null engine");
+    CK(cudaSetDevice(e->cfg.device));
+    ChubParams P;
+    int rc = fill_params(e, P);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t) stream;
+    if (step_index >= 0) {
+        long long v = step_index;
+        CK(cudaMemcpyAsync(e->step_index, &v, sizeof v, cudaMemcpyHostToDevice, s));
+        CK(cudaStreamSynchronize(s));  // v lives on this stack frame
+    }
+    P.reset_mask = mask_dev;
+    chub_launch_reset(P, s);
+    CK(cudaGetLastError());
+    return CHUB_OK;
+}
+
+extern "C" int chub_step(chub_engine *e, const float *actions_dev, void *stream) {
+    if (!e || !actions_dev) return fail(CHUB_ERR_ARG, "chub_step: null argument");
+    CK(cudaSetDevice(e->cfg.device));
+    ChubParams P;
+    int rc = fill_params(e, P);
+    if (rc) return rc;
+    P.actions = actions_dev;
+    cudaStream_t s = (cudaStream_t) stream;
+    chub_launch_step(P, s);
+    chub_launch_tick(e->step_index, 1, s);
+    CK(cudaGetLastError());
+    e->launches += 1;
+    return CHUB_OK;
+}
+
+extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *obs_host, float *reward_host,
+                              uint8_t *done_host, void *stream) {
+    if (!e || !actions_host) return fail(CHUB_ERR_ARG, "chub_step_host: null argument");
+    CK(cudaSetDevice(e->cfg.device));
+    cudaStream_t s = (cudaStream_t) stream;
+    CK(cudaMemcpyAsync(e->actions_stage, actions_host, sizeof(float) * (size_t) e->H * e->cfg.action_stride,
+                       cudaMemcpyHostToDevice, s));
+    int rc = chub_step(e, e->actions_stage, stream);
+    if (rc) return rc;
+    if (obs_host) CK(cudaMemcpyAsync(obs_host, e->obs, sizeof(float) * (size_t) e->H * CHUB_OBS_DIM, cudaMemcpyDeviceToHost, s));
+    if (reward_host) CK(cudaMemcpyAsync(reward_host, e->reward, sizeof(float) * (size_t) e->H, cudaMemcpyDeviceToHost, s));
+    if (done_host) CK(cudaMemcpyAsync(done_host, e->done, (size_t) e->H, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return CHUB_OK;
+}
+
+extern "C" int chub_reset_host(chub_engine *e, float *obs_host, void *stream) {
+    int rc = chub_reset(e, nullptr, 0, stream);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t) stream;
+    if (obs_host) CK(cudaMemcpyAsync(obs_host, e->obs, sizeof(float) * (size_t) e->H * CHUB_OBS_DIM, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return CHUB_OK;
+}
+
+extern "C" int chub_rollout_capture(chub_engine *e, const float *actions_dev, int32_t n_steps, void *stream) {
+    if (!e || !actions_dev || n_steps < 1) return fail(CHUB_ERR_ARG, "chub_rollout_capture: bad argument");
+    CK(cudaSetDevice(e->cfg.device));
+    ChubParams P;
+    int rc = fill_params(e, P);
+    if (rc) return rc;
+    P.actions = actions_dev;
+    if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
+    if (e->graph) { cudaGraphDestroy(e->graph); e->graph = nullptr; }
+    cudaStream_t s = (cudaStream_t) stream;
+    cudaStream_t cap = s;
+    bool own = false;
+    if (cap == nullptr) {  // the legacy default stream cannot be captured
+        CK(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
+        own = true;
+    }
+    CK(cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal));
+    for (int j = 0; j < n_steps; ++j) {  // the step offset is baked per node; one tick per replay
+        P.step_offset = j;
+        chub_launch_step(P, cap);
+    }
+    chub_launch_tick(e->step_index, n_steps, cap);
+    cudaError_t ce = cudaStreamEndCapture(cap, &e->graph);
+    if (own) cudaStreamDestroy(cap);
+    if (ce != cudaSuccess) return fail(CHUB_ERR_CUDA, std::string("capture: ") + cudaGetErrorString(ce));
+    CK(cudaGraphInstantiate(&e->graph_exec, e->graph, 0));
+    e->graph_steps = n_steps;
+    return CHUB_OK;
+}
+
+extern "C" int chub_rollout(chub_engine *e, void *stream) {
+    if (!e || !e->graph_exec) return fail(CHUB_ERR_STATE, "chub_rollout: capture a rollout first");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaGraphLaunch(e->graph_exec, (cudaStream_t) stream));
+    e->launches += e->graph_steps;
+    return CHUB_OK;
+}
+
+extern "C" int chub_counters(chub_engine *e, int64_t *step_index, int64_t *launches, uint32_t *error_or) {
+    if (!e) return fail(CHUB_ERR_ARG, "chub_counters: null engine");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    if (step_index) {
+        long long v = 0;
+        CK(cudaMemcpy(&v, e->step_index, sizeof v, cudaMemcpyDeviceToHost));
+        *step_index = v;
+    }
+    if (launches) *launches = e->launches;
+    if (error_or) {
+        std::vector<uint32_t> er(e->H);
+        CK(cudaMemcpy(er.data(), e->err, sizeof(uint32_t) * e->H, cudaMemcpyDeviceToHost));
+        uint32_t o = 0;
+        for (uint32_t v : er) o |= v;
+        *error_or = o;
+    }
+    return CHUB_OK;
+}
+
+// ---- output buffers, DLPack ----
+struct BufInfo { void *ptr; int64_t bytes; int ndim; int64_t shape[2]; uint8_t code, bits; };
+static bool buf_info(chub_engine *e, int which, BufInfo &b) {
+    const int64_t H = e->H;
+    switch (which) {
+        case CHUB_BUF_OBS: b = {e->obs, H * CHUB_OBS_DIM * 4, 2, {H, CHUB_OBS_DIM}, 2, 32}; return true;
+        case CHUB_BUF_REWARD: b = {e->reward, H * 4, 1, {H, 1}, 2, 32}; return true;
+        case CHUB_BUF_DONE: b = {e->done, H, 1, {H, 1}, 1, 8}; return true;
+        case CHUB_BUF_STATS: b = {e->stats, H * 16, 2, {H, 4}, 2, 32}; return true;
+        case CHUB_BUF_LAST_STATS: b = {e->last_stats, H * 16, 2, {H, 4}, 2, 32}; return true;
+        case CHUB_BUF_ERROR: b = {e->err, H * 4, 1, {H, 1}, 1, 32}; return true;
+    }
+    return false;
+}
+
+extern "C" int chub_buffer(chub_engine *e, int32_t which, void **dev_ptr, int64_t *bytes) {
+    BufInfo b;
+    if (!e || !buf_info(e, which, b)) return fail(CHUB_ERR_ARG, "chub_buffer: bad argument");
+    if (dev_ptr) *dev_ptr = b.ptr;
+    if (bytes) *bytes = b.bytes;
+    return CHUB_OK;
+}
+
+// DLPack v0.8 structures (public ABI of dlpack.h, declared here to avoid a dependency)
+extern "C" {
+typedef struct { int32_t device_type; int32_t device_id; } ChubDLDevice;
+typedef struct { uint8_t code; uint8_t bits; uint16_t lanes; } ChubDLDataType;
+typedef struct {
+    void *data; ChubDLDevice device; int32_t ndim; ChubDLDataType dtype;
+    int64_t *shape; int64_t *strides; uint64_t byte_offset;
+} ChubDLTensor;
+typedef struct ChubDLManagedTensor {
+    ChubDLTensor dl_tensor; void *manager_ctx; void (*deleter)(struct ChubDLManagedTensor *);
+} ChubDLManagedTensor;
+}
+struct DLHolder { ChubDLManagedTensor t; int64_t shape[2]; chub_engine *e; };
+static void dl_deleter(ChubDLManagedTensor *t) {
+    DLHolder *hld = (DLHolder *) t->manager_ctx;
+    engine_unref(hld->e);
+    delete hld;
+}
+
+extern "C" int chub_tensor(chub_engine *e, int32_t which, void **dl_managed_tensor) {
+    BufInfo b;
+    if (!e || !dl_managed_tensor || !buf_info(e, which, b)) return fail(CHUB_ERR_ARG, "chub_tensor: bad argument");
+    DLHolder *hld = new DLHolder();
+    hld->e = e;
+    hld->shape[0] = b.shape[0]; hld->shape[1] = b.shape[1];
+    hld->t.dl_tensor.data = b.ptr;
+    hld->t.dl_tensor.device = {2 /* kDLCUDA */, e->cfg.device};
+    hld->t.dl_tensor.ndim = b.ndim;
+    hld->t.dl_tensor.dtype = {b.code, b.bits, 1};
+    hld->t.dl_tensor.shape = hld->shape;
+    hld->t.dl_tensor.strides = nullptr;
+    hld->t.dl_tensor.byte_offset = 0;
+    hld->t.manager_ctx = hld;
+    hld->t.deleter = dl_deleter;
+    e->refcount += 1;
+    *dl_managed_tensor = &hld->t;
+    return CHUB_OK;
+}
+
+// ---- read-back ----
+extern "C" int chub_get_field(chub_engine *e, int32_t field, void *host_out) {
+    if (!e || !host_out || !e->have_classes) return fail(CHUB_ERR_ARG, "chub_get_field: bad argument");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    const int H = e->H, Hp = e->Hpad;
+    int32_t *oi = (int32_t *) host_out;
+    float *of = (float *) host_out;
+    double *od = (double *) host_out;
+    if (field < 32) {
+        const size_t slots = (size_t) (e->S0 + e->S1) * Hp;
+        std::vector<uint4> pile(slots);
+        std::vector<float> arrive(slots);
+        CK(cudaMemcpy(pile.data(), e->pile, slots * sizeof(uint4), cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(arrive.data(), e->arrive, slots * sizeof(float), cudaMemcpyDeviceToHost));
+        for (int h = 0; h < H; ++h) {
+            const ChubClass &c = e->classes[e->hub_class[h]];
+            for (int s = 0; s < 2; ++s)
+                for (int i = 0; i < CHUB_MAX_PILES; ++i) {
+                    const size_t o = ((size_t) h * 2 + s) * CHUB_MAX_PILES + i;
+                    uint4 r = make_uint4(0, 0, 0, 0);
+                    float arr = 0.f;
+                    if (i < c.n[s]) {
+                        const size_t idx = (size_t) ((s ? e->S0 : 0) + i) * Hp + h;
+                        r = pile[idx];
+                        arr = arrive[idx];
+                    }
+                    const bool car = r.w & PW_CAR;
+                    float fx, fy, fz;
+                    memcpy(&fx, &r.x, 4); memcpy(&fy, &r.y, 4); memcpy(&fz, &r.z, 4);
+                    switch (field) {
+                        case CHUB_F_PILE_CAR: oi[o] = car; break;
+                        case CHUB_F_PILE_CHARGE: oi[o] = (r.w & PW_CHARGE) ? 1 : 0; break;
+                        case CHUB_F_PILE_URGENT: oi[o] = (r.w & PW_URGENT) ? 1 : 0; break;
+                        case CHUB_F_PILE_STAY: oi[o] = car ? (int) (r.w & 0xff) : 0; break;
+                        case CHUB_F_PILE_ALREADY: oi[o] = car ? (int) ((r.w >> 8) & 0xff) : 0; break;
+                        case CHUB_F_PILE_SOC: of[o] = car ? fx : 0.f; break;
+                        case CHUB_F_PILE_TARGET: of[o] = car ? fy : 0.f; break;
+                        case CHUB_F_PILE_POWER: of[o] = car ? fz : 0.f; break;
+                        case CHUB_F_PILE_ARRIVE: of[o] = car ? arr : 0.f; break;
+                        default: return fail(CHUB_ERR_ARG, "chub_get_field: unknown pile field");
+                    }
+                }
+        }
+        return CHUB_OK;
+    }
+    if (field >= CHUB_F_ST_MIN_POWER && field <= CHUB_F_ST_MAX_POWER) {
+        if (!e->st_power) return fail(CHUB_ERR_STATE, "chub_get_field: station powers need diagnostics=1");
+        std::vector<float> sp((size_t) 6 * Hp);
+        CK(cudaMemcpy(sp.data(), e->st_power, sp.size() * sizeof(float), cudaMemcpyDeviceToHost));
+        const int col = field - CHUB_F_ST_MIN_POWER;
+        for (int h = 0; h < H; ++h)
+            for (int s = 0; s < 2; ++s) of[(size_t) h * 2 + s] = sp[(size_t) (3 * s + col) * Hp + h];
+        return CHUB_OK;
+    }
+    if (field >= CHUB_F_DIAG) {
+        const int k = field - CHUB_F_DIAG;
+        if (!e->diag || k >= CHUB_D_COUNT) return fail(CHUB_ERR_STATE, "chub_get_field: diagnostics column unavailable");
+        CK(cudaMemcpy(od, e->diag + (size_t) k * Hp, sizeof(double) * H, cudaMemcpyDeviceToHost));
+        return CHUB_OK;
+    }
+    if (field == CHUB_F_HUB_STORE) {
+        CK(cudaMemcpy(od, e->store, sizeof(double) * H, cudaMemcpyDeviceToHost));
+        return CHUB_OK;
+    }
+    std::vector<uint4> hubA(H);
+    CK(cudaMemcpy(hubA.data(), e->hubA, sizeof(uint4) * H, cudaMemcpyDeviceToHost));
+    std::vector<uint4> pile;
+    if (field == CHUB_F_ST_CAR_NUMBER) {
+        pile.resize((size_t) (e->S0 + e->S1) * Hp);
+        CK(cudaMemcpy(pile.data(), e->pile, pile.size() * sizeof(uint4), cudaMemcpyDeviceToHost));
+    }
+    for (int h = 0; h < H; ++h) {
+        const uint4 a = hubA[h];
+        switch (field) {
+            case CHUB_F_ST_LINE: oi[2 * h] = (a.z >> 8) & 0xff; oi[2 * h + 1] = (a.z >> 16) & 0xff; break;
+            case CHUB_F_ST_FLOW_IN: oi[2 * h] = (int) (a.w & 0xff) - 128; oi[2 * h + 1] = (int) ((a.w >> 8) & 0xff) - 128; break;
+            case CHUB_F_ST_CAR_NUMBER: {
+                const ChubClass &c = e->classes[e->hub_class[h]];
+                for (int s = 0; s < 2; ++s) {
+                    int cnt = 0;
+                    for (int i = 0; i < c.n[s]; ++i)
+                        cnt += (pile[(size_t) ((s ? e->S0 : 0) + i) * Hp + h].w & PW_CAR) ? 1 : 0;
+                    oi[2 * h + s] = cnt;
+                }
+                break;
+            }
+            case CHUB_F_HUB_T: oi[h] = a.z & 0xff; break;
+            case CHUB_F_HUB_UCTR: oi[h] = (int32_t) a.y; break;
+            case CHUB_F_HUB_LCG: oi[h] = (int32_t) a.x; break;
+            case CHUB_F_FCEV_ARRIVE: oi[h] = a.w >> 24; break;
+            case CHUB_F_FCEV_QN: oi[h] = a.z >> 24; break;
+            default: return fail(CHUB_ERR_ARG, "chub_get_field: unknown field");
+        }
+    }
+    return CHUB_OK;
+}
+
+// ---- checkpoint blob: every mutable state array, in a fixed order ----
+struct Seg { void *p; size_t bytes; };
+static std::vector<Seg> state_segments(chub_engine *e) {
+    const size_t Hp = e->Hpad, slots = (size_t) (e->S0 + e->S1) * Hp;
+    return {{e->pile, slots * sizeof(uint4)}, {e->arrive, slots * sizeof(float)}, {e->hubA, Hp * sizeof(uint4)},
+            {e->store, Hp * sizeof(double)}, {e->keys, Hp * sizeof(uint2)}, {e->stats, Hp * sizeof(float4)},
+            {e->last_stats, Hp * sizeof(float4)}, {e->err, Hp * sizeof(uint32_t)},
+            {e->qsoc, Hp * CHUB_FCEV_QCAP * sizeof(float)}, {e->step_index, sizeof(long long)}};
+}
+extern "C" int64_t chub_state_bytes(chub_engine *e) {
+    if (!e || !e->have_classes) return -1;
+    size_t n = 0;
+    for (const Seg &s : state_segments(e)) n += s.bytes;
+    return (int64_t) n;
+}
+extern "C" int chub_get_state(chub_engine *e, void *host_blob) {
+    if (!e || !host_blob || !e->have_classes) return fail(CHUB_ERR_ARG, "chub_get_state: bad argument");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    char *o = (char *) host_blob;
+    for (const Seg &s : state_segments(e)) {
+        CK(cudaMemcpy(o, s.p, s.bytes, cudaMemcpyDeviceToHost));
+        o += s.bytes;
+    }
+    return CHUB_OK;
+}
+extern "C" int chub_set_state(chub_engine *e, const void *host_blob) {
+    if (!e || !host_blob || !e->have_classes) return fail(CHUB_ERR_ARG, "chub_set_state: bad argument");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    const char *o = (const char *) host_blob;
+    for (const Seg &s : state_segments(e)) {
+        CK(cudaMemcpy(s.p, o, s.bytes, cudaMemcpyHostToDevice));
+        o += s.bytes;
+    }
+    e->have_seed = true;
+    return CHUB_OK;
+}
+
+// pinned host memory for the callers of chub_step_host
+extern "C" int chub_alloc_host(int64_t bytes, void **out) {
+    if (!out || bytes <= 0) return fail(CHUB_ERR_ARG, "chub_alloc_host: bad argument");
+    CK(cudaMallocHost(out, (size_t) bytes));
+    return CHUB_OK;
+}
+extern "C" int chub_free_host(void *p) {
+    if (p) CK(cudaFreeHost(p));
+    return CHUB_OK;
+}

@@ -1,0 +1,52 @@
+// chub_kernels.cuh -- launch parameters and HBM layout of the hub step / reset kernels.
+#pragma once
+#include "chub_device.cuh"
+
+// HBM layout (SoA, hub index fastest so a warp of 32 hubs touches one contiguous row):
+//   pile[(slot) * Hpad + h]   uint4 {soc f32, target f32, power f32, packed}     slot = station0 piles, then station1 piles
+//   arrive[(slot) * Hpad + h] float  arrival SOC ("init_soc" column; written once per car, never read by the step)
+//   hubA[h]                   uint4 {minstd state, U counter, packed1, packed2}
+//   store[h]                  double hydrogen store mass in grams
+//   keys[h]                   uint2  U-stream keys (read only)
+//   stats[h], last_stats[h]   float4 {episode return, income, grid energy, incomplete departures}
+//   qsoc[(j) * Hpad + h]      float  FCEV backlog arrival SOCs (cold; touched only when a backlog exists)
+// packed pile word : bits 0-7 stay_time, 8-15 already_stay_time, 16 car, 17 charge, 18 urgent,
+//                    19-23 ceil(needed_time) cache (0 = needed_time <= 0)
+// packed1          : bits 0-7 t (time hole), 8-15 line[0], 16-23 line[1], 24-31 FCEV backlog length
+// packed2          : bits 0-7 flow_in[0]+128, 8-15 flow_in[1]+128, 16-23 FCEV line, 24-31 FCEV arrivals
+#define PW_CAR (1u << 16)
+#define PW_CHARGE (1u << 17)
+#define PW_URGENT (1u << 18)
+
+struct ChubParams {
+    int H, Hpad, S0, S1;
+    int n_classes, action_stride, auto_reset, diagnostics;
+    int trace_len, trace_per_hub;
+    int step_offset;                  // added to *step_index (graph-captured rollouts bake 0..n-1)
+    const long long *step_index;      // device: absolute step index of the state being left
+    uint4 *pile;
+    float *arrive;
+    uint4 *hubA;
+    double *store;
+    const uint2 *keys;
+    const int *cls;                   // NULL when n_classes == 1
+    float4 *stats, *last_stats;
+    uint32_t *err;
+    float *qsoc;
+    const ChubClass *classes;
+    const double *el_table;           // [n_classes][102]
+    const uint16_t *lut;              // [96][1000] traffic count for u = r/999.f (CHS.hpp:731-743)
+    const double *pv, *wd, *price_tr;
+    const float *actions;
+    float *obs;
+    float *reward;
+    uint8_t *done;
+    double *diag;                     // [CHUB_D_COUNT][Hpad] or NULL
+    float *st_power;                  // [6][Hpad] (min,charge,max) x 2 stations, or NULL
+    const uint8_t *reset_mask;        // reset kernel only
+};
+
+void chub_launch_step(const ChubParams &p, cudaStream_t s);
+void chub_launch_reset(const ChubParams &p, cudaStream_t s);
+void chub_launch_tick(long long *step_index, int n, cudaStream_t s);
+cudaError_t chub_upload_const(const ChubConst &c);

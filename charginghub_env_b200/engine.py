@@ -1,0 +1,265 @@
+"""HubEngine: Python face of the C ABI (include/chub.h) -- one shard of hubs on one B200.
+
+It mirrors, for a batch, what the reference does for one hub through EvcsspManagerEnv_v6
+(evcssp_env_cpp/envs/evcssp_manager.py:19-414): constructor kwargs become hub classes, reset() and
+step(action) keep their meaning, observations / rewards / done flags come back as torch tensors
+that alias engine memory through DLPack (no copy), or as numpy arrays through the host-buffer path.
+All stepping happens in the CUDA library; this module contains no simulation arithmetic.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+from . import _lib
+from ._lib import ChubError, check
+
+_DATA = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "hub_tables.npz")
+_TYPE = {"fast": _lib.FAST, "slow": _lib.SLOW}
+
+
+def load_tables(path=None):
+    """Static tables of the hub model: arrival CDF, prices, PV / wind day traces (tools/make_data.py)."""
+    z = np.load(path or _DATA)
+    price = np.ascontiguousarray(z["price"], np.float64)
+    k = 2 * np.pi / 96
+    return dict(arrival_cdf=np.ascontiguousarray(z["arrival_cdf"], np.float64), price=price,
+                price_mean=float(np.mean(price)), price_std=float(np.std(price)),
+                time_sin=np.sin(k * np.arange(96, dtype=np.float64)),
+                pv_days=np.ascontiguousarray(z["pv_days"], np.float64),
+                wd_days=np.ascontiguousarray(z["wd_days"], np.float64))
+
+
+def make_hub_class(station_list=(20, 25), station_type_list=("fast", "slow"), constant_charging=False,
+                   hydro_prod_rate=None, hydro_store_vlt=None, seed_rand=True, init_soc=0.5, fc_max_power=None,
+                   fcev_permeate=0.01, use_lagrange=False, renew_fluctuate=0, price_fluctuate=0, hydro_loss=0,
+                   el_table=None):
+    """The reference's constructor kwargs (evcssp_manager.py:25-27) -> chub_hub_class."""
+    if len(station_list) != 2 or len(station_type_list) != 2:
+        raise ValueError("station_list and station_type_list must have length 2")  # evcssp_manager.py:37
+    c = _lib.HubClass()
+    c.n_piles[0], c.n_piles[1] = int(station_list[0]), int(station_list[1])
+    try:
+        c.station_type[0], c.station_type[1] = _TYPE[station_type_list[0]], _TYPE[station_type_list[1]]
+    except KeyError:
+        raise ValueError("EVS type must be fast or slow")  # Aggregator_Simple.py:196
+    c.constant_charging = int(bool(constant_charging))
+    c.hydro_prod_rate = float(hydro_prod_rate) if hydro_prod_rate is not None else -1.0
+    c.hydro_store_vlt = float(hydro_store_vlt) if hydro_store_vlt is not None else -1.0
+    c.init_soc = float(init_soc)
+    c.fc_max_power = float(fc_max_power) if fc_max_power is not None else -1.0
+    c.fcev_permeate = float(fcev_permeate)
+    c.hydro_loss = float(hydro_loss)
+    keep = None
+    if el_table is not None:
+        keep = np.ascontiguousarray(el_table, np.float64)
+        if keep.shape != (_lib.EL_TABLE,):
+            raise ValueError("el_table must have %d entries" % _lib.EL_TABLE)
+        c.el_table = keep.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
+    return c, keep
+
+
+def _dptr(a):
+    return a.ctypes.data_as(ctypes.c_void_p) if a is not None else None
+
+
+def _tensor_ptr(t):
+    """Device pointer of a torch CUDA tensor (float32/uint8, contiguous) or a raw int."""
+    if isinstance(t, int):
+        return ctypes.c_void_p(t)
+    if not t.is_cuda or not t.is_contiguous():
+        raise ValueError("expected a contiguous CUDA tensor")
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def _current_stream(device):
+    import torch
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+class HubEngine(object):
+    def __init__(self, n_hubs, classes=None, hub_class=None, device=0, hub_id_base=0, action_stride=None,
+                 auto_reset=False, diagnostics=False, tables=None, seed=0):
+        self.lib = _lib.load()
+        classes = list(classes) if classes is not None else [dict()]
+        self.class_kwargs = classes
+        self._keep = []
+        arr = (_lib.HubClass * len(classes))()
+        n_act = 0
+        for k, kw in enumerate(classes):
+            c, keep = make_hub_class(**kw)
+            arr[k] = c
+            self._keep.append(keep)
+            n_act = max(n_act, c.n_piles[0] + c.n_piles[1] + 2)
+        self.n_hubs = int(n_hubs)
+        self.device = int(device)
+        self.action_dim = n_act
+        self.action_stride = int(action_stride) if action_stride is not None else n_act
+        cfg = _lib.Config(n_hubs=self.n_hubs, device=self.device, hub_id_base=int(hub_id_base),
+                          n_classes=len(classes), action_stride=self.action_stride,
+                          auto_reset=int(bool(auto_reset)), diagnostics=int(bool(diagnostics)))
+        h = ctypes.c_void_p()
+        check(self.lib.chub_create(ctypes.byref(cfg), ctypes.byref(h)))
+        self.h = h
+        self.diagnostics = bool(diagnostics)
+        hc = None
+        if hub_class is not None:
+            hc = np.ascontiguousarray(hub_class, np.int32)
+            if hc.shape != (self.n_hubs,):
+                raise ValueError("hub_class must have one entry per hub")
+        self.hub_class = hc
+        check(self.lib.chub_set_hub_classes(self.h, arr, len(classes), _dptr(hc)))
+        self.tables = tables if tables is not None else load_tables()
+        t = _lib.Tables()
+        self._tab_keep = [np.ascontiguousarray(self.tables[k], np.float64) for k in ("arrival_cdf", "price", "time_sin")]
+        t.arrival_cdf = self._tab_keep[0].ctypes.data_as(ctypes.POINTER(ctypes.c_double))
+        t.price = self._tab_keep[1].ctypes.data_as(ctypes.POINTER(ctypes.c_double))
+        t.time_sin = self._tab_keep[2].ctypes.data_as(ctypes.POINTER(ctypes.c_double))
+        t.price_mean, t.price_std = float(self.tables["price_mean"]), float(self.tables["price_std"])
+        check(self.lib.chub_set_tables(self.h, ctypes.byref(t)))
+        self._tensors = {}
+        self._host = None
+        if seed is not None:
+            self.seed(seed)
+
+    # ---- lifetime ----
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h.value:
+            self._tensors.clear()
+            if self._host is not None:
+                for p in self._host["ptrs"]:
+                    self.lib.chub_free_host(p)
+                self._host = None
+            self.lib.chub_destroy(self.h)
+            self.h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- configuration ----
+    def class_table(self, k=0):
+        out = np.empty(_lib.EL_TABLE, np.float64)
+        check(self.lib.chub_get_class_table(self.h, k, _dptr(out)))
+        return out
+
+    def algorithmic_bytes(self, k=0):
+        return int(self.lib.chub_algorithmic_bytes(self.h, k))
+
+    def set_traces(self, pv, wd, price, per_hub=False):
+        """pv (already x5), wd, price (table[t-1] + noise): [L] shared or [L, n_hubs] per hub."""
+        a = [np.ascontiguousarray(x, np.float64) for x in (pv, wd, price)]
+        want = (a[0].shape[0], self.n_hubs) if per_hub else (a[0].shape[0],)
+        for x in a:
+            if x.shape != want:
+                raise ValueError("trace shape %s, expected %s" % (x.shape, want))
+        check(self.lib.chub_set_traces(self.h, _dptr(a[0]), _dptr(a[1]), _dptr(a[2]), a[0].shape[0], int(per_hub)))
+
+    def seed(self, base_seed):
+        check(self.lib.chub_seed(self.h, ctypes.c_uint64(int(base_seed) & ((1 << 64) - 1))))
+
+    def seed_explicit(self, key0, key1, lcg, uctr=None):
+        a = [np.ascontiguousarray(x, np.uint32) for x in (key0, key1, lcg)]
+        c = np.ascontiguousarray(uctr, np.uint32) if uctr is not None else None
+        check(self.lib.chub_seed_explicit(self.h, _dptr(a[0]), _dptr(a[1]), _dptr(c), _dptr(a[2])))
+
+    # ---- device path ----
+    def _stream(self, stream):
+        if stream is not None:
+            return ctypes.c_void_p(int(stream))
+        return _current_stream(self.device)
+
+    def reset(self, mask=None, step_index=0, stream=None):
+        """reset() of every hub (or of hubs whose mask byte is set; mask = CUDA uint8 tensor)."""
+        m = _tensor_ptr(mask) if mask is not None else None
+        check(self.lib.chub_reset(self.h, m, int(step_index), self._stream(stream)))
+        return self.tensor("obs")
+
+    def step(self, actions, stream=None):
+        """step(action) of every hub.  actions: CUDA float32 [n_hubs, action_stride] in [-1, 1]."""
+        if tuple(actions.shape) != (self.n_hubs, self.action_stride):
+            raise ValueError("actions must be [%d, %d]" % (self.n_hubs, self.action_stride))  # evcssp_manager.py:148
+        check(self.lib.chub_step(self.h, _tensor_ptr(actions), self._stream(stream)))
+        return self.tensor("obs"), self.tensor("reward"), self.tensor("done")
+
+    def capture_rollout(self, actions, n_steps, stream=None):
+        check(self.lib.chub_rollout_capture(self.h, _tensor_ptr(actions), int(n_steps), self._stream(stream)))
+
+    def rollout(self, stream=None):
+        check(self.lib.chub_rollout(self.h, self._stream(stream)))
+
+    def tensor(self, name):
+        """torch view (DLPack, zero copy) of an engine buffer: obs, reward, done, stats, last_stats, error."""
+        if name in self._tensors:
+            return self._tensors[name]
+        import torch
+        which = {"obs": _lib.BUF_OBS, "reward": _lib.BUF_REWARD, "done": _lib.BUF_DONE, "stats": _lib.BUF_STATS,
+                 "last_stats": _lib.BUF_LAST_STATS, "error": _lib.BUF_ERROR}[name]
+        p = ctypes.c_void_p()
+        check(self.lib.chub_tensor(self.h, which, ctypes.byref(p)))
+        ctypes.pythonapi.PyCapsule_New.restype = ctypes.py_object
+        ctypes.pythonapi.PyCapsule_New.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_void_p]
+        cap = ctypes.pythonapi.PyCapsule_New(p, b"dltensor", None)
+        t = torch.from_dlpack(cap)
+        self._tensors[name] = t
+        return t
+
+    # ---- host path (what a CPU caller of the reference has) ----
+    def host_buffers(self):
+        """Pinned numpy arrays: actions [H, stride] f32, obs [H, 13] f32, reward [H] f32, done [H] u8."""
+        if self._host is None:
+            def pinned(n, ct, dt, shape):
+                p = ctypes.c_void_p()
+                check(self.lib.chub_alloc_host(n * ctypes.sizeof(ct), ctypes.byref(p)))
+                a = np.ctypeslib.as_array((ct * n).from_address(p.value)).view(dt).reshape(shape)
+                return p, a
+            H, S = self.n_hubs, self.action_stride
+            pa, a = pinned(H * S, ctypes.c_float, np.float32, (H, S))
+            po, o = pinned(H * _lib.OBS_DIM, ctypes.c_float, np.float32, (H, _lib.OBS_DIM))
+            pr, r = pinned(H, ctypes.c_float, np.float32, (H,))
+            pd, d = pinned(H, ctypes.c_uint8, np.uint8, (H,))
+            self._host = dict(ptrs=[pa, po, pr, pd], actions=a, obs=o, reward=r, done=d)
+        return self._host
+
+    def step_host(self, actions=None, stream=0):
+        """Host-buffer step: H2D actions, step, D2H obs/reward/done, synchronise."""
+        hb = self.host_buffers()
+        if actions is not None:
+            hb["actions"][...] = actions
+        check(self.lib.chub_step_host(self.h, _dptr(hb["actions"]), _dptr(hb["obs"]), _dptr(hb["reward"]),
+                                      _dptr(hb["done"]), ctypes.c_void_p(int(stream))))
+        return hb["obs"], hb["reward"], hb["done"]
+
+    def reset_host(self, stream=0):
+        hb = self.host_buffers()
+        check(self.lib.chub_reset_host(self.h, _dptr(hb["obs"]), ctypes.c_void_p(int(stream))))
+        return hb["obs"]
+
+    # ---- read-back ----
+    def get(self, name):
+        fid, dt, shp = _lib.FIELDS[name]
+        out = np.empty((self.n_hubs,) + shp, dtype=dt)
+        check(self.lib.chub_get_field(self.h, fid, _dptr(out)))
+        return out
+
+    def counters(self):
+        s, l, e = ctypes.c_int64(), ctypes.c_int64(), ctypes.c_uint32()
+        check(self.lib.chub_counters(self.h, ctypes.byref(s), ctypes.byref(l), ctypes.byref(e)))
+        return dict(step_index=s.value, launches=l.value, error_or=e.value)
+
+    def get_state(self):
+        n = int(self.lib.chub_state_bytes(self.h))
+        blob = np.empty(n, np.uint8)
+        check(self.lib.chub_get_state(self.h, _dptr(blob)))
+        return blob
+
+    def set_state(self, blob):
+        blob = np.ascontiguousarray(blob, np.uint8)
+        if blob.size != int(self.lib.chub_state_bytes(self.h)):
+            raise ValueError("state blob size mismatch")
+        check(self.lib.chub_set_state(self.h, _dptr(blob)))
+
+
+__all__ = ["HubEngine", "ChubError", "load_tables", "make_hub_class"]

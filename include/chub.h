@@ -1,0 +1,187 @@
+/* chub.h -- C ABI of the B200 batched charging-hub stepping engine (libchub.so).
+ *
+ * This is the drop-in boundary for the reference's step/reset path.  In the reference that path
+ * crosses a Boost.Python module, `pyevstation` (evcssp_env_cpp/envs/lion_cpp20/main.cpp:19-290),
+ * roughly ten times per env step and per hub: SlowChargeStation/FastChargeStation.evs_step /
+ * evs_reset (main.cpp:186-233, called from Aggregator_Simple.py:141-142,168-169), Vector_float
+ * appends (Aggregator_Simple.py:132-139), PoissonNumber.hv_car_number_wrt_poisson and
+ * CarArriveRandom.mk_soc (hydro_sys.py:251,259), and ~20 attribute reads
+ * (evcssp_manager.py:366-368, Aggregator_Simple.py:208-218).  Here the WHOLE of
+ * EvcsspManagerEnv_v6.step()/reset() (evcssp_manager.py:136-316) for a batch of hubs is one call.
+ *
+ * Conventions: plain C, no exceptions; every function returns CHUB_OK (0) or a negative error and
+ * records a message readable with chub_last_error(); all device work is stream ordered on the
+ * cudaStream_t passed in (as void*; NULL = legacy default stream); the engine owns all device
+ * memory; pointers named *_dev are device pointers owned by the caller.  One engine per CUDA
+ * device; calls on one engine must be serialised by the caller.
+ */
+#ifndef CHUB_H
+#define CHUB_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CHUB_OK 0
+#define CHUB_ERR_ARG (-1)
+#define CHUB_ERR_CUDA (-2)
+#define CHUB_ERR_STATE (-3)
+#define CHUB_ERR_UNSUPPORTED (-4)
+
+#define CHUB_MAX_PILES 32   /* piles per station (fast or slow) */
+#define CHUB_OBS_DIM 13     /* evcssp_manager.py:74-95 with both stations populated */
+#define CHUB_EL_TABLE 102   /* hy_power_speed_list, hydro_sys.py:154-157 */
+#define CHUB_FCEV_QCAP 8    /* FCEV backlog entries kept per hub (reference list is unbounded) */
+#define CHUB_DAY 96         /* steps per episode, evcssp_manager.py:53 */
+
+#define CHUB_FAST 0
+#define CHUB_SLOW 1
+
+/* sticky per-hub error bits (the reference would print or raise) */
+#define CHUB_HUBERR_FCEV_OVERFLOW 1u   /* FCEV list longer than CHUB_FCEV_QCAP (hydro_sys.py:266-285) */
+#define CHUB_HUBERR_STORE_ASSERT 2u    /* hydro_sys.py:111-112 assert would have fired */
+#define CHUB_HUBERR_COUNTER 4u         /* a stay/queue counter left its packed range */
+
+typedef struct chub_engine chub_engine;
+
+/* Engine-wide configuration. */
+typedef struct chub_config {
+    int32_t n_hubs;          /* hubs stepped by THIS engine (the local shard) */
+    int32_t device;          /* CUDA device ordinal */
+    int64_t hub_id_base;     /* global id of local hub 0; seeds are f(base_seed, global id) */
+    int32_t n_classes;       /* number of hub parameter classes (>=1) */
+    int32_t action_stride;   /* floats per hub row of the action matrix, >= max(n0+n1)+2 */
+    int32_t auto_reset;      /* 1: a hub that reports done is reset inside the same launch */
+    int32_t diagnostics;     /* 1: also write the fp64 diagnostic columns (parity tests) */
+    int32_t reserved[4];
+} chub_config;
+
+/* One hub parameter class == one set of the reference's constructor kwargs
+ * (evcssp_manager.py:25-27, test/env_test.py:10-30).  Negative optional values mean "None". */
+typedef struct chub_hub_class {
+    int32_t n_piles[2];          /* station_list */
+    int32_t station_type[2];     /* station_type_list: CHUB_FAST / CHUB_SLOW */
+    int32_t constant_charging;
+    int32_t reserved;
+    double hydro_prod_rate;      /* m^3/h; <=0 -> 430 (hydro_sys.py:140-143) */
+    double hydro_store_vlt;      /* m^3;   <=0 -> 5000 (hydro_sys.py:96) */
+    double init_soc;             /* store SOC at reset, in [0.1, 1] (hydro_sys.py:137) */
+    double fc_max_power;         /* kW; <0 -> 100 (hydro_sys.py:401-404) */
+    double fcev_permeate;        /* hydro_sys.py:248 */
+    double hydro_loss;           /* hydro_sys.py:121 */
+    /* optional explicit electrolyser power table (hy_power_speed_list); NULL -> the engine builds
+     * the table the reference obtains when the store is not clipped during construction */
+    const double *el_table;      /* [CHUB_EL_TABLE] or NULL */
+} chub_hub_class;
+
+/* Static tables (host pointers, copied). */
+typedef struct chub_tables {
+    const double *arrival_cdf;   /* [96][301] car_flow_possibility_list as parsed by CHS.hpp:93-175 */
+    const double *price;         /* [96] price_after_MAD_96 (Aggregator_Simple.py:9-15) */
+    double price_mean, price_std;/* evcssp_manager.py:45-46 */
+    const double *time_sin;      /* [96] sin(2*pi*t/96) (evcssp_manager.py:319-320) */
+} chub_tables;
+
+/* Which buffer chub_buffer()/chub_tensor() exposes. */
+enum chub_buffer_id {
+    CHUB_BUF_OBS = 0,        /* float32 [n_hubs][13] */
+    CHUB_BUF_REWARD = 1,     /* float32 [n_hubs] */
+    CHUB_BUF_DONE = 2,       /* uint8   [n_hubs] */
+    CHUB_BUF_STATS = 3,      /* float32 [n_hubs][4]: episode return, income, grid energy drawn (kW-steps), incomplete departures */
+    CHUB_BUF_LAST_STATS = 4, /* float32 [n_hubs][4]: the same, frozen at the last completed episode */
+    CHUB_BUF_ERROR = 5       /* uint32  [n_hubs] sticky error bits */
+};
+
+/* Field ids for chub_get_field (read-back for parity tests, introspection, checkpoints).
+ * Output is hub-major, dense, host memory. */
+enum chub_field_id {
+    CHUB_F_PILE_CAR = 0, CHUB_F_PILE_CHARGE, CHUB_F_PILE_URGENT, CHUB_F_PILE_STAY, CHUB_F_PILE_ALREADY, /* int32 [H][2][32] */
+    CHUB_F_PILE_SOC = 16, CHUB_F_PILE_TARGET, CHUB_F_PILE_POWER, CHUB_F_PILE_ARRIVE,                   /* float [H][2][32] */
+    CHUB_F_ST_LINE = 32, CHUB_F_ST_FLOW_IN, CHUB_F_ST_CAR_NUMBER,                                      /* int32 [H][2] */
+    CHUB_F_ST_MIN_POWER = 48, CHUB_F_ST_CHARGE_POWER, CHUB_F_ST_MAX_POWER,                             /* float [H][2], diagnostics only */
+    CHUB_F_HUB_T = 64, CHUB_F_HUB_UCTR, CHUB_F_HUB_LCG, CHUB_F_FCEV_ARRIVE, CHUB_F_FCEV_QN,            /* int32 [H] */
+    CHUB_F_HUB_STORE = 80,                                                                             /* double [H] */
+    CHUB_F_DIAG = 96   /* CHUB_F_DIAG + k: double [H], diagnostics column k (enum chub_diag_id) */
+};
+
+enum chub_diag_id {
+    CHUB_D_REWARD = 0, CHUB_D_INCOME, CHUB_D_HY_FLOW, CHUB_D_H2_POWER, CHUB_D_FC_POWER, CHUB_D_HY_USE,
+    CHUB_D_NOT_MEET, CHUB_D_HY_TO_USE, CHUB_D_DEMAND, CHUB_D_EV_GRID0, CHUB_D_EV_GRID1, CHUB_D_H2_GRID,
+    CHUB_D_HY_ACT, CHUB_D_STORE_SOC, CHUB_D_COUNT
+};
+
+const char *chub_last_error(void);
+int chub_version(void);
+
+int chub_create(const chub_config *cfg, chub_engine **out);
+int chub_destroy(chub_engine *e);
+
+/* classes[n_classes]; hub_class = per-hub class index [n_hubs] (host) or NULL when n_classes == 1 */
+int chub_set_hub_classes(chub_engine *e, const chub_hub_class *classes, int32_t n_classes, const int32_t *hub_class);
+int chub_set_tables(chub_engine *e, const chub_tables *t);
+/* read back the electrolyser table the engine uses for class k (host, [CHUB_EL_TABLE]) */
+int chub_get_class_table(chub_engine *e, int32_t k, double *out);
+
+/* Exogenous traces (the reference's ReNew + OU noise + price list, renewable.py:21-76,
+ * evcssp_manager.py:344-361): value seen in the state at absolute step index s is trace[s % length].
+ * pv is the scaled PV power (x5), wd the wind power, price = table[t-1] + noise.
+ * per_hub = 0: arrays [length];  per_hub = 1: arrays [length][n_hubs].  Host pointers, copied. */
+int chub_set_traces(chub_engine *e, const double *pv, const double *wd, const double *price,
+                    int32_t length, int32_t per_hub);
+
+/* Streams: either derive (key0,key1,minstd state) from base_seed and the global hub id
+ * (include/chub_rng.h), or set them explicitly (host arrays [n_hubs]; uctr may be NULL = 0). */
+int chub_seed(chub_engine *e, uint64_t base_seed);
+int chub_seed_explicit(chub_engine *e, const uint32_t *key0, const uint32_t *key1, const uint32_t *uctr,
+                       const uint32_t *lcg);
+
+/* reset(): EvcsspManagerEnv_v6.reset (evcssp_manager.py:304-316) for every hub, or for hubs whose
+ * mask byte is non-zero (mask_dev: device uint8 [n_hubs] or NULL).  Also rewinds the absolute
+ * step index to `step_index` (use 0).  Fills the obs buffer. */
+int chub_reset(chub_engine *e, const uint8_t *mask_dev, int64_t step_index, void *stream);
+
+/* step(action): EvcsspManagerEnv_v6.step (evcssp_manager.py:136-302) for every hub.
+ * actions_dev: float32 [n_hubs][action_stride], row = [pile actions of station 0, station 1, a[-2], a[-1]]
+ * in [-1,1] exactly as the reference's action vector.  Fills obs / reward / done buffers. */
+int chub_step(chub_engine *e, const float *actions_dev, void *stream);
+
+/* The same through HOST buffers (what a CPU caller of the reference has): copies the actions in,
+ * steps, copies obs/reward/done out, and synchronises the stream.  Any out pointer may be NULL. */
+int chub_step_host(chub_engine *e, const float *actions_host, float *obs_host, float *reward_host,
+                   uint8_t *done_host, void *stream);
+int chub_reset_host(chub_engine *e, float *obs_host, void *stream);
+
+/* n_steps step launches captured once into a CUDA graph and replayed; the action buffer is re-read
+ * at every step, so a policy writing into it on the same stream may be captured by the caller
+ * instead.  chub_rollout replays the captured graph. */
+int chub_rollout_capture(chub_engine *e, const float *actions_dev, int32_t n_steps, void *stream);
+int chub_rollout(chub_engine *e, void *stream);
+
+/* Raw device pointer + byte size of an engine-owned output buffer. */
+int chub_buffer(chub_engine *e, int32_t which, void **dev_ptr, int64_t *bytes);
+/* DLPack export (DLManagedTensor*, version 0.8 layout) of the same buffers; the tensor is a view and
+ * keeps the engine alive until its deleter runs. */
+int chub_tensor(chub_engine *e, int32_t which, void **dl_managed_tensor);
+
+/* Parity / checkpoint read-back (synchronises). */
+int chub_get_field(chub_engine *e, int32_t field, void *host_out);
+int64_t chub_state_bytes(chub_engine *e);
+int chub_get_state(chub_engine *e, void *host_blob);
+int chub_set_state(chub_engine *e, const void *host_blob);
+
+/* Absolute step index, number of step kernel launches so far, and sum of sticky error bits. */
+int chub_counters(chub_engine *e, int64_t *step_index, int64_t *launches, uint32_t *error_or);
+
+/* Pinned host memory for chub_step_host / chub_reset_host callers. */
+int chub_alloc_host(int64_t bytes, void **out);
+int chub_free_host(void *p);
+
+/* Algorithmic HBM bytes of one hub-step for class k: B(nf,ns) of SURVEY.md section 8d. */
+int64_t chub_algorithmic_bytes(chub_engine *e, int32_t k);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CHUB_H */
