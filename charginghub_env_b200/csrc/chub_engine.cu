@@ -39,7 +39,7 @@ struct chub_engine {
     uint4 *pile = nullptr; float *arrive = nullptr; uint4 *hubA = nullptr; double *store = nullptr;
     uint2 *keys = nullptr; int *cls = nullptr; float4 *stats = nullptr, *last_stats = nullptr;
     uint32_t *err = nullptr; float *qsoc = nullptr; ChubClass *d_classes = nullptr; double *d_el = nullptr;
-    uint16_t *lut = nullptr; double *pv = nullptr, *wd = nullptr, *price_tr = nullptr;
+    uint16_t *lut = nullptr; float *s2t_lut = nullptr; double *pv = nullptr, *wd = nullptr, *price_tr = nullptr;
     float *obs = nullptr, *reward = nullptr; uint8_t *done = nullptr; double *diag = nullptr; float *st_power = nullptr;
     long long *step_index = nullptr;
     float *actions_stage = nullptr;  // device copy target of chub_step_host
@@ -59,7 +59,7 @@ static void engine_free(chub_engine *e) {
     if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
     if (e->graph) cudaGraphDestroy(e->graph);
     void *ptrs[] = {e->pile, e->arrive, e->hubA, e->store, e->keys, e->cls, e->stats, e->last_stats, e->err, e->qsoc,
-                    e->d_classes, e->d_el, e->lut, e->pv, e->wd, e->price_tr, e->obs, e->reward, e->done, e->diag,
+                    e->d_classes, e->d_el, e->lut, e->s2t_lut, e->pv, e->wd, e->price_tr, e->obs, e->reward, e->done, e->diag,
                     e->st_power, e->step_index, e->actions_stage};
     for (void *p : ptrs)
         if (p) cudaFree(p);
@@ -95,7 +95,7 @@ extern "C" int chub_create(const chub_config *cfg, chub_engine **out) {
     auto A = [&](cudaError_t x) { if (r == cudaSuccess) r = x; };
     A(dalloc(&e->hubA, Hp)); A(dalloc(&e->store, Hp)); A(dalloc(&e->keys, Hp));
     A(dalloc(&e->stats, Hp)); A(dalloc(&e->last_stats, Hp)); A(dalloc(&e->err, Hp));
-    A(dalloc(&e->qsoc, Hp * CHUB_FCEV_QCAP)); A(dalloc(&e->lut, (size_t) 96 * 1000));
+    A(dalloc(&e->qsoc, Hp * CHUB_FCEV_QCAP)); A(dalloc(&e->lut, (size_t) 96 * 1000)); A(dalloc(&e->s2t_lut, (size_t) 4000));
     A(dalloc(&e->obs, Hp * CHUB_OBS_DIM)); A(dalloc(&e->reward, Hp)); A(dalloc(&e->done, Hp));
     A(dalloc(&e->step_index, 1)); A(dalloc(&e->actions_stage, Hp * (size_t) cfg->action_stride));
     if (cfg->diagnostics) { A(dalloc(&e->diag, Hp * CHUB_D_COUNT)); A(dalloc(&e->st_power, Hp * 6)); }
@@ -295,6 +295,9 @@ extern "C" int chub_set_tables(chub_engine *e, const chub_tables *t) {
         }
     }
     CK(cudaMemcpy(e->lut, lut.data(), lut.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
+    chub_launch_s2t_lut(e->s2t_lut, nullptr);  // device-built so the step kernel and the table agree bit for bit
+    CK(cudaGetLastError());
+    CK(cudaDeviceSynchronize());
     e->have_tables = true;
     return CHUB_OK;
 }
@@ -375,7 +378,7 @@ static int fill_params(chub_engine *e, ChubParams &P) {
     P.step_offset = 0; P.step_index = e->step_index;
     P.pile = e->pile; P.arrive = e->arrive; P.hubA = e->hubA; P.store = e->store; P.keys = e->keys; P.cls = e->cls;
     P.stats = e->stats; P.last_stats = e->last_stats; P.err = e->err; P.qsoc = e->qsoc;
-    P.classes = e->d_classes; P.el_table = e->d_el; P.lut = e->lut;
+    P.classes = e->d_classes; P.el_table = e->d_el; P.lut = e->lut; P.s2t_lut = e->s2t_lut;
     P.pv = e->pv; P.wd = e->wd; P.price_tr = e->price_tr;
     P.actions = nullptr; P.obs = e->obs; P.reward = e->reward; P.done = e->done;
     P.diag = e->diag; P.st_power = e->st_power; P.reset_mask = nullptr;
@@ -594,10 +597,10 @@ extern "C" int chub_get_field(chub_engine *e, int32_t field, void *host_out) {
                         case CHUB_F_PILE_CAR: oi[o] = car; break;
                         case CHUB_F_PILE_CHARGE: oi[o] = (r.w & PW_CHARGE) ? 1 : 0; break;
                         case CHUB_F_PILE_URGENT: oi[o] = (r.w & PW_URGENT) ? 1 : 0; break;
-                        case CHUB_F_PILE_STAY: oi[o] = car ? (int) (r.w & 0xff) : 0; break;
-                        case CHUB_F_PILE_ALREADY: oi[o] = car ? (int) ((r.w >> 8) & 0xff) : 0; break;
+                        case CHUB_F_PILE_STAY: oi[o] = car ? (int) PW_STAY(r.w) : 0; break;
+                        case CHUB_F_PILE_ALREADY: oi[o] = car ? (int) PW_ALREADY(r.w) : 0; break;
                         case CHUB_F_PILE_SOC: of[o] = car ? fx : 0.f; break;
-                        case CHUB_F_PILE_TARGET: of[o] = car ? fy : 0.f; break;
+                        case CHUB_F_PILE_TARGET: of[o] = car ? (float) PW_TU(r.w) / 999.0f * 20.0f + 80.0f : 0.f; break;
                         case CHUB_F_PILE_POWER: of[o] = car ? fz : 0.f; break;
                         case CHUB_F_PILE_ARRIVE: of[o] = car ? arr : 0.f; break;
                         default: return fail(CHUB_ERR_ARG, "chub_get_field: unknown pile field");

@@ -23,12 +23,23 @@ struct StationOut {
     int incomplete;     // departures below target (the reference prints, CHS.hpp:916-921)
 };
 
-// One EV station, one hub.  RESET = false: evs_step(vector) (CHS.hpp:1188-1207 / 1499-1518);
-// RESET = true: evs_reset (CHS.hpp:1209-1231 / 1520-1542).  Piles are visited once, ascending.
-template <bool RESET>
-__device__ __forceinline__ StationOut station_pass(const ChubParams &P, int h, int slot0, int n, int type, int cp,
-                                                   int t, int line, unsigned long long act_bits, HubRng &rng,
-                                                   uint32_t &err) {
+__device__ __forceinline__ float target_of(uint32_t tu) {  // uniform_rand(80, 100), CHS.hpp:41-42, 867
+    return (float) tu / 999.0f * 20.0f + 80.0f;
+}
+
+// One EV station of one hub.  RESET = false: evs_step(vector) (CHS.hpp:1188-1207 / 1499-1518);
+// RESET = true: evs_reset (CHS.hpp:1209-1231 / 1520-1542).
+//
+// Work is split so that the lanes of a warp (32 different hubs) execute the expensive code together:
+//   scan   : ascending read of the packed words only -> bit masks (occupied, charging, departing)
+//   loop A : each lane walks ITS OWN charging piles (car_step + urgency)            -- convergent fp64
+//   loop B : each lane walks ITS OWN newly assigned piles in ascending order (add_car, serial RNG)
+//   pass C : ascending coalesced sweep: non-charging bookkeeping (remove_car) and the station sums in
+//            the reference's fp32 summation order (calculate_output)
+// "First k empty piles" (assign_car / find_empty, CHS.hpp:417-451) is bit arithmetic on the occupancy mask.
+template <bool RESET, int TYPE>
+__device__ __forceinline__ StationOut station_pass(const ChubParams &P, int h, int slot0, int n, int cp, int t,
+                                                   int line, uint32_t act_bits, HubRng &rng, uint32_t &err) {
     StationOut o;
     o.incomplete = 0;
     // ---- station-level draws of receive_car (CHS.hpp:1272-1306), before any per-car draw ----
@@ -38,8 +49,7 @@ __device__ __forceinline__ StationOut station_pass(const ChubParams &P, int h, i
         line = 0;
     } else {
         int N = (int) __ldg(&P.lut[t * 1000 + rng_u1000(rng)]);
-        float pin = (type == CHUB_FAST) ? 0.15f : 0.1f;
-        in_car = (int) roundf(pin * 0.2f * (float) N);
+        in_car = (int) roundf((TYPE == CHUB_FAST ? 0.15f : 0.1f) * 0.2f * (float) N);
     }
     int kept = 0;
     for (int w = 0; w < line; ++w) {  // reneging: keep if u > 0.1*logf(w+1)
@@ -52,77 +62,139 @@ __device__ __forceinline__ StationOut station_pass(const ChubParams &P, int h, i
         float a = rng_u01(rng);
         if (a <= kC.balk[min(line + k, 63)] && k <= n) true_in += 1;
     }
-    o.flow = (type == CHUB_SLOW) ? true_in : in_car;  // the slow/fast asymmetry, CHS.hpp:1306 vs 1617
+    o.flow = (TYPE == CHUB_SLOW) ? true_in : in_car;  // the slow/fast asymmetry, CHS.hpp:1306 vs 1617
     const int want = line + o.flow;
 
-    float mn = 0.0f, mx = 0.0f, now = 0.0f;
-    int number = 0, empties = 0;
     uint4 *row = P.pile + (size_t) slot0 * P.Hpad + h;
-    uint4 rec = make_uint4(0u, 0u, 0u, 0u);
-    if (!RESET && n > 0) rec = *row;
-    for (int i = 0; i < n; ++i) {
-        uint4 cur = rec;
-        if (!RESET && i + 1 < n) rec = row[(size_t) (i + 1) * P.Hpad];  // prefetch the next pile
-        uint32_t w = RESET ? 0u : cur.w;
-        float soc = __uint_as_float(cur.x), target = __uint_as_float(cur.y), power = __uint_as_float(cur.z);
-        bool changed = RESET;
-        if (w & PW_CAR) {
-            int stay = w & 0xff, already = (w >> 8) & 0xff, cn = (w >> 19) & 0x1f;
-            // judge_feasibility + assign_on_off_piece (CHS.hpp:1404-1413, 1364-1373)
-            bool charging = (w & PW_URGENT) || ((act_bits >> i) & 1ull);
-            if (charging) {  // car_step (CHS.hpp:900-905 / 1065-1070)
-                float tt = curve_s2t(type, cp, soc) + 1.0f;
-                curve_step(type, cp, tt, soc, power);
-                float needed = curve_s2t(type, cp, target) - curve_s2t(type, cp, soc);
-                cn = needed > 0.0f ? (int) ceilf(needed) : 0;
+    const size_t ld = (size_t) P.Hpad;
+    const float *tlut = P.s2t_lut + (cp * 2 + TYPE) * 1000;  // s2t(target) for the 1000 possible targets
+    const uint32_t nmask = n >= 32 ? 0xffffffffu : ((1u << n) - 1u);
+
+    // ---- scan ----
+    uint32_t car_mask = 0u, chg_mask = 0u, dep_mask = 0u;
+    if (!RESET) {
+        for (int i = 0; i < n; ++i) {
+            const uint32_t w = row[i * ld].w;
+            const uint32_t bit = 1u << i;
+            if (w & PW_CAR) {
+                car_mask |= bit;
+                // judge_feasibility + assign_on_off_piece (CHS.hpp:1404-1413, 1364-1373)
+                if ((w & PW_URGENT) || (act_bits & bit)) chg_mask |= bit;
+                if ((int) PW_STAY(w) - ((int) PW_ALREADY(w) + 1) <= 0) dep_mask |= bit;  // remove_car
             }
-            already += 1;  // remove_car (CHS.hpp:912-923 / 1077-1088)
+        }
+    }
+    const uint32_t occ_after = car_mask & ~dep_mask;
+    const int empties = n - __popc(occ_after);
+    const int assigned = min(want, empties);  // assign_car, wait == true (CHS.hpp:417-430); may be negative
+    o.line = min(want - assigned, 10);
+    uint32_t add_mask = 0u;
+    {
+        uint32_t freeb = ~occ_after & nmask;
+        for (int k = 0; k < assigned; ++k) {  // the first `assigned` empty piles, ascending
+            uint32_t b = freeb & (0u - freeb);
+            add_mask |= b;
+            freeb ^= b;
+        }
+    }
+
+    // ---- loop A: car_step for this hub's charging piles (CHS.hpp:900-905 / 1065-1070) ----
+    if (!RESET) {
+        uint32_t m = chg_mask;
+        while (m) {
+            const int i = __ffs(m) - 1;
+            m &= m - 1u;
+            uint4 r = row[i * ld];
+            const uint32_t w = r.w;
+            float soc, power;
+            curve_step(TYPE, cp, __uint_as_float(r.y) + 1.0f, soc, power);
+            const float tsoc = curve_s2t(TYPE, cp, soc);
+            const uint32_t tu = PW_TU(w);
+            const float needed = __ldg(&tlut[tu]) - tsoc;
+            const int cn = needed > 0.0f ? (int) ceilf(needed) : 0;
+            const int stay = PW_STAY(w), already = PW_ALREADY(w) + 1;
             if (stay - already <= 0) {
-                if (ceilf(soc) < floorf(target)) o.incomplete += 1;
-                w = 0u;
-                soc = target = power = 0.0f;
+                if (ceilf(soc) < floorf(target_of(tu))) o.incomplete += 1;
+                r = make_uint4(0u, 0u, 0u, 0u);
             } else {
-                w = (uint32_t) stay | ((uint32_t) already << 8) | PW_CAR | (charging ? PW_CHARGE : 0u) |
-                    ((uint32_t) cn << 19);
+                const bool urgent = cn > 0 && (stay - already) <= cn;
+                r = make_uint4(__float_as_uint(soc), __float_as_uint(tsoc), __float_as_uint(power),
+                               (uint32_t) stay | ((uint32_t) already << 6) | PW_CAR | PW_CHARGE |
+                                   (urgent ? PW_URGENT : 0u) | ((uint32_t) cn << 15) | (tu << 20));
             }
-            changed = true;
+            row[i * ld] = r;
         }
-        if (!(w & PW_CAR)) {
-            if (empties < want) {  // this is one of the first `assign_number` empty piles: add_car
-                float arrive = rng_mk_soc(rng);                               // E  CHS.hpp:865
-                target = (float) rng_u1000(rng) / 999.0f * 20.0f + 80.0f;     // U  CHS.hpp:867
-                soc = arrive;
-                float t_soc = curve_s2t(type, cp, soc);
-                float needed = curve_s2t(type, cp, target) - t_soc;
-                int must_needed = (int) ceilf(needed);                        // CHS.hpp:933-937
-                int stay = must_needed + rng_late_time(rng);                  // E  CHS.hpp:869
-                power = curve_t2p(type, cp, t_soc);                           // CHS.hpp:872-874
-                int cn = needed > 0.0f ? must_needed : 0;
-                if (stay > 255 || stay < 1 || cn > 31) { err |= CHUB_HUBERR_COUNTER; stay = min(max(stay, 1), 255); cn = min(cn, 31); }
-                w = (uint32_t) stay | PW_CAR | ((uint32_t) cn << 19);
-                P.arrive[(size_t) (slot0 + i) * P.Hpad + h] = arrive;
-                changed = true;
+    }
+    // ---- loop B: add_car for the newly assigned piles, ascending (CHS.hpp:864-877 / 1029-1042) ----
+    {
+        uint32_t m = add_mask;
+        while (m) {
+            const int i = __ffs(m) - 1;
+            m &= m - 1u;
+            const float arrive = rng_mk_soc(rng);                 // E
+            const uint32_t tu = (uint32_t) rng_u1000(rng);        // U  (target = u/999*20+80)
+            const float tsoc = curve_s2t(TYPE, cp, arrive);
+            const float needed = __ldg(&tlut[tu]) - tsoc;
+            const int must_needed = (int) ceilf(needed);          // calculate_min_charging_time
+            int stay = must_needed + rng_late_time(rng);          // E
+            const float power = curve_t2p(TYPE, cp, tsoc);
+            int cn = needed > 0.0f ? must_needed : 0;
+            if (stay > 63 || stay < 1 || cn > 31) {
+                err |= CHUB_HUBERR_COUNTER;
+                stay = min(max(stay, 1), 63);
+                cn = min(cn, 31);
             }
-            empties += 1;
+            const bool urgent = cn > 0 && stay <= cn;
+            row[i * ld] = make_uint4(__float_as_uint(arrive), __float_as_uint(tsoc), __float_as_uint(power),
+                                     (uint32_t) stay | PW_CAR | (urgent ? PW_URGENT : 0u) | ((uint32_t) cn << 15) |
+                                         (tu << 20));
+            P.arrive[(size_t) (slot0 + i) * ld + h] = arrive;
         }
-        if (w & PW_CAR) {  // calculate_needed + calculate_output for the NEXT interval (CHS.hpp:1233-1261)
-            int left = (int) (w & 0xff) - (int) ((w >> 8) & 0xff);
-            int cn = (w >> 19) & 0x1f;
-            bool urgent = cn > 0 && left <= cn;
-            w = urgent ? (w | PW_URGENT) : (w & ~PW_URGENT);
+    }
+    // ---- pass C: remaining bookkeeping + calculate_output in ascending fp32 order (CHS.hpp:1233-1261) ----
+    float mn = 0.0f, mx = 0.0f, now = 0.0f;
+    int number = 0;
+    const uint32_t done_mask = chg_mask | add_mask;
+    for (int i = 0; i < n; ++i) {
+        const uint32_t bit = 1u << i;
+        if (RESET && !(add_mask & bit)) {
+            row[i * ld] = make_uint4(0u, 0u, 0u, 0u);
+            continue;
+        }
+        if (!RESET && !((car_mask | add_mask) & bit)) continue;  // stays empty: nothing to read
+        uint4 r = row[i * ld];
+        uint32_t w = r.w;
+        if (!(done_mask & bit)) {  // occupied, not charging this step: remove_car only
+            const int stay = PW_STAY(w), already = PW_ALREADY(w) + 1;
+            if (dep_mask & bit) {
+                if (ceilf(__uint_as_float(r.x)) < floorf(target_of(PW_TU(w)))) o.incomplete += 1;
+                w = 0u;
+                r = make_uint4(0u, 0u, 0u, 0u);
+            } else {
+                const int cn = PW_CN(w);
+                const bool urgent = cn > 0 && (stay - already) <= cn;
+                w = (w & ~(PW_CHARGE | PW_URGENT | (0x3fu << 6))) | ((uint32_t) already << 6) | (urgent ? PW_URGENT : 0u);
+                r.w = w;
+            }
+            row[i * ld] = r;
+        }
+        if (w & PW_CAR) {
+            const float power = __uint_as_float(r.z);
             number += 1;
             mx += power;
-            if (urgent) mn += power;
+            if (w & PW_URGENT) mn += power;
             if (w & PW_CHARGE) now += power;
         }
-        if (changed) row[(size_t) i * P.Hpad] = make_uint4(__float_as_uint(soc), __float_as_uint(target),
-                                                           __float_as_uint(power), w);
     }
-    // assign_car, wait == true (CHS.hpp:417-430)
-    int assigned = min(want, empties);
-    o.line = min(want - assigned, 10);
     o.mn = mn; o.mx = mx; o.now = now; o.number = number;
     return o;
+}
+
+template <bool RESET>
+__device__ __forceinline__ StationOut station_any(const ChubParams &P, int h, int slot0, int n, int type, int cp, int t,
+                                                  int line, uint32_t act_bits, HubRng &rng, uint32_t &err) {
+    if (type == CHUB_SLOW) return station_pass<RESET, CHUB_SLOW>(P, h, slot0, n, cp, t, line, act_bits, rng, err);
+    return station_pass<RESET, CHUB_FAST>(P, h, slot0, n, cp, t, line, act_bits, rng, err);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -278,8 +350,8 @@ __device__ __forceinline__ void write_obs(const ChubParams &P, int h, const Chub
 // EvcsspManagerEnv_v6.reset (evcssp_manager.py:304-316): both stations, hydrogen store, FCEV queue
 __device__ __forceinline__ void hub_reset_body(const ChubParams &P, int h, const ChubClass &c, HubVars &v,
                                                StationOut &s0, StationOut &s1) {
-    s0 = station_pass<true>(P, h, 0, c.n[0], c.type[0], c.constant, 0, 0, 0ull, v.rng, v.err);
-    s1 = station_pass<true>(P, h, P.S0, c.n[1], c.type[1], c.constant, 0, 0, 0ull, v.rng, v.err);
+    s0 = station_any<true>(P, h, 0, c.n[0], c.type[0], c.constant, 0, 0, 0u, v.rng, v.err);
+    s1 = station_any<true>(P, h, P.S0, c.n[1], c.type[1], c.constant, 0, 0, 0u, v.rng, v.err);
     v.t = 0;
     v.line0 = s0.line; v.line1 = s1.line;
     v.flow0 = s0.flow; v.flow1 = s1.flow;
@@ -343,9 +415,9 @@ __global__ void __launch_bounds__(128) chub_step_kernel(const ChubParams P) {
     trace_at(P, h, k, pv_t, wd_t, pr_t);
 
     // ---- the two EV stations, station 0 first (Aggregator_Simple.py:141-142) ----
-    StationOut s0 = station_pass<false>(P, h, 0, n0, c.type[0], c.constant, v.t, v.line0, bits, v.rng, v.err);
-    StationOut s1 = station_pass<false>(P, h, P.S0, n1, c.type[1], c.constant, v.t, v.line1,
-                                        n0 >= 64 ? 0ull : (bits >> n0), v.rng, v.err);
+    StationOut s0 = station_any<false>(P, h, 0, n0, c.type[0], c.constant, v.t, v.line0, (uint32_t) bits, v.rng, v.err);
+    StationOut s1 = station_any<false>(P, h, P.S0, n1, c.type[1], c.constant, v.t, v.line1,
+                                       (uint32_t) (bits >> n0), v.rng, v.err);
     v.line0 = s0.line; v.line1 = s1.line;
     v.flow0 = s0.flow; v.flow1 = s1.flow;
 
@@ -518,6 +590,15 @@ __global__ void __launch_bounds__(128) chub_reset_kernel(const ChubParams P) {
     write_obs(P, h, c, 0, s0, s1, c.init_soc, pv, wd, pr);
     hub_store(P, h, v);
 }
+
+// s2t(target) for the 1000 possible target SOCs x {fast, slow} x {curve, constant power}
+__global__ void chub_s2t_lut_kernel(float *out) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= 4000) return;
+    const int cp = idx / 2000, type = (idx / 1000) % 2, u = idx % 1000;
+    out[idx] = curve_s2t(type, cp, target_of((uint32_t) u));
+}
+void chub_launch_s2t_lut(float *out, cudaStream_t s) { chub_s2t_lut_kernel<<<(4000 + 127) / 128, 128, 0, s>>>(out); }
 
 __global__ void chub_tick_kernel(long long *step_index, int n) { *step_index += n; }
 

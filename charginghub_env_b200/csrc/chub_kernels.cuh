@@ -3,20 +3,24 @@
 #include "chub_device.cuh"
 
 // HBM layout (SoA, hub index fastest so a warp of 32 hubs touches one contiguous row):
-//   pile[(slot) * Hpad + h]   uint4 {soc f32, target f32, power f32, packed}     slot = station0 piles, then station1 piles
+//   pile[(slot) * Hpad + h]   uint4 {soc f32, s2t(soc) f32, power f32, packed}  slot = station0 piles, then station1 piles
 //   arrive[(slot) * Hpad + h] float  arrival SOC ("init_soc" column; written once per car, never read by the step)
 //   hubA[h]                   uint4 {minstd state, U counter, packed1, packed2}
 //   store[h]                  double hydrogen store mass in grams
 //   keys[h]                   uint2  U-stream keys (read only)
 //   stats[h], last_stats[h]   float4 {episode return, income, grid energy, incomplete departures}
 //   qsoc[(j) * Hpad + h]      float  FCEV backlog arrival SOCs (cold; touched only when a backlog exists)
-// packed pile word : bits 0-7 stay_time, 8-15 already_stay_time, 16 car, 17 charge, 18 urgent,
-//                    19-23 ceil(needed_time) cache (0 = needed_time <= 0)
+// packed pile word : bits 0-5 stay_time, 6-11 already_stay_time, 12 car, 13 charge, 14 urgent,
+//                    15-19 ceil(needed_time) cache (0 = needed_time <= 0), 20-29 target draw u (target = u/999*20+80)
 // packed1          : bits 0-7 t (time hole), 8-15 line[0], 16-23 line[1], 24-31 FCEV backlog length
 // packed2          : bits 0-7 flow_in[0]+128, 8-15 flow_in[1]+128, 16-23 FCEV line, 24-31 FCEV arrivals
-#define PW_CAR (1u << 16)
-#define PW_CHARGE (1u << 17)
-#define PW_URGENT (1u << 18)
+#define PW_CAR (1u << 12)
+#define PW_CHARGE (1u << 13)
+#define PW_URGENT (1u << 14)
+#define PW_STAY(w) ((w) & 0x3fu)
+#define PW_ALREADY(w) (((w) >> 6) & 0x3fu)
+#define PW_CN(w) (((w) >> 15) & 0x1fu)
+#define PW_TU(w) (((w) >> 20) & 0x3ffu)
 
 struct ChubParams {
     int H, Hpad, S0, S1;
@@ -36,6 +40,7 @@ struct ChubParams {
     const ChubClass *classes;
     const double *el_table;           // [n_classes][102]
     const uint16_t *lut;              // [96][1000] traffic count for u = r/999.f (CHS.hpp:731-743)
+    const float *s2t_lut;             // [2 constant][2 type][1000] soc_to_time(target(u))
     const double *pv, *wd, *price_tr;
     const float *actions;
     float *obs;
@@ -48,5 +53,6 @@ struct ChubParams {
 
 void chub_launch_step(const ChubParams &p, cudaStream_t s);
 void chub_launch_reset(const ChubParams &p, cudaStream_t s);
+void chub_launch_s2t_lut(float *out, cudaStream_t s);
 void chub_launch_tick(long long *step_index, int n, cudaStream_t s);
 cudaError_t chub_upload_const(const ChubConst &c);
