@@ -14,6 +14,7 @@
 
 #include "../../include/chub.h"
 #include "../../include/chub_rng.h"
+#include "chub_fastmath.h"
 
 // ---------------------------------------------------------------------------------------------
 // constant-memory tables, filled by the host (chub_engine.cu) with this machine's glibc
@@ -54,6 +55,7 @@ struct ChubClass {
 
 #ifdef CHUB_KERNEL_TU  // device code below is compiled only into chub_kernels.cu
 __constant__ ChubConst kC;
+__device__ ChubLogEntry kLogTab[CHUB_LOG_N];  // reduction table of chub_log (global memory: lanes index it divergently)
 
 // ---------------------------------------------------------------------------------------------
 // per-hub random streams (include/chub_rng.h)
@@ -78,7 +80,11 @@ __device__ __forceinline__ double rng_canon_d(HubRng &r) {
     double a = (double) (rng_e(r) - 1u);
     double b = (double) (rng_e(r) - 1u);
     double sum = a + b * 2147483646.0;
-    double ret = sum / 4611686009837453316.0;  // (2^31-2)^2 rounded to double = 2^62 - 2^33
+    // sum / D with D = (2^31-2)^2 rounded to double = 2^62 - 2^33: reciprocal estimate plus one fma residual
+    // correction (Markstein) gives the correctly rounded quotient without the generic division routine
+    const double D = 4611686009837453312.0, rD = 1.0 / 4611686009837453312.0;
+    double q0 = sum * rD;
+    double ret = fma(fma(-q0, D, sum), rD, q0);
     if (ret >= 1.0) ret = 0.99999999999999988898;
     return ret;
 }
@@ -99,7 +105,7 @@ __device__ __forceinline__ double rng_normal_d(HubRng &r, double mean, double sd
         y = 2.0 * rng_canon_d(r) - 1.0;
         r2 = x * x + y * y;
     } while (r2 > 1.0 || r2 == 0.0);
-    double mult = sqrt(-2.0 * log(r2) / r2);
+    double mult = sqrt(chub_div(-2.0 * chub_log(r2, kLogTab), r2));
     return (y * mult) * sd + mean;
 }
 // float flavour (CHS.hpp:819-820, 833-834).  logf is taken as the correctly rounded fp32 log
@@ -111,7 +117,7 @@ __device__ __forceinline__ float rng_normal_f(HubRng &r, float mean, float sd) {
         y = 2.0f * rng_canon_f(r) - 1.0f;
         r2 = x * x + y * y;
     } while (r2 > 1.0f || r2 == 0.0f);
-    float lg = (float) log((double) r2);
+    float lg = (float) chub_log((double) r2, kLogTab);
     float mult = sqrtf(-2.0f * lg / r2);
     float ret = y * mult;
     return ret * sd + mean;
@@ -142,7 +148,8 @@ __device__ __forceinline__ float slow_s2t(float s) {
     if (d <= 100.0) {
         double p = fma(fma(fma(fma(kC.slow_stt2_a, d, -0.001529), d, 0.1871), d, -10.15), d, 213.1);
         float q = (float) (p + 0.1787983924863248);
-        return (float) ((double) q + (0.2012016075138625 * (d - 73.89239629561729)) / 26.10760370438271);
+        return (float) ((double) q + chub_div_const(0.2012016075138625 * (d - 73.89239629561729), 26.10760370438271,
+                                                    1.0 / 26.10760370438271));
     }
     return 14.68f;
 }
@@ -156,15 +163,15 @@ __device__ __forceinline__ void slow_step(float t, float &soc, float &power) {
     } else if (td <= 2.33 * 4) {
         ch = (float) (y * fma(fma(fma(fma(-0.0004112, y, 0.0023025), y, 0.03562 / 3), y, 0.011895), y, 6.007));
     } else if (td <= 3.67 * 4) {
-        ch = (float) (-4.041 * y + 19.140115 * log(fabs(y - 0.485)) + 11.943306312699628);
+        ch = (float) (-4.041 * y + 19.140115 * chub_log(fabs(y - 0.485), kLogTab) + 11.943306312699628);
     } else {
         ch = kC.slow_c2_end;
     }
-    soc = (float) ((double) (100.0f * ch) / 19.285746346634653);
+    soc = (float) chub_div_const((double) (100.0f * ch), 19.285746346634653, 1.0 / 19.285746346634653);
     if (td < 2.33 * 4) {
         power = (float) fma(fma(fma(fma(-0.002056, y, 0.00921), y, 0.03562), y, 0.02379), y, 6.007);
     } else if (td < 3.67 * 4) {
-        power = (float) ((-4.041 * y + 21.1) / (y - 0.485));
+        power = (float) chub_div(-4.041 * y + 21.1, y - 0.485);
     } else {
         power = 0.0f;
     }
@@ -172,7 +179,7 @@ __device__ __forceinline__ void slow_step(float t, float &soc, float &power) {
 __device__ __forceinline__ float slow_t2p(float t) {
     double y = (double) (t * 0.25f), td = (double) t;
     if (td < 2.33 * 4) return (float) fma(fma(fma(fma(-0.002056, y, 0.00921), y, 0.03562), y, 0.02379), y, 6.007);
-    if (td < 3.67 * 4) return (float) ((-4.041 * y + 21.1) / (y - 0.485));
+    if (td < 3.67 * 4) return (float) chub_div(-4.041 * y + 21.1, y - 0.485);
     return 0.0f;
 }
 
@@ -186,7 +193,7 @@ __device__ __forceinline__ float fast_s2t(float s) {
     double p4z = (double) (-62.97f * zf), q3z = (double) (-50.12f * zf);
     double num = fma(fma((double) -18.18f, z, (double) 9.559f), z, (double) 48.99f) * z2 + p4z + (double) 29.09f;
     double den = fma(fma(z, 1.0, (double) -23.9f), z, (double) 56.48f) * z2 + q3z + (double) 18.96f;
-    return (float) (num / den);
+    return (float) chub_div(num, den);
 }
 __device__ __forceinline__ float fast_aa2(double x) {
     double p = x * fma(fma(fma(fma(0.0002253 / 5, x, -(0.03572 / 4)), x, 2.016 / 3), x, -(48.76 / 2)), x, 457.7);
@@ -196,7 +203,7 @@ __device__ __forceinline__ void fast_step(float t, float &soc, float &power) {
     float xf = t * 15.0f;
     double x = (double) xf, td = (double) t;
     double ex = 0.0;
-    if (td > 0.0 && td <= 28.7 / 15) ex = exp(0.053 * x);
+    if (td > 0.0 && td <= 28.7 / 15) ex = chub_exp(0.053 * x);
     if (td <= 0.0) {
         soc = 0.0f;
     } else if (td <= 28.7 / 15) {
@@ -208,7 +215,7 @@ __device__ __forceinline__ void fast_step(float t, float &soc, float &power) {
         soc = 100.0f;
     }
     if (td >= 0.0 && td < 28.7 / 15) {
-        if (td <= 0.0) ex = exp(0.053 * x);
+        if (td <= 0.0) ex = chub_exp(0.053 * x);
         power = (float) (0.7194 * ex + 47.78);
     } else if (td >= 0.0 && td < 51.2 / 15) {
         power = (float) fma(fma(fma(fma(0.0002253, x, -0.03572), x, 2.016), x, -48.76), x, 457.7);
@@ -218,7 +225,7 @@ __device__ __forceinline__ void fast_step(float t, float &soc, float &power) {
 }
 __device__ __forceinline__ float fast_t2p(float t) {
     double x = (double) (t * 15.0f), td = (double) t;
-    if (td >= 0.0 && td < 28.7 / 15) return (float) (0.7194 * exp(0.053 * x) + 47.78);
+    if (td >= 0.0 && td < 28.7 / 15) return (float) (0.7194 * chub_exp(0.053 * x) + 47.78);
     if (td >= 0.0 && td < 51.2 / 15) return (float) fma(fma(fma(fma(0.0002253, x, -0.03572), x, 2.016), x, -48.76), x, 457.7);
     return 0.0f;
 }

@@ -13,7 +13,13 @@
 #define CHUB_KERNEL_TU
 #include "chub_kernels.cuh"
 
-cudaError_t chub_upload_const(const ChubConst &c) { return cudaMemcpyToSymbol(kC, &c, sizeof(ChubConst)); }
+cudaError_t chub_upload_const(const ChubConst &c) {
+    ChubLogEntry tab[CHUB_LOG_N];
+    chub_build_log_table(tab);
+    cudaError_t r = cudaMemcpyToSymbol(kLogTab, tab, sizeof tab);
+    if (r != cudaSuccess) return r;
+    return cudaMemcpyToSymbol(kC, &c, sizeof(ChubConst));
+}
 
 struct StationOut {
     float mn, mx, now;  // min_power, max_power, charge_power (CHS.hpp:1257-1259)

@@ -34,7 +34,10 @@ CHUB_HD uint32_t chub_rand31(uint32_t key0, uint32_t key1, uint32_t counter) {
 
 /* minstd_rand0 step; state stays in [1, 2^31-2]. */
 CHUB_HD uint32_t chub_minstd_next(uint32_t x) {
-    return (uint32_t) (((uint64_t) x * 16807ull) % 2147483647ull);
+    /* 2^31 == 1 (mod 2^31-1): fold the high bits instead of dividing; identical to the % form */
+    uint64_t p = (uint64_t) x * 16807ull;
+    uint32_t r = (uint32_t) (p & 0x7fffffffull) + (uint32_t) (p >> 31);
+    return r >= 2147483647u ? r - 2147483647u : r;
 }
 
 CHUB_HD uint64_t chub_splitmix64(uint64_t z) {

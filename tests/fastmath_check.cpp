@@ -1,0 +1,55 @@
+// Host check of csrc/chub_fastmath.h against libm over the argument ranges the step kernel uses.
+#include <cstdio>
+#include <cstdlib>
+#include <cmath>
+#include <random>
+#include "../charginghub_env_b200/csrc/chub_fastmath.h"
+
+static double ulp_err(double got, double want) {
+    if (got == want) return 0.0;
+    double u = std::nextafter(std::fabs(want), INFINITY) - std::fabs(want);
+    return std::fabs(got - want) / u;
+}
+
+int main(int argc, char **argv) {
+    long n = argc > 1 ? atol(argv[1]) : 2000000;
+    ChubLogEntry tab[CHUB_LOG_N];
+    chub_build_log_table(tab);
+    std::mt19937_64 g(12345);
+    std::uniform_real_distribution<double> U(0.0, 1.0);
+    double max_log_a = 0, max_log_b = 0, max_exp = 0;
+    long f_log = 0, f_exp = 0, f_norm = 0, bad_div = 0;
+    for (long i = 0; i < n; ++i) {
+        // slow charger: log|y - 0.485| with y in (2.33, 3.67]  (CHS.hpp:564-566)
+        float yf = (float) (2.33 + (3.67 - 2.33) * U(g));
+        double a = std::fabs((double) yf - 0.485);
+        double l1 = chub_log(a, tab), l0 = std::log(a);
+        max_log_a = std::fmax(max_log_a, ulp_err(l1, l0));
+        float c1 = (float) (-4.041 * yf + 19.140115 * l1 + 11.943306312699628);
+        float c0 = (float) (-4.041 * yf + 19.140115 * l0 + 11.943306312699628);
+        f_log += c1 != c0;
+        // polar normal: log(r2), r2 in (0, 1], both tiny and near-1 values
+        double r2 = (i & 1) ? U(g) : std::pow(U(g), 12.0);
+        if (r2 <= 0) r2 = 1e-300;
+        double m1 = chub_log(r2, tab), m0 = std::log(r2);
+        max_log_b = std::fmax(max_log_b, std::fabs(m1 - m0) / std::fmax(std::fabs(m0), 1e-3) / 2.220446049250313e-16);
+        float y = (float) U(g);
+        float v1 = (float) (y * std::sqrt(-2 * m1 / r2) * 3.0 + 7.0), v0 = (float) (y * std::sqrt(-2 * m0 / r2) * 3.0 + 7.0);
+        f_norm += v1 != v0;
+        // fast charger: exp(0.053 x), x in [0, 28.7]  (CHS.hpp:684-695)
+        float xf = (float) (28.7 * U(g));
+        double e1 = chub_exp(0.053 * xf), e0 = std::exp(0.053 * xf);
+        max_exp = std::fmax(max_exp, ulp_err(e1, e0));
+        f_exp += (float) (0.7194 * e1 + 47.78) != (float) (0.7194 * e0 + 47.78);
+        // division by constants
+        double num = 100.0 * U(g);
+        bad_div += chub_div_const(num, 19.285746346634653, 1.0 / 19.285746346634653) != num / 19.285746346634653;
+        bad_div += chub_div_const(num, 26.10760370438271, 1.0 / 26.10760370438271) != num / 26.10760370438271;
+        double den = 0.5 + 40 * U(g);
+        bad_div += chub_div(num, den) != num / den;
+    }
+    printf("{\"n\": %ld, \"log_curve_max_ulp\": %.3f, \"log_normal_max_relerr_eps\": %.3f, \"exp_max_ulp\": %.3f, "
+           "\"float_mismatch_log\": %ld, \"float_mismatch_normal\": %ld, \"float_mismatch_exp\": %ld, \"div_mismatch\": %ld}\n",
+           n, max_log_a, max_log_b, max_exp, f_log, f_norm, f_exp, bad_div);
+    return 0;
+}
