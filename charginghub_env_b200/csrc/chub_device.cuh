@@ -70,15 +70,16 @@ __device__ __forceinline__ float rng_u01(HubRng &r) {  // uniform_rand(0,1): tr*
     float tr = (float) rng_u1000(r) / 999.0f;
     return tr * 1.0f + 0.0f;
 }
-__device__ __forceinline__ uint32_t rng_e(HubRng &r) {
-    r.lcg = chub_minstd_next(r.lcg);
-    return r.lcg;
-}
+// The minstd-driven normals are deliberately NOT inlined: they are called from several places
+// (both station types, reset, FCEV arrivals) and one shared copy keeps the step kernel inside the
+// instruction cache.  State goes in and out by value so nothing is forced into local memory.
 
 // libstdc++ generate_canonical<double,53> over minstd_rand0: two draws (bits/random.tcc:3349-3381)
-__device__ __forceinline__ double rng_canon_d(HubRng &r) {
-    double a = (double) (rng_e(r) - 1u);
-    double b = (double) (rng_e(r) - 1u);
+__device__ __forceinline__ double canon_d(uint32_t &lcg) {
+    lcg = chub_minstd_next(lcg);
+    double a = (double) (lcg - 1u);
+    lcg = chub_minstd_next(lcg);
+    double b = (double) (lcg - 1u);
     double sum = a + b * 2147483646.0;
     // sum / D with D = (2^31-2)^2 rounded to double = 2^62 - 2^33: reciprocal estimate plus one fma residual
     // correction (Markstein) gives the correctly rounded quotient without the generic division routine
@@ -89,51 +90,59 @@ __device__ __forceinline__ double rng_canon_d(HubRng &r) {
     return ret;
 }
 // generate_canonical<float,24>: one draw, divisor float(2147483646) = 2^31
-__device__ __forceinline__ float rng_canon_f(HubRng &r) {
-    float a = (float) (rng_e(r) - 1u);
-    float ret = a * 4.656612873077392578125e-10f;  // exact: division by 2^31
+__device__ __forceinline__ float canon_f(uint32_t &lcg) {
+    lcg = chub_minstd_next(lcg);
+    float ret = (float) (lcg - 1u) * 4.656612873077392578125e-10f;  // exact: division by 2^31
     if (ret >= 1.0f) ret = 0.99999994f;
     return ret;
 }
 
-// std::normal_distribution<double>(mean, sd)(e) on a FRESH distribution object (CHS.hpp:805-806):
-// Marsaglia polar, second variate discarded (bits/random.tcc:1811-1844).
-__device__ __forceinline__ double rng_normal_d(HubRng &r, double mean, double sd) {
+// mk_soc (CHS.hpp:804-814): std::normal_distribution<double>(7, 3)(e) on a FRESH distribution object --
+// Marsaglia polar, second variate discarded (bits/random.tcc:1811-1844) -- clamped and mapped to an SOC.
+// Returns {soc bits, new minstd state}.
+__device__ __noinline__ uint2 draw_mk_soc(uint32_t lcg) {
     double x, y, r2;
     do {
-        x = 2.0 * rng_canon_d(r) - 1.0;
-        y = 2.0 * rng_canon_d(r) - 1.0;
+        x = 2.0 * canon_d(lcg) - 1.0;
+        y = 2.0 * canon_d(lcg) - 1.0;
         r2 = x * x + y * y;
     } while (r2 > 1.0 || r2 == 0.0);
     double mult = sqrt(chub_div(-2.0 * chub_log(r2, kLogTab), r2));
-    return (y * mult) * sd + mean;
+    float de = (float) ((y * mult) * 3.0 + 7.0);
+    de = fminf(fmaxf(de, 1.0f), 10.0f);
+    return make_uint2(__float_as_uint((float) (75.0 - 5.0 * (double) de)), lcg);
 }
-// float flavour (CHS.hpp:819-820, 833-834).  logf is taken as the correctly rounded fp32 log
-// (fp64 log narrowed), which is what glibc's logf returns except on rare hard cases.
-__device__ __forceinline__ float rng_normal_f(HubRng &r, float mean, float sd) {
+// float normal with unit-free (mean, sd) (CHS.hpp:819-820, 833-834).  logf is taken as the correctly
+// rounded fp32 log (fp64 log narrowed), which is what glibc's logf returns except on rare hard cases.
+// Returns {value bits, new minstd state}.
+__device__ __noinline__ uint2 draw_normal_f(uint32_t lcg, float mean, float sd) {
     float x, y, r2;
     do {
-        x = 2.0f * rng_canon_f(r) - 1.0f;
-        y = 2.0f * rng_canon_f(r) - 1.0f;
+        x = 2.0f * canon_f(lcg) - 1.0f;
+        y = 2.0f * canon_f(lcg) - 1.0f;
         r2 = x * x + y * y;
     } while (r2 > 1.0f || r2 == 0.0f);
     float lg = (float) chub_log((double) r2, kLogTab);
     float mult = sqrtf(-2.0f * lg / r2);
     float ret = y * mult;
-    return ret * sd + mean;
+    return make_uint2(__float_as_uint(ret * sd + mean), lcg);
 }
 
-__device__ __forceinline__ float rng_mk_soc(HubRng &r) {  // CHS.hpp:804-814
-    float de = (float) rng_normal_d(r, 7.0, 3.0);
-    de = fminf(fmaxf(de, 1.0f), 10.0f);
-    return (float) (75.0 - 5.0 * (double) de);
+__device__ __forceinline__ float rng_mk_soc(HubRng &r) {
+    uint2 v = draw_mk_soc(r.lcg);
+    r.lcg = v.y;
+    return __uint_as_float(v.x);
 }
 __device__ __forceinline__ int rng_late_time(HubRng &r) {  // CHS.hpp:816-830 ("slow" for both pile types)
-    int d = (int) roundf(rng_normal_f(r, 2.0f, 2.0f));
+    uint2 v = draw_normal_f(r.lcg, 2.0f, 2.0f);
+    r.lcg = v.y;
+    int d = (int) roundf(__uint_as_float(v.x));
     return d > 0 ? d : 0;
 }
 __device__ __forceinline__ int rng_init_cars(HubRng &r, int mu) {  // CHS.hpp:832-842, theta 3
-    int t = (int) roundf(rng_normal_f(r, (float) mu, 1.0f));
+    uint2 v = draw_normal_f(r.lcg, (float) mu, 1.0f);
+    r.lcg = v.y;
+    int t = (int) roundf(__uint_as_float(v.x));
     return min(max(t, mu - 3), mu + 3);
 }
 
@@ -248,26 +257,34 @@ __device__ __forceinline__ void const_step(float t, double tmax, float pconst, f
 #define CHUB_SLOW_PCONST ((float) 5.254973139368931)
 #define CHUB_FAST_PCONST ((float) 36.44764034125146)
 
-// dispatch on (station type, constant_charging); both are uniform across a homogeneous batch
-__device__ __forceinline__ float curve_s2t(int type, int cp, float s) {
-    if (cp) return const_s2t(s, type == CHUB_SLOW ? CHUB_SLOW_TMAX : CHUB_FAST_TMAX);
-    return type == CHUB_SLOW ? slow_s2t(s) : fast_s2t(s);
+// dispatch on (station type, constant_charging), both compile-time in the step kernel
+template <int TYPE, int CP>
+__device__ __forceinline__ float curve_s2t(float s) {
+    if (CP) return const_s2t(s, TYPE == CHUB_SLOW ? CHUB_SLOW_TMAX : CHUB_FAST_TMAX);
+    return TYPE == CHUB_SLOW ? slow_s2t(s) : fast_s2t(s);
 }
-__device__ __forceinline__ void curve_step(int type, int cp, float t, float &soc, float &power) {
-    if (cp) {
-        const_step(t, type == CHUB_SLOW ? CHUB_SLOW_TMAX : CHUB_FAST_TMAX,
-                   type == CHUB_SLOW ? CHUB_SLOW_PCONST : CHUB_FAST_PCONST, soc, power);
-    } else if (type == CHUB_SLOW) {
+template <int TYPE, int CP>
+__device__ __forceinline__ void curve_step(float t, float &soc, float &power) {
+    if (CP) {
+        const_step(t, TYPE == CHUB_SLOW ? CHUB_SLOW_TMAX : CHUB_FAST_TMAX,
+                   TYPE == CHUB_SLOW ? CHUB_SLOW_PCONST : CHUB_FAST_PCONST, soc, power);
+    } else if (TYPE == CHUB_SLOW) {
         slow_step(t, soc, power);
     } else {
         fast_step(t, soc, power);
     }
 }
-__device__ __forceinline__ float curve_t2p(int type, int cp, float t) {
-    if (cp) {
-        double tmax = type == CHUB_SLOW ? CHUB_SLOW_TMAX : CHUB_FAST_TMAX;
-        return (tmax >= (double) t && t >= 0.0f) ? (type == CHUB_SLOW ? CHUB_SLOW_PCONST : CHUB_FAST_PCONST) : 0.0f;
+template <int TYPE, int CP>
+__device__ __forceinline__ float curve_t2p(float t) {
+    if (CP) {
+        const double tmax = TYPE == CHUB_SLOW ? CHUB_SLOW_TMAX : CHUB_FAST_TMAX;
+        return (tmax >= (double) t && t >= 0.0f) ? (TYPE == CHUB_SLOW ? CHUB_SLOW_PCONST : CHUB_FAST_PCONST) : 0.0f;
     }
-    return type == CHUB_SLOW ? slow_t2p(t) : fast_t2p(t);
+    return TYPE == CHUB_SLOW ? slow_t2p(t) : fast_t2p(t);
+}
+// run-time flavour for the table-building kernel
+__device__ __forceinline__ float curve_s2t_rt(int type, int cp, float s) {
+    if (type == CHUB_SLOW) return cp ? curve_s2t<CHUB_SLOW, 1>(s) : curve_s2t<CHUB_SLOW, 0>(s);
+    return cp ? curve_s2t<CHUB_FAST, 1>(s) : curve_s2t<CHUB_FAST, 0>(s);
 }
 #endif  // CHUB_KERNEL_TU

@@ -376,6 +376,11 @@ static int fill_params(chub_engine *e, ChubParams &P) {
     P.auto_reset = e->cfg.auto_reset; P.diagnostics = e->cfg.diagnostics;
     P.trace_len = e->trace_len; P.trace_per_hub = e->trace_per_hub;
     P.step_offset = 0; P.step_index = e->step_index;
+    {   // experiment knobs (defaults are the measured best)
+        const char *b = getenv("CHUB_BLOCK"), *y = getenv("CHUB_PHASE_SYNC");
+        P.block = b ? atoi(b) : 51202;
+        P.phase_sync = y ? atoi(y) : 0;
+    }
     P.pile = e->pile; P.arrive = e->arrive; P.hubA = e->hubA; P.store = e->store; P.keys = e->keys; P.cls = e->cls;
     P.stats = e->stats; P.last_stats = e->last_stats; P.err = e->err; P.qsoc = e->qsoc;
     P.classes = e->d_classes; P.el_table = e->d_el; P.lut = e->lut; P.s2t_lut = e->s2t_lut;

@@ -43,9 +43,9 @@ __device__ __forceinline__ float target_of(uint32_t tu) {  // uniform_rand(80, 1
 //   pass C : ascending coalesced sweep: non-charging bookkeeping (remove_car) and the station sums in
 //            the reference's fp32 summation order (calculate_output)
 // "First k empty piles" (assign_car / find_empty, CHS.hpp:417-451) is bit arithmetic on the occupancy mask.
-template <bool RESET, int TYPE>
-__device__ __forceinline__ StationOut station_pass(const ChubParams &P, int h, int slot0, int n, int cp, int t,
-                                                   int line, uint32_t act_bits, HubRng &rng, uint32_t &err) {
+template <bool RESET, int TYPE, int CP>
+__device__ __forceinline__ StationOut station_pass(const ChubParams &P, int h, int slot0, int n, int t, int line,
+                                                   uint32_t act_bits, HubRng &rng, uint32_t &err) {
     StationOut o;
     o.incomplete = 0;
     // ---- station-level draws of receive_car (CHS.hpp:1272-1306), before any per-car draw ----
@@ -73,12 +73,13 @@ __device__ __forceinline__ StationOut station_pass(const ChubParams &P, int h, i
 
     uint4 *row = P.pile + (size_t) slot0 * P.Hpad + h;
     const size_t ld = (size_t) P.Hpad;
-    const float *tlut = P.s2t_lut + (cp * 2 + TYPE) * 1000;  // s2t(target) for the 1000 possible targets
+    const float *tlut = P.s2t_lut + (CP * 2 + TYPE) * 1000;  // s2t(target) for the 1000 possible targets
     const uint32_t nmask = n >= 32 ? 0xffffffffu : ((1u << n) - 1u);
 
     // ---- scan ----
     uint32_t car_mask = 0u, chg_mask = 0u, dep_mask = 0u;
     if (!RESET) {
+#pragma unroll 4
         for (int i = 0; i < n; ++i) {
             const uint32_t w = row[i * ld].w;
             const uint32_t bit = 1u << i;
@@ -107,14 +108,17 @@ __device__ __forceinline__ StationOut station_pass(const ChubParams &P, int h, i
     // ---- loop A: car_step for this hub's charging piles (CHS.hpp:900-905 / 1065-1070) ----
     if (!RESET) {
         uint32_t m = chg_mask;
+        uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
+        if (m) nxt = row[(__ffs(m) - 1) * ld];
         while (m) {
             const int i = __ffs(m) - 1;
             m &= m - 1u;
-            uint4 r = row[i * ld];
+            uint4 r = nxt;
+            if (m) nxt = row[(__ffs(m) - 1) * ld];  // prefetch this lane's next charging pile
             const uint32_t w = r.w;
             float soc, power;
-            curve_step(TYPE, cp, __uint_as_float(r.y) + 1.0f, soc, power);
-            const float tsoc = curve_s2t(TYPE, cp, soc);
+            curve_step<TYPE, CP>(__uint_as_float(r.y) + 1.0f, soc, power);
+            const float tsoc = curve_s2t<TYPE, CP>(soc);
             const uint32_t tu = PW_TU(w);
             const float needed = __ldg(&tlut[tu]) - tsoc;
             const int cn = needed > 0.0f ? (int) ceilf(needed) : 0;
@@ -139,11 +143,11 @@ __device__ __forceinline__ StationOut station_pass(const ChubParams &P, int h, i
             m &= m - 1u;
             const float arrive = rng_mk_soc(rng);                 // E
             const uint32_t tu = (uint32_t) rng_u1000(rng);        // U  (target = u/999*20+80)
-            const float tsoc = curve_s2t(TYPE, cp, arrive);
+            const float tsoc = curve_s2t<TYPE, CP>(arrive);
             const float needed = __ldg(&tlut[tu]) - tsoc;
             const int must_needed = (int) ceilf(needed);          // calculate_min_charging_time
             int stay = must_needed + rng_late_time(rng);          // E
-            const float power = curve_t2p(TYPE, cp, tsoc);
+            const float power = curve_t2p<TYPE, CP>(tsoc);
             int cn = needed > 0.0f ? must_needed : 0;
             if (stay > 63 || stay < 1 || cn > 31) {
                 err |= CHUB_HUBERR_COUNTER;
@@ -199,8 +203,12 @@ __device__ __forceinline__ StationOut station_pass(const ChubParams &P, int h, i
 template <bool RESET>
 __device__ __forceinline__ StationOut station_any(const ChubParams &P, int h, int slot0, int n, int type, int cp, int t,
                                                   int line, uint32_t act_bits, HubRng &rng, uint32_t &err) {
-    if (type == CHUB_SLOW) return station_pass<RESET, CHUB_SLOW>(P, h, slot0, n, cp, t, line, act_bits, rng, err);
-    return station_pass<RESET, CHUB_FAST>(P, h, slot0, n, cp, t, line, act_bits, rng, err);
+    if (cp) {  // constant-power charging (constant_charging=True): cold instantiations
+        if (type == CHUB_SLOW) return station_pass<RESET, CHUB_SLOW, 1>(P, h, slot0, n, t, line, act_bits, rng, err);
+        return station_pass<RESET, CHUB_FAST, 1>(P, h, slot0, n, t, line, act_bits, rng, err);
+    }
+    if (type == CHUB_SLOW) return station_pass<RESET, CHUB_SLOW, 0>(P, h, slot0, n, t, line, act_bits, rng, err);
+    return station_pass<RESET, CHUB_FAST, 0>(P, h, slot0, n, t, line, act_bits, rng, err);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -353,16 +361,31 @@ __device__ __forceinline__ void write_obs(const ChubParams &P, int h, const Chub
     for (int j = 0; j < CHUB_OBS_DIM; ++j) dst[j] = o[j];
 }
 
-// EvcsspManagerEnv_v6.reset (evcssp_manager.py:304-316): both stations, hydrogen store, FCEV queue
-__device__ __forceinline__ void hub_reset_body(const ChubParams &P, int h, const ChubClass &c, HubVars &v,
-                                               StationOut &s0, StationOut &s1) {
-    s0 = station_any<true>(P, h, 0, c.n[0], c.type[0], c.constant, 0, 0, 0u, v.rng, v.err);
-    s1 = station_any<true>(P, h, P.S0, c.n[1], c.type[1], c.constant, 0, 0, 0u, v.rng, v.err);
+// EvcsspManagerEnv_v6.reset (evcssp_manager.py:304-316) of one hub, from and to HBM: both stations
+// (evs_reset), hydrogen store, FCEV queue, episode statistics, first observation of the new episode.
+// Out of line on purpose: the step kernel calls it once per hub per 96 steps (fused auto-reset).
+__device__ __noinline__ void hub_reset_full(const ChubParams &P, int h, long long k_obs) {
+    const int ci = P.cls ? __ldg(&P.cls[h]) : 0;
+    const ChubClass &c = P.classes[ci];
+    HubVars v;
+    hub_load(P, h, v);
+    StationOut s0 = station_any<true>(P, h, 0, c.n[0], c.type[0], c.constant, 0, 0, 0u, v.rng, v.err);
+    StationOut s1 = station_any<true>(P, h, P.S0, c.n[1], c.type[1], c.constant, 0, 0, 0u, v.rng, v.err);
     v.t = 0;
     v.line0 = s0.line; v.line1 = s1.line;
     v.flow0 = s0.flow; v.flow1 = s1.flow;
     v.qn = 0; v.fline = 0; v.farr = 0;
     v.store = c.init_mass;
+    P.stats[h] = make_float4(0.f, 0.f, 0.f, 0.f);
+    double pv, wd, pr;
+    trace_at(P, h, k_obs, pv, wd, pr);
+    write_obs(P, h, c, 0, s0, s1, c.init_soc, pv, wd, pr);
+    if (P.diag) {
+        const size_t s = (size_t) P.Hpad;
+        float *q = P.st_power + h;
+        q[0 * s] = s0.mn; q[1 * s] = s0.now; q[2 * s] = s0.mx; q[3 * s] = s1.mn; q[4 * s] = s1.now; q[5 * s] = s1.mx;
+    }
+    hub_store(P, h, v);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -403,7 +426,8 @@ __device__ __forceinline__ void load_actions(const ChubParams &P, int h, bool ac
     }
 }
 
-__global__ void __launch_bounds__(128) chub_step_kernel(const ChubParams P) {
+template <int BLOCK, int MINB>
+__global__ void __launch_bounds__(BLOCK, MINB) chub_step_kernel(const __grid_constant__ ChubParams P) {
     const int h = blockIdx.x * blockDim.x + threadIdx.x;
     const bool active = h < P.H;
     const int ci = (active && P.cls) ? __ldg(&P.cls[h]) : 0;
@@ -412,18 +436,24 @@ __global__ void __launch_bounds__(128) chub_step_kernel(const ChubParams P) {
     unsigned long long bits;
     float a_m2, a_m1;
     load_actions(P, h, active, n0 + n1, bits, a_m2, a_m1);
-    if (!active) return;
 
     HubVars v;
-    hub_load(P, h, v);
+    v.err = 0u; v.t = 0; v.line0 = v.line1 = 0;
+    if (active) hub_load(P, h, v);
     const long long k = *P.step_index + P.step_offset;
-    double pv_t, wd_t, pr_t;
-    trace_at(P, h, k, pv_t, wd_t, pr_t);
+    double pv_t = 0.0, wd_t = 0.0, pr_t = 0.0;
+    if (active) trace_at(P, h, k, pv_t, wd_t, pr_t);
 
     // ---- the two EV stations, station 0 first (Aggregator_Simple.py:141-142) ----
-    StationOut s0 = station_any<false>(P, h, 0, n0, c.type[0], c.constant, v.t, v.line0, (uint32_t) bits, v.rng, v.err);
-    StationOut s1 = station_any<false>(P, h, P.S0, n1, c.type[1], c.constant, v.t, v.line1,
-                                       (uint32_t) (bits >> n0), v.rng, v.err);
+    // phase_sync keeps the warps of a block inside the same code region (instruction-cache locality)
+    StationOut s0, s1;
+    if (P.phase_sync) __syncthreads();
+    if (active) s0 = station_any<false>(P, h, 0, n0, c.type[0], c.constant, v.t, v.line0, (uint32_t) bits, v.rng, v.err);
+    if (P.phase_sync) __syncthreads();
+    if (active) s1 = station_any<false>(P, h, P.S0, n1, c.type[1], c.constant, v.t, v.line1,
+                                        (uint32_t) (bits >> n0), v.rng, v.err);
+    if (P.phase_sync) __syncthreads();
+    if (!active) return;
     v.line0 = s0.line; v.line1 = s1.line;
     v.flow0 = s0.flow; v.flow1 = s1.flow;
 
@@ -556,45 +586,33 @@ __global__ void __launch_bounds__(128) chub_step_kernel(const ChubParams P) {
     if (done) {
         P.last_stats[h] = st;
         st = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (P.auto_reset) {  // fused auto-reset: the returned obs is the first one of the next episode
-            hub_reset_body(P, h, c, v, s0, s1);
-            store_soc = c.init_soc;
-        }
     }
     P.stats[h] = st;
     P.reward[h] = (float) reward;
     P.done[h] = done ? 1 : 0;
-
-    double pv_n, wd_n, pr_n;
-    trace_at(P, h, k + 1, pv_n, wd_n, pr_n);
-    write_obs(P, h, c, v.t, s0, s1, store_soc, pv_n, wd_n, pr_n);
     hub_store(P, h, v);
+    if (done && P.auto_reset) {  // fused auto-reset: the returned obs is the first one of the next episode
+        hub_reset_full(P, h, k + 1);
+    } else {
+        double pv_n, wd_n, pr_n;
+        trace_at(P, h, k + 1, pv_n, wd_n, pr_n);
+        write_obs(P, h, c, v.t, s0, s1, store_soc, pv_n, wd_n, pr_n);
+    }
 }
 
-__global__ void __launch_bounds__(128) chub_reset_kernel(const ChubParams P) {
+__global__ void __launch_bounds__(128) chub_reset_kernel(const __grid_constant__ ChubParams P) {
     const int h = blockIdx.x * blockDim.x + threadIdx.x;
     if (h >= P.H) return;
     if (P.reset_mask && !P.reset_mask[h]) return;
-    const int ci = P.cls ? __ldg(&P.cls[h]) : 0;
-    const ChubClass &c = P.classes[ci];
-    HubVars v;
-    hub_load(P, h, v);
-    StationOut s0, s1;
-    hub_reset_body(P, h, c, v, s0, s1);
-    P.stats[h] = make_float4(0.f, 0.f, 0.f, 0.f);
     P.reward[h] = 0.0f;
     P.done[h] = 0;
     if (P.diag) {
+        const int ci = P.cls ? __ldg(&P.cls[h]) : 0;
         const size_t s = (size_t) P.Hpad;
         for (int j = 0; j < CHUB_D_COUNT; ++j) P.diag[j * s + h] = 0.0;
-        P.diag[CHUB_D_STORE_SOC * s + h] = c.init_soc;
-        float *q = P.st_power + h;
-        q[0 * s] = s0.mn; q[1 * s] = s0.now; q[2 * s] = s0.mx; q[3 * s] = s1.mn; q[4 * s] = s1.now; q[5 * s] = s1.mx;
+        P.diag[CHUB_D_STORE_SOC * s + h] = P.classes[ci].init_soc;
     }
-    double pv, wd, pr;
-    trace_at(P, h, *P.step_index, pv, wd, pr);
-    write_obs(P, h, c, 0, s0, s1, c.init_soc, pv, wd, pr);
-    hub_store(P, h, v);
+    hub_reset_full(P, h, *P.step_index);
 }
 
 // s2t(target) for the 1000 possible target SOCs x {fast, slow} x {curve, constant power}
@@ -602,15 +620,26 @@ __global__ void chub_s2t_lut_kernel(float *out) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= 4000) return;
     const int cp = idx / 2000, type = (idx / 1000) % 2, u = idx % 1000;
-    out[idx] = curve_s2t(type, cp, target_of((uint32_t) u));
+    out[idx] = curve_s2t_rt(type, cp, target_of((uint32_t) u));
 }
 void chub_launch_s2t_lut(float *out, cudaStream_t s) { chub_s2t_lut_kernel<<<(4000 + 127) / 128, 128, 0, s>>>(out); }
 
 __global__ void chub_tick_kernel(long long *step_index, int n) { *step_index += n; }
 
+#define CHUB_LAUNCH(B, M) chub_step_kernel<B, M><<<(p.H + (B) - 1) / (B), B, 0, s>>>(p)
 void chub_launch_step(const ChubParams &p, cudaStream_t s) {
-    const int block = 128;
-    chub_step_kernel<<<(p.H + block - 1) / block, block, 0, s>>>(p);
+    switch (p.block) {  // block size * 100 + min blocks per SM (register budget = 65536 / (block * minb))
+        case 12808: CHUB_LAUNCH(128, 8); break;
+        case 12810: CHUB_LAUNCH(128, 10); break;
+        case 12812: CHUB_LAUNCH(128, 12); break;
+        case 25604: CHUB_LAUNCH(256, 4); break;
+        case 25605: CHUB_LAUNCH(256, 5); break;
+        case 25606: CHUB_LAUNCH(256, 6); break;
+        case 51203: CHUB_LAUNCH(512, 3); break;
+        case 102401: CHUB_LAUNCH(1024, 1); break;
+        case 76801: CHUB_LAUNCH(768, 1); break;
+        default: CHUB_LAUNCH(512, 2); break;
+    }
 }
 void chub_launch_reset(const ChubParams &p, cudaStream_t s) {
     const int block = 128;

@@ -26,6 +26,7 @@ struct ChubParams {
     int H, Hpad, S0, S1;
     int n_classes, action_stride, auto_reset, diagnostics;
     int trace_len, trace_per_hub;
+    int block, phase_sync;            // launch shape of the step kernel
     int step_offset;                  // added to *step_index (graph-captured rollouts bake 0..n-1)
     const long long *step_index;      // device: absolute step index of the state being left
     uint4 *pile;
