@@ -11,7 +11,7 @@ OUT = os.path.join(CSRC, "libchub.so")
 # -fmad=false: the kernels reproduce the reference's separately rounded multiply/add; fused ops are
 # written explicitly as fma() where the design wants them (see csrc/chub_device.cuh).
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",
-              "-shared", "-Xcompiler", "-fPIC"]
+              "-shared", "-Xcompiler", "-fPIC,-fno-builtin-pow"]
 
 
 def up_to_date():

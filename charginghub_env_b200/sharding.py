@@ -1,0 +1,69 @@
+"""Multi-GPU layout of a hub batch: contiguous shards, no per-step communication.
+
+Hubs share nothing (each reference env is an isolated process; only read-only tables are common:
+CHS.hpp:23, Aggregator_Simple.py:12-15, renewable.py:12-18), so rank g of G steps the global hub
+range [lo, hi) on its own GPU.  Per-hub random streams are a function of the GLOBAL hub id
+(include/chub_rng.h), which makes results independent of G.  The only exchange is one gather of
+the episode-statistics buffer per rollout (torch.distributed: NCCL on GPUs, gloo in CPU tests).
+"""
+import numpy as np
+
+
+def shard_range(n_total, rank, world):
+    """Contiguous [lo, hi) of rank; the first n_total % world ranks get one extra hub."""
+    if not (0 <= rank < world) or n_total < 0:
+        raise ValueError("bad shard request")
+    base, extra = divmod(int(n_total), int(world))
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def hub_streams(base_seed, hub_ids):
+    """(key0, key1, minstd state) of each global hub id -- Python mirror of chub_hub_streams()."""
+    M = (1 << 64) - 1
+
+    def mix(z):
+        z = (z + 0x9E3779B97F4A7C15) & M
+        z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & M
+        z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & M
+        return z ^ (z >> 31)
+
+    k0, k1, e0 = [], [], []
+    for h in hub_ids:
+        s = mix((int(base_seed) ^ ((int(h) * 0xD1342543DE82EF95) & M)) & M)
+        r = mix(s)
+        k0.append(s & 0xFFFFFFFF)
+        k1.append(s >> 32)
+        e0.append(1 + (r % 2147483646))
+    return np.array(k0, np.uint32), np.array(k1, np.uint32), np.array(e0, np.uint32)
+
+
+def gather_stats(local_stats, n_total, dst=0):
+    """Gather per-hub episode statistics [n_local, K] of every rank on `dst`; returns [n_total, K] there
+    (None elsewhere).  Shards may differ in length by one hub, so rows are padded to the longest shard."""
+    import torch
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return local_stats
+    world, rank = dist.get_world_size(), dist.get_rank()
+    longest = shard_range(n_total, 0, world)[1]
+    pad = torch.zeros((longest,) + tuple(local_stats.shape[1:]), dtype=local_stats.dtype, device=local_stats.device)
+    pad[: local_stats.shape[0]] = local_stats
+    bufs = [torch.empty_like(pad) for _ in range(world)] if rank == dst else None
+    dist.gather(pad, bufs, dst=dst)
+    if rank != dst:
+        return None
+    parts = []
+    for r in range(world):
+        lo, hi = shard_range(n_total, r, world)
+        parts.append(bufs[r][: hi - lo])
+    return torch.cat(parts, 0)
+
+
+def reduce_stats(local_stats):
+    """Sum of the statistics columns over all hubs of all ranks (the 32-byte variant of the gather)."""
+    import torch.distributed as dist
+    s = local_stats.sum(0)
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(s)
+    return s

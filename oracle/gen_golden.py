@@ -1,0 +1,70 @@
+"""TEST INFRASTRUCTURE ONLY.  Generate tests/golden/*.npz by running the UNMODIFIED reference
+(/root/reference through oracle/ref_env.py) on seeded streams and pre-drawn actions.
+
+The reference's own tests hold no golden vectors, so these traces -- outputs of
+the reference itself, produced in this container (glibc / libstdc++ of this image, Python 3.12) --
+are what pins the oracle (tests/test_oracle_golden.py) and the CUDA engine (tests/test_gpu_golden.py)
+on machines where /root/reference does not exist.  Run:  python -m oracle.gen_golden
+"""
+import os
+
+import numpy as np
+
+from . import ref_env, ref_rollout
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+BASE = dict(ref_env.DEFAULT_KWARGS)
+
+CASES = {
+    # name: (kwargs, hubs, steps, base_seed)
+    "default_hub": (BASE, 6, 96, 0x5EED),
+    "small_fast_big_slow_perm05": (dict(BASE, station_list=[4, 32], fcev_permeate=0.05, hydro_prod_rate=430,
+                                        hydro_store_vlt=10.0, init_soc=0.8, fc_max_power=200), 4, 96, 11),
+    "slow_first_loss": (dict(BASE, station_list=[32, 5], station_type_list=["slow", "fast"], fcev_permeate=0.02,
+                             hydro_prod_rate=50, hydro_store_vlt=100.0, init_soc=0.45, fc_max_power=50,
+                             hydro_loss=0.02), 4, 96, 12),
+    "constant_charging": (dict(BASE, constant_charging=True), 3, 96, 13),
+    "two_fast_low_store": (dict(BASE, station_list=[7, 9], station_type_list=["fast", "fast"], fcev_permeate=0.05,
+                                hydro_store_vlt=10.0, init_soc=0.1), 3, 96, 14),
+    "two_slow_defaults_none": (dict(BASE, station_list=[12, 12], station_type_list=["slow", "slow"],
+                                    hydro_prod_rate=None, hydro_store_vlt=None, fc_max_power=None, init_soc=0.5),
+                               3, 96, 15),
+}
+
+KEEP = ["pile_car", "pile_charge", "pile_urgent", "pile_stay", "pile_already", "pile_soc", "pile_target",
+        "pile_power", "pile_arrive", "st_line", "st_flow_in", "st_car_number", "st_min_power", "st_charge_power",
+        "st_max_power", "hub_t", "hub_uctr", "hub_lcg", "fcev_arrive", "fcev_qn", "hub_done", "store", "store_soc",
+        "reward", "income", "hy_flow", "h2_power", "fc_power", "hy_use", "not_meet", "hy_to_use", "demand",
+        "h2_grid", "hy_act", "pv", "wd", "price", "obs"]
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    tabs = ref_rollout.reference_tables()
+    for name, (kw, H, T, seed) in CASES.items():
+        A = sum(kw["station_list"]) + 2
+        actions = np.random.RandomState(1234 + seed).uniform(-1, 1, (T, H, A)).astype(np.float32)
+        out, env = ref_rollout.reference_rollout(kw, seed, np.arange(H), actions)
+        pack = {k: out[k] for k in KEEP}
+        for k in ("pile_car", "pile_charge", "pile_urgent", "pile_stay", "pile_already"):
+            pack[k] = pack[k].astype(np.int8)
+        for k in ("st_line", "st_flow_in", "st_car_number", "hub_t", "fcev_arrive", "fcev_qn", "hub_done"):
+            pack[k] = pack[k].astype(np.int16)
+        pack["hub_uctr"] = pack["hub_uctr"].astype(np.uint32)
+        pack["hub_lcg"] = pack["hub_lcg"].astype(np.uint32)
+        pack["actions"] = actions
+        pack["el_table"] = np.array(env.hy_sys.hy_power_speed_list, np.float64)
+        pack["transformer"] = np.array([s.transformer_limit for s in env.env_aggregator.evcssp_evs_objects], np.float64)
+        kws = dict(kw)
+        pack["kwargs_repr"] = np.array(repr(kws))
+        pack["base_seed"] = np.array(seed, np.uint64)
+        path = os.path.join(OUT, name + ".npz")
+        np.savez_compressed(path, **pack)
+        print(name, H, "hubs", T, "steps ->", os.path.getsize(path), "bytes")
+    np.savez_compressed(os.path.join(OUT, "tables_check.npz"), flow_row0=tabs["flow"][0], flow_row50=tabs["flow"][50],
+                        price=tabs["price"], price_mean=tabs["price_mean"], price_std=tabs["price_std"],
+                        sin_table=tabs["sin_table"])
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,66 @@
+"""CPU: host-side logic of the package that needs no GPU -- shard arithmetic, stream derivation,
+hub-class marshalling, packaged tables."""
+import numpy as np
+
+from charginghub_env_b200 import make_hub_class, sharding
+from oracle import oracle as O
+from tests import common as C
+
+
+def test_shard_ranges_partition_the_batch():
+    for n, w in [(1048576, 8), (10, 4), (7, 8), (4194304, 8), (5, 1)]:
+        edges = [sharding.shard_range(n, r, w) for r in range(w)]
+        assert edges[0][0] == 0 and edges[-1][1] == n
+        assert all(edges[r][1] == edges[r + 1][0] for r in range(w - 1))
+        sizes = [b - a for a, b in edges]
+        assert max(sizes) - min(sizes) <= 1
+
+
+def test_python_stream_mirror_equals_c_header():
+    """sharding.hub_streams (used to seed explicit streams) == chub_hub_streams() in include/chub_rng.h."""
+    ids = np.array([0, 1, 2, 4095, 4096, 1048575, 4194303], np.int64)
+    k0, k1, e0 = sharding.hub_streams(0x5EED, ids)
+    for j, h in enumerate(ids):
+        orc = O.Oracle(1, [C.DEFAULT_KW])
+        orc.seed_base(0x5EED, int(h))
+        assert np.uint32(orc.get("hub_lcg")[0]) == e0[j]
+        # keys are not readable back, so check them through the first U draw: step-free, via reset draws
+    assert len(set(e0.tolist())) == len(ids) and (e0 >= 1).all() and (e0 <= 2147483646).all()
+    assert len(set(zip(k0.tolist(), k1.tolist()))) == len(ids)
+
+
+def test_streams_do_not_depend_on_sharding(tables):
+    """Hub 5 of a 1-shard batch == hub 1 of the shard that starts at global id 4."""
+    rs = np.random.RandomState(3)
+    pv, wd, pr = C.synth_traces(tables, 9, rs)
+    a = rs.uniform(-1, 1, (8, 47)).astype(np.float32)
+    whole = O.Oracle(8, [C.DEFAULT_KW], tables=C.oracle_tables(tables))
+    whole.seed_base(7, 0)
+    part = O.Oracle(4, [C.DEFAULT_KW], tables=C.oracle_tables(tables))
+    part.seed_base(7, 4)
+    whole.reset(pv[0], wd[0], pr[0])
+    part.reset(pv[0], wd[0], pr[0])
+    for t in range(8):
+        whole.step(a, pv[t + 1], wd[t + 1], pr[t + 1])
+        part.step(a[4:], pv[t + 1], wd[t + 1], pr[t + 1])
+    for name in ("pile_soc", "pile_stay", "st_line", "reward", "store"):
+        assert np.array_equal(whole.get(name)[4:], part.get(name)), name
+
+
+def test_hub_class_marshalling():
+    c, keep = make_hub_class(**C.DEFAULT_KW)
+    assert (c.n_piles[0], c.n_piles[1]) == (20, 25) and (c.station_type[0], c.station_type[1]) == (0, 1)
+    assert c.hydro_prod_rate == 100.0 and c.hydro_store_vlt == 25.0 and c.init_soc == 0.2 and keep is None
+    c, _ = make_hub_class(station_list=[3, 4], station_type_list=["slow", "slow"])
+    assert c.hydro_prod_rate < 0 and c.hydro_store_vlt < 0 and c.fc_max_power < 0  # None -> engine defaults
+    tab = np.arange(102, dtype=np.float64)
+    c, keep = make_hub_class(el_table=tab)
+    assert keep is not None and c.el_table[101] == 101.0
+
+
+def test_packaged_tables(tables):
+    assert tables["arrival_cdf"].shape == (96, 301) and tables["price"].shape == (96,)
+    assert tables["pv_days"].shape == (100, 96) and tables["wd_days"].shape == (150, 96)
+    cdf = tables["arrival_cdf"]
+    assert (np.diff(cdf, axis=1) >= -1e-6).all() and cdf.max() <= 1.0 + 1e-6  # rows are CDFs
+    assert abs(tables["price_mean"] - tables["price"].mean()) < 1e-15

@@ -1,0 +1,70 @@
+"""CPU: the C restatement (oracle/hub_oracle.c) against golden traces produced by the UNMODIFIED
+reference (oracle/gen_golden.py, run where /root/reference exists).  Integers and fp32 state must be
+bit-identical at every step; fp64 hydrogen/reward quantities are compared to 1e-12 relative because the
+fixtures were generated under Python 3.12, whose built-in sum() is compensated (the reference's target
+Python 3.7 and this restatement add left to right) -- a last-bit difference only when >= 2 FCEVs queue."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from tests import common as C
+
+GOLD = sorted(g for g in glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz"))
+              if not g.endswith("tables_check.npz"))
+EXACT = ["pile_car", "pile_charge", "pile_urgent", "pile_stay", "pile_already", "pile_soc", "pile_target",
+         "pile_power", "pile_arrive", "st_line", "st_flow_in", "st_car_number", "st_min_power", "st_charge_power",
+         "st_max_power", "hub_t", "hub_uctr", "hub_lcg", "fcev_qn"]
+STEP_ONLY_EXACT = ["fcev_arrive", "hub_done", "hy_flow", "h2_power", "fc_power", "hy_act", "h2_grid"]
+NEAR = ["store", "store_soc", "obs"]
+STEP_ONLY_NEAR = ["reward", "income", "hy_use", "not_meet", "hy_to_use", "demand"]
+
+
+def load_case(path):
+    z = np.load(path)
+    kw = eval(str(z["kwargs_repr"]), {"__builtins__": {}})  # a dict literal written by gen_golden.py
+    return z, kw
+
+
+def test_fixtures_present():
+    assert len(GOLD) >= 6
+
+
+def test_tables_match_reference(tables):
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "tables_check.npz"))
+    assert np.array_equal(tables["arrival_cdf"][0], z["flow_row0"])
+    assert np.array_equal(tables["arrival_cdf"][50], z["flow_row50"])
+    assert np.array_equal(tables["price"], z["price"])
+    assert tables["price_mean"] == float(z["price_mean"]) and tables["price_std"] == float(z["price_std"])
+    assert np.allclose(tables["time_sin"], z["sin_table"], rtol=0, atol=1e-15)
+
+
+@pytest.mark.parametrize("path", GOLD, ids=[os.path.basename(p)[:-4] for p in GOLD])
+def test_oracle_reproduces_reference(path, tables):
+    z, kw = load_case(path)
+    T, H, A = z["actions"].shape
+    orc = O.Oracle(H, [kw], tables=C.oracle_tables(tables), el_tables=[z["el_table"]])
+    d = orc.class_derived(0)
+    assert d["transformer0"] == z["transformer"][0] and d["transformer1"] == z["transformer"][1]
+    orc.seed_base(int(z["base_seed"]), 0)
+    orc.reset(z["pv"][0], z["wd"][0], z["price"][0])
+
+    def check(t):
+        for name in EXACT + (STEP_ONLY_EXACT if t else []):
+            a, b = z[name][t], orc.get(name)
+            if name in ("hub_uctr", "hub_lcg"):
+                b = b.astype(np.uint32)
+            assert np.array_equal(a.astype(b.dtype), b), (name, t)
+        for name in NEAR + (STEP_ONLY_NEAR if t else []):
+            a, b = z[name][t], orc.get(name)
+            if name == "obs":
+                b = b[:, :a.shape[1]]
+            assert np.allclose(a, b, rtol=1e-12, atol=1e-12), (name, t)
+
+    check(0)
+    for t in range(T):
+        orc.step(z["actions"][t], z["pv"][t + 1], z["wd"][t + 1], z["price"][t + 1])
+        check(t + 1)
+    assert (orc.get("hub_err") == 0).all()

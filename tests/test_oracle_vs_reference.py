@@ -1,0 +1,60 @@
+"""CPU, only where /root/reference exists: the C restatement against the LIVE unmodified reference
+(pybind11 shim over CHS.hpp + the reference's own Python layer), larger than the committed fixtures."""
+import numpy as np
+import pytest
+
+from oracle import ref_env
+from tests import common as C
+
+pytestmark = pytest.mark.skipif(not (ref_env.reference_available() and ref_env.shim_path()),
+                                reason="needs /root/reference and oracle/_ref (make -C oracle ref)")
+
+
+def _compare(kw, H, T, seed):
+    from oracle import oracle as O, ref_rollout
+    actions = np.random.RandomState(99 + seed).uniform(-1, 1, (T, H, sum(kw["station_list"]) + 2)).astype(np.float32)
+    ref, env = ref_rollout.reference_rollout(kw, seed, np.arange(H), actions)
+    tabs = ref_rollout.reference_tables()
+    orc = O.Oracle(H, [kw], tables=tabs, el_tables=[np.array(env.hy_sys.hy_power_speed_list)])
+    orc.seed_base(seed, 0)
+    orc.reset(ref["pv"][0], ref["wd"][0], ref["price"][0])
+    exact = ["pile_car", "pile_charge", "pile_urgent", "pile_stay", "pile_already", "pile_soc", "pile_target",
+             "pile_power", "pile_arrive", "pile_emergency", "st_line", "st_flow_in", "st_car_number",
+             "st_min_power", "st_charge_power", "st_max_power", "hub_uctr", "hub_lcg", "fcev_qn"]
+    for t in range(T + 1):
+        if t:
+            orc.step(actions[t - 1], ref["pv"][t], ref["wd"][t], ref["price"][t])
+        for name in exact:
+            b = orc.get(name)
+            if name in ("hub_uctr", "hub_lcg"):
+                b = b.astype(np.uint32)
+            assert np.array_equal(ref[name][t].astype(b.dtype), b), (name, t)
+        for name in ("store", "store_soc") + (("reward", "income", "demand", "hy_use", "not_meet") if t else ()):
+            assert np.allclose(ref[name][t], orc.get(name), rtol=1e-12, atol=1e-12), (name, t)
+        assert np.allclose(ref["obs"][t], orc.get("obs")[:, :ref["obs"].shape[2]], rtol=1e-12, atol=1e-12)
+
+
+def test_default_hub_live():
+    _compare(dict(ref_env.DEFAULT_KWARGS), 24, 96, 777)
+
+
+def test_unclipped_table_equals_reference_list():
+    from oracle import oracle as O
+    Env = ref_env.load_reference_env_class()
+    with ref_env.quiet():
+        env = Env(**ref_env.DEFAULT_KWARGS)
+    orc = O.Oracle(1, [dict(ref_env.DEFAULT_KWARGS)])
+    assert np.array_equal(np.array(env.hy_sys.hy_power_speed_list), orc.class_table(0))
+
+
+def test_curves_against_reference_functions():
+    """Each restated curve against the compiled reference function on 200k random fp32 arguments."""
+    from oracle import oracle as O
+    ps = ref_env.load_shim()
+    rs = np.random.RandomState(5)
+    for which, lo, hi in [(0, -1, 16), (1, -1, 16), (2, -5, 105), (3, -1, 4), (4, -1, 4), (5, -5, 105)]:
+        x = rs.uniform(lo, hi, 200000).astype(np.float32)
+        for cp in (False, True):
+            a = np.asarray(ps.curve_batch(which, x, cp))
+            b = O.curve_batch(which, x, cp)
+            assert np.array_equal(a, b), (which, cp)
