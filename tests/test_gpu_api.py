@@ -1,0 +1,124 @@
+"""-m gpu: behaviour of the C-ABI surface itself -- host path, graph rollouts, checkpoints, DLPack, errors."""
+import numpy as np
+import pytest
+
+from tests import common as C
+
+pytestmark = pytest.mark.gpu
+
+
+def _engine(H, tables, seed=1, **kw):
+    from charginghub_env_b200 import HubEngine
+    rs = np.random.RandomState(seed)
+    eng = HubEngine(H, [C.DEFAULT_KW], device=0, tables=tables, seed=seed, **kw)
+    eng.set_traces(*C.synth_traces(tables, 400, rs))
+    return eng, rs
+
+
+def test_unclipped_table_equals_oracle_table(tables):
+    from oracle import oracle as O
+    eng, _ = _engine(32, tables)
+    assert np.array_equal(eng.class_table(0), O.Oracle(1, [C.DEFAULT_KW]).class_table(0))
+    assert eng.algorithmic_bytes(0) == 1845  # SURVEY.md 8d, default hub
+
+
+def test_host_path_equals_device_path(tables):
+    import torch
+    a_eng, rs = _engine(300, tables, seed=3)
+    b_eng, _ = _engine(300, tables, seed=3)
+    a_eng.reset()
+    obs_h = b_eng.reset_host().copy()
+    assert np.array_equal(a_eng.tensor("obs").cpu().numpy(), obs_h)
+    for t in range(20):
+        a = rs.uniform(-1, 1, (300, 47)).astype(np.float32)
+        o, r, d = a_eng.step(torch.from_numpy(a).cuda())
+        oh, rh, dh = b_eng.step_host(a)
+        assert np.array_equal(o.cpu().numpy(), oh) and np.array_equal(r.cpu().numpy(), rh)
+        assert np.array_equal(d.cpu().numpy(), dh)
+
+
+def test_graph_rollout_equals_stepwise(tables):
+    import torch
+    a_eng, rs = _engine(1000, tables, seed=5, auto_reset=True)
+    b_eng, _ = _engine(1000, tables, seed=5, auto_reset=True)
+    acts = torch.from_numpy(rs.uniform(-1, 1, (1000, 47)).astype(np.float32)).cuda()
+    a_eng.reset()
+    b_eng.reset()
+    b_eng.capture_rollout(acts, 16)
+    for rep in range(7):  # 112 steps: crosses the day boundary, so the trace index must advance per replay
+        for _ in range(16):
+            a_eng.step(acts)
+        b_eng.rollout()
+    torch.cuda.synchronize()
+    assert a_eng.counters()["step_index"] == b_eng.counters()["step_index"] == 112
+    for name in ("pile_soc", "pile_stay", "st_line", "hub_uctr", "hub_lcg", "store", "hub_t"):
+        assert np.array_equal(a_eng.get(name), b_eng.get(name)), name
+    assert np.array_equal(a_eng.tensor("obs").cpu().numpy(), b_eng.tensor("obs").cpu().numpy())
+    assert np.array_equal(a_eng.tensor("stats").cpu().numpy(), b_eng.tensor("stats").cpu().numpy())
+
+
+def test_checkpoint_roundtrip(tables):
+    import torch
+    eng, rs = _engine(500, tables, seed=7)
+    acts = [torch.from_numpy(rs.uniform(-1, 1, (500, 47)).astype(np.float32)).cuda() for _ in range(20)]
+    eng.reset()
+    for a in acts[:10]:
+        eng.step(a)
+    blob = eng.get_state()
+    for a in acts[10:]:
+        eng.step(a)
+    torch.cuda.synchronize()
+    want = {n: eng.get(n) for n in ("pile_soc", "pile_power", "pile_stay", "st_line", "store", "hub_lcg")}
+    want_obs = eng.tensor("obs").cpu().numpy().copy()
+    eng.set_state(blob)
+    for a in acts[10:]:
+        eng.step(a)
+    torch.cuda.synchronize()
+    for n, v in want.items():
+        assert np.array_equal(eng.get(n), v), n
+    assert np.array_equal(eng.tensor("obs").cpu().numpy(), want_obs)
+
+
+def test_dlpack_views_alias_engine_memory(tables):
+    import torch
+    eng, rs = _engine(64, tables)
+    obs = eng.reset()
+    assert obs.is_cuda and obs.shape == (64, 13) and obs.dtype == torch.float32
+    rew, done = eng.tensor("reward"), eng.tensor("done")
+    assert rew.shape == (64,) and done.dtype == torch.uint8
+    before = obs.clone()
+    eng.step(torch.from_numpy(rs.uniform(-1, 1, (64, 47)).astype(np.float32)).cuda())
+    torch.cuda.synchronize()
+    assert not torch.equal(before, obs)  # same memory, updated in place by the kernel
+    keep = eng.tensor("stats")
+    eng.close()  # views keep the engine alive until they die
+    assert torch.isfinite(keep).all()
+
+
+def test_errors_are_reported_not_printed(tables):
+    import torch
+    from charginghub_env_b200 import ChubError, HubEngine
+    eng = HubEngine(16, [C.DEFAULT_KW], device=0, tables=tables)
+    with pytest.raises(ChubError):  # no traces yet
+        eng.reset()
+    with pytest.raises(ValueError):  # action width, evcssp_manager.py:148
+        eng.set_traces(*C.synth_traces(tables, 10, np.random.RandomState(0)))
+        eng.step(torch.zeros((16, 46), device="cuda"))
+    with pytest.raises(ChubError):
+        HubEngine(16, [dict(C.DEFAULT_KW, init_soc=0.05)], device=0, tables=tables)  # hydro_sys.py:137
+    with pytest.raises(ChubError):
+        HubEngine(16, [dict(C.DEFAULT_KW, station_list=[40, 2])], device=0, tables=tables)
+
+
+def test_fcev_backlog_overflow_sets_error_bit(tables):
+    """A permeate of 1.0 floods the FCEV list; the engine keeps 8 entries and raises the sticky bit."""
+    import torch
+    from charginghub_env_b200 import HubEngine
+    eng = HubEngine(64, [dict(C.DEFAULT_KW, fcev_permeate=1.0)], device=0, tables=tables, seed=2)
+    eng.set_traces(*C.synth_traces(tables, 100, np.random.RandomState(0)))
+    eng.reset()
+    a = torch.zeros((64, 47), device="cuda")
+    for _ in range(60):
+        eng.step(a)
+    assert eng.counters()["error_or"] & 1
+    assert (eng.tensor("error").cpu().numpy() & 1).any()
