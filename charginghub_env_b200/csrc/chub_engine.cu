@@ -327,6 +327,18 @@ extern "C" int chub_set_traces(chub_engine *e, const double *pv, const double *w
     return CHUB_OK;
 }
 
+extern "C" int chub_poke_trace(chub_engine *e, int32_t slot, double pv, double wd, double price, void *stream) {
+    if (!e || !e->have_traces || e->trace_per_hub || slot < 0 || slot >= e->trace_len)
+        return fail(CHUB_ERR_ARG, "chub_poke_trace: needs shared traces and a slot inside them");
+    CK(cudaSetDevice(e->cfg.device));
+    cudaStream_t s = (cudaStream_t) stream;
+    CK(cudaMemcpyAsync(e->pv + slot, &pv, sizeof(double), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(e->wd + slot, &wd, sizeof(double), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(e->price_tr + slot, &price, sizeof(double), cudaMemcpyHostToDevice, s));
+    CK(cudaStreamSynchronize(s));  // the three doubles live on this stack frame
+    return CHUB_OK;
+}
+
 static int upload_streams(chub_engine *e, const std::vector<uint2> &keys, const std::vector<uint4> &hubA) {
     CK(cudaMemcpy(e->keys, keys.data(), sizeof(uint2) * e->H, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(e->hubA, hubA.data(), sizeof(uint4) * e->H, cudaMemcpyHostToDevice));

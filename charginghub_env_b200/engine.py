@@ -157,6 +157,9 @@ class HubEngine(object):
                 raise ValueError("trace shape %s, expected %s" % (x.shape, want))
         check(self.lib.chub_set_traces(self.h, _dptr(a[0]), _dptr(a[1]), _dptr(a[2]), a[0].shape[0], int(per_hub)))
 
+    def poke_trace(self, slot, pv, wd, price, stream=0):
+        check(self.lib.chub_poke_trace(self.h, int(slot), float(pv), float(wd), float(price), ctypes.c_void_p(int(stream))))
+
     def seed(self, base_seed):
         check(self.lib.chub_seed(self.h, ctypes.c_uint64(int(base_seed) & ((1 << 64) - 1))))
 

@@ -131,6 +131,10 @@ int chub_get_class_table(chub_engine *e, int32_t k, double *out);
 int chub_set_traces(chub_engine *e, const double *pv, const double *wd, const double *price,
                     int32_t length, int32_t per_hub);
 
+/* Overwrite one slot of SHARED traces (an online caller that generates the exogenous values step by
+ * step, like the single-hub gym wrapper, keeps a short ring and pokes the next slot before each step). */
+int chub_poke_trace(chub_engine *e, int32_t slot, double pv, double wd, double price, void *stream);
+
 /* Streams: either derive (key0,key1,minstd state) from base_seed and the global hub id
  * (include/chub_rng.h), or set them explicitly (host arrays [n_hubs]; uctr may be NULL = 0). */
 int chub_seed(chub_engine *e, uint64_t base_seed);
