@@ -399,29 +399,37 @@ __device__ __forceinline__ void load_actions(const ChubParams &P, int h, bool ac
     const int lane = threadIdx.x & 31;
     const int h0 = h - lane;
     bits = 0ull; a_m2 = 0.0f; a_m1 = 0.0f;
-    const int my_na = active ? na : -2;
-    for (int r = 0; r < 32; ++r) {
-        const int row_na = __shfl_sync(full, my_na, r);
-        if (row_na < 0) continue;  // uniform: that lane has no hub
-        const float *rowp = P.actions + (size_t) (h0 + r) * P.action_stride;
-        unsigned m0 = 0u, m1 = 0u;
-        float e2 = 0.0f, e1 = 0.0f;
-        for (int c = 0; c * 32 < row_na + 2; ++c) {
-            const int idx = c * 32 + lane;
-            float v = (idx < row_na + 2) ? __ldg(rowp + idx) : -1.0f;
-            bool on = (idx < row_na) && ((v + 1.0f) / 2.0f >= 0.5f);
-            unsigned m = __ballot_sync(full, on);
-            if (c == 0) m0 = m;
-            if (c == 1) m1 = m;
-            float s2 = __shfl_sync(full, v, row_na & 31);
-            float s1 = __shfl_sync(full, v, (row_na + 1) & 31);
-            if ((row_na >> 5) == c) e2 = s2;
-            if (((row_na + 1) >> 5) == c) e1 = s1;
+    const int my_na = active ? na : -2;  // -2: no hub in this lane -> every column predicate is false
+    // eight rows per batch: all their loads are issued before the first value is used, so the warp
+    // pays four memory round trips for its 32 rows instead of one per row and chunk
+    for (int r0 = 0; r0 < 32; r0 += 8) {
+        float v[8][3];
+        int rna[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            rna[j] = __shfl_sync(full, my_na, r0 + j);
+            const float *rowp = P.actions + (size_t) (h0 + r0 + j) * P.action_stride;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                const int idx = c * 32 + lane;
+                v[j][c] = (idx < rna[j] + 2) ? __ldg(rowp + idx) : -1.0f;
+            }
         }
-        if (lane == r) {
-            bits = (unsigned long long) m0 | ((unsigned long long) m1 << 32);
-            a_m2 = e2;  // action[-2] -> electrolyser set-point (the reference swaps the last two)
-            a_m1 = e1;  // action[-1] -> fuel-cell set-point
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int n = rna[j];
+            const unsigned m0 = __ballot_sync(full, lane < n && (v[j][0] + 1.0f) / 2.0f >= 0.5f);
+            const unsigned m1 = __ballot_sync(full, 32 + lane < n && (v[j][1] + 1.0f) / 2.0f >= 0.5f);
+            const int c2 = n >> 5, c1 = (n + 1) >> 5;  // chunks holding action[-2] and action[-1]
+            const float t2 = c2 == 0 ? v[j][0] : (c2 == 1 ? v[j][1] : v[j][2]);
+            const float t1 = c1 == 0 ? v[j][0] : (c1 == 1 ? v[j][1] : v[j][2]);
+            const float e2 = __shfl_sync(full, t2, n & 31);
+            const float e1 = __shfl_sync(full, t1, (n + 1) & 31);
+            if (lane == r0 + j) {
+                bits = (unsigned long long) m0 | ((unsigned long long) m1 << 32);
+                a_m2 = e2;  // action[-2] -> electrolyser set-point (the reference swaps the last two)
+                a_m1 = e1;  // action[-1] -> fuel-cell set-point
+            }
         }
     }
 }
@@ -446,14 +454,18 @@ __global__ void __launch_bounds__(BLOCK, MINB) chub_step_kernel(const __grid_con
 
     // ---- the two EV stations, station 0 first (Aggregator_Simple.py:141-142) ----
     // phase_sync keeps the warps of a block inside the same code region (instruction-cache locality)
-    StationOut s0, s1;
-    if (P.phase_sync) __syncthreads();
-    if (active) s0 = station_any<false>(P, h, 0, n0, c.type[0], c.constant, v.t, v.line0, (uint32_t) bits, v.rng, v.err);
-    if (P.phase_sync) __syncthreads();
-    if (active) s1 = station_any<false>(P, h, P.S0, n1, c.type[1], c.constant, v.t, v.line1,
+    StationOut s0 = {}, s1 = {};
+    if (P.phase_sync & 1) __syncthreads();
+    if (active && !(P.phase_sync & 2)) s0 = station_any<false>(P, h, 0, n0, c.type[0], c.constant, v.t, v.line0, (uint32_t) bits, v.rng, v.err);
+    if (P.phase_sync & 1) __syncthreads();
+    if (active && !(P.phase_sync & 4)) s1 = station_any<false>(P, h, P.S0, n1, c.type[1], c.constant, v.t, v.line1,
                                         (uint32_t) (bits >> n0), v.rng, v.err);
-    if (P.phase_sync) __syncthreads();
+    if (P.phase_sync & 1) __syncthreads();
     if (!active) return;
+    if (P.phase_sync & 8) {  // timing ablation only: stations without the hub section
+        hub_store(P, h, v);
+        return;
+    }
     v.line0 = s0.line; v.line1 = s1.line;
     v.flow0 = s0.flow; v.flow1 = s1.flow;
 
