@@ -23,7 +23,7 @@ struct ChubConst {
     float balk[64];        // expf((float)-(0.01 * k))               CHS.hpp:1299
     double price[96];      // price_after_MAD_96                     Aggregator_Simple.py:9-15
     double time_sin[96];   // sin(2 pi t / 96)                       evcssp_manager.py:319-320
-    double price_mean, price_std;
+    double price_mean, price_std, r_price_std;
     // curve constants that the reference evaluates with libm at run time
     float fast_aa1_c;      // (float)((0.7194/0.053) * exp(0))       CHS.hpp:693
     float fast_aa2_c;      // aa_part2_c                             CHS.hpp:698-700
@@ -47,6 +47,7 @@ struct ChubClass {
     float possible_in_f;   // (float) 0.3
     float transformer[2];  // CHS.hpp:1153-1154 / 1463-1464
     double half[2];        // transformer / 2 (evcssp_manager.py:377)
+    double r_half[2], r_el_cells, r_el_den, r_cap_mass;  // correctly rounded reciprocals for chub_div_const
     double v_h_max, v_M, cap_mass, cap_floor /* cap_mass*0.1 */, floor_01 /* 0.1*cap_mass */;
     double init_soc, init_mass, loss, fc_cells, cpr_w12;
     double el_cells;       // integer valued

@@ -163,6 +163,10 @@ static void derive_class(const chub_hub_class &in, ChubClass &c, double *table) 
     c.init_mass = in.init_soc * c.cap_mass;
     c.loss = in.hydro_loss;
     c.fc_cells = in.fc_max_power < 0 ? 100.0 : in.fc_max_power;
+    for (int k = 0; k < 2; ++k) c.r_half[k] = c.half[k] != 0.0 ? 1.0 / c.half[k] : 0.0;
+    c.r_el_cells = c.el_cells != 0.0 ? 1.0 / c.el_cells : 0.0;
+    c.r_el_den = 1.0 / c.el_den;
+    c.r_cap_mass = 1.0 / c.cap_mass;
     if (in.el_table) {
         memcpy(table, in.el_table, sizeof(double) * CHUB_EL_TABLE);
     } else {  // hy_step(0.01*i) on an unclipped store (hydro_sys.py:153-157, 172-186)
@@ -261,6 +265,7 @@ extern "C" int chub_set_tables(chub_engine *e, const chub_tables *t) {
     memcpy(c.time_sin, t->time_sin, sizeof c.time_sin);
     c.price_mean = t->price_mean;
     c.price_std = t->price_std;
+    c.r_price_std = 1.0 / t->price_std;
     c.fast_aa1_c = (float) ((0.7194 / 0.053) * std::exp(0));
     c.fast_aa2_c = (float) (h_fast_aa1((float) 28.7, c.fast_aa1_c) - h_fast_anti(28.7));
     {

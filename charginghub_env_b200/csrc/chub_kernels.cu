@@ -215,22 +215,25 @@ __device__ __forceinline__ StationOut station_any(const ChubParams &P, int h, in
 // hydrogen side (hydro_sys.py), fp64 like the reference's Python floats; every expression keeps
 // Python's evaluation order and -fmad=false keeps each multiply/add separately rounded.
 
+// x / D for a literal D: exactly the IEEE quotient (Markstein correction), 3 instructions instead of ~25
+#define DIVC(x, D) chub_div_const((x), (D), 1.0 / (D))
+
 __device__ __forceinline__ double py_max(double a, double b) { return b > a ? b : a; }  // Python max(a, b)
 __device__ __forceinline__ double py_min(double a, double b) { return b < a ? b : a; }  // Python min(a, b)
 
 __device__ __forceinline__ double el_power(const ChubClass &c, double m) {  // Electrolyser.get_power, hydro_sys.py:38-48
     if (c.el_cells == 0.0) return 0.0;
-    double v_H_mass = m / c.el_cells;
-    double v_H_mol = v_H_mass / 2.02;
+    double v_H_mass = chub_div_const(m, c.el_cells, c.r_el_cells);
+    double v_H_mol = DIVC(v_H_mass, 2.02);
     double v_H_L = v_H_mol * c.v_M;
     double v_H = v_H_L * 1000.0 * 60.0;
-    double temp = v_H * 2.0 * 96487.0 / c.el_den;
+    double temp = chub_div_const(v_H * 2.0 * 96487.0, c.el_den, c.r_el_den);
     double power = (temp * temp) * 0.326 + temp * 1.476;
-    return c.el_cells * power / 1000.0;
+    return DIVC(c.el_cells * power, 1000.0);
 }
 __device__ __forceinline__ double cpr_power(const ChubClass &c, double m) {  // Compressor.generate_W, hydro_sys.py:74-82
-    double n = m / 2.02;
-    return (n * c.cpr_w12 / 0.8) / 1000.0;
+    double n = DIVC(m, 2.02);
+    return DIVC(DIVC(n * c.cpr_w12, 0.8), 1000.0);
 }
 
 // SAE J2601 table: initial pressure -> target pressure (hydro_sys.py:338-388)
@@ -249,9 +252,9 @@ __device__ __forceinline__ void fcev_need(float soc_f, double &minutes, double &
     if (soc < 0.5) soc = 0.5;
     double p0 = (soc * 0.01) * 70.0;
     double tp = j2601_target(p0);
-    if (p0 < 5.0) minutes = (69.0 - p0) / 18.5 + kC.topoff_time;
-    else minutes = (tp - p0) / 18.5;
-    grams = kC.fcev_cap * (tp / 70.0) - kC.fcev_cap * (p0 / 70.0);
+    if (p0 < 5.0) minutes = DIVC(69.0 - p0, 18.5) + kC.topoff_time;
+    else minutes = DIVC(tp - p0, 18.5);
+    grams = kC.fcev_cap * DIVC(tp, 70.0) - kC.fcev_cap * DIVC(p0, 70.0);
 }
 
 // HyFCEVStation.hvs_step with a backlog or several arrivals (hydro_sys.py:266-285); rare, kept
@@ -340,22 +343,22 @@ __device__ __forceinline__ void write_obs(const ChubParams &P, int h, const Chub
     for (int j = 0; j < CHUB_OBS_DIM; ++j) o[j] = 0.0f;
     int k = 0;
     o[k++] = (float) kC.time_sin[t];
-    o[k++] = (float) ((pr - kC.price_mean) / kC.price_std);
+    o[k++] = (float) chub_div_const(pr - kC.price_mean, kC.price_std, kC.r_price_std);
     if (c.n[0] > 0) {
-        o[k++] = (float) (((double) s0.mn - c.half[0]) / c.half[0]);
-        o[k++] = (float) (((double) s0.now - c.half[0]) / c.half[0]);
-        o[k++] = (float) (((double) s0.mx - c.half[0]) / c.half[0]);
-        o[k++] = (float) ((double) s0.line / 5.0);
+        o[k++] = (float) chub_div_const((double) s0.mn - c.half[0], c.half[0], c.r_half[0]);
+        o[k++] = (float) chub_div_const((double) s0.now - c.half[0], c.half[0], c.r_half[0]);
+        o[k++] = (float) chub_div_const((double) s0.mx - c.half[0], c.half[0], c.r_half[0]);
+        o[k++] = (float) DIVC((double) s0.line, 5.0);
     }
     if (c.n[1] > 0) {
-        o[k++] = (float) (((double) s1.mn - c.half[1]) / c.half[1]);
-        o[k++] = (float) (((double) s1.now - c.half[1]) / c.half[1]);
-        o[k++] = (float) (((double) s1.mx - c.half[1]) / c.half[1]);
-        o[k++] = (float) ((double) s1.line / 5.0);
+        o[k++] = (float) chub_div_const((double) s1.mn - c.half[1], c.half[1], c.r_half[1]);
+        o[k++] = (float) chub_div_const((double) s1.now - c.half[1], c.half[1], c.r_half[1]);
+        o[k++] = (float) chub_div_const((double) s1.mx - c.half[1], c.half[1], c.r_half[1]);
+        o[k++] = (float) DIVC((double) s1.line, 5.0);
     }
     o[k++] = (float) store_soc;
-    o[k++] = (float) (pv / 210.0);
-    o[k++] = (float) (wd / 92.0);
+    o[k++] = (float) DIVC(pv, 210.0);
+    o[k++] = (float) DIVC(wd, 92.0);
     float *dst = P.obs + (size_t) h * CHUB_OBS_DIM;
 #pragma unroll
     for (int j = 0; j < CHUB_OBS_DIM; ++j) dst[j] = o[j];
@@ -513,7 +516,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) chub_step_kernel(const __grid_con
     const double must = py_max(0.0, c.cap_mass * 0.1 - v.store);
     const double upper = py_max(c.cap_mass - v.store, 0.0);
     const double charge_temp = py_max(py_min(act * c.v_h_max * 900.0, upper), must);
-    double flow = charge_temp / 900.0;
+    double flow = DIVC(charge_temp, 900.0);
     flow = py_min(flow, c.v_h_max);
     const double ele_kw = el_power(c, flow);
     const double cpr_kw = cpr_power(c, flow);
@@ -525,7 +528,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) chub_step_kernel(const __grid_con
     const double not_meet = demand - hy_use;
     v.store -= hy_use;
     v.store -= v.store * c.loss;
-    double store_soc = v.store / c.cap_mass;
+    double store_soc = chub_div_const(v.store, c.cap_mass, c.r_cap_mass);
     const double h2_kw = ele_kw + cpr_kw;
     const bool gen_hy = flow > 0.5;
 
@@ -537,7 +540,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) chub_step_kernel(const __grid_con
         ev_sum = py_max(0.0, ev_sum - renew);
         const double s = 0.0 + l0 + l1;
         if (s > 0.0) {
-            const double rate = ev_sum / s;
+            const double rate = chub_div(ev_sum, s);
             l0 = rate * l0;
             l1 = rate * l1;
         }
@@ -549,7 +552,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) chub_step_kernel(const __grid_con
     if (fc > c.fc_cells) fc = c.fc_cells;
     else if (fc < 0.0) fc = 0.0;
     else if (fc > ev_sum) fc = ev_sum;
-    double hy_fc = fc * 1500.0 / 119.6;
+    double hy_fc = DIVC(fc * 1500.0, 119.6);
     hy_fc = py_min(v.store, hy_fc);
     v.store -= hy_fc;
     const double fc_kw = py_max(0.0, fc);
@@ -557,14 +560,14 @@ __global__ void __launch_bounds__(BLOCK, MINB) chub_step_kernel(const __grid_con
     {
         const double s = 0.0 + l0 + l1;
         if (s > 0.0) {
-            const double rate = ev_sum / s;
+            const double rate = chub_div(ev_sum, s);
             l0 = rate * l0;
             l1 = rate * l1;
         }
     }
     // ---- income and reward (evcssp_manager.py:234-269) ----
     const double hy_loss = -6.0 / 1000.0 * hy_fc;
-    const double p4 = pr_t / 4.0;
+    const double p4 = pr_t * 0.25;
     const double inc_fast = 0.42 / 4.0 * cp0 - p4 * l0;
     const double inc_slow = 0.21 / 4.0 * cp1 - p4 * l1;
     const double inc_evs = inc_fast + inc_slow;
@@ -573,7 +576,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) chub_step_kernel(const __grid_con
     const double nm_loss = -10.0 / 1000.0 * not_meet;
     const double hy_cost = -p4 * h2_grid;
     const double income = inc_hys + inc_evs + serve + hy_cost;
-    const double reward = (inc_hys + inc_evs + serve + hy_cost + 1.0 * hy_loss + nm_loss) / 50.0;
+    const double reward = DIVC(inc_hys + inc_evs + serve + hy_cost + 1.0 * hy_loss + nm_loss, 50.0);
     const bool done = v.t + 1 >= CHUB_DAY;
     v.t = (v.t + 1) % CHUB_DAY;
 

@@ -45,6 +45,14 @@ int main(int argc, char **argv) {
         double num = 100.0 * U(g);
         bad_div += chub_div_const(num, 19.285746346634653, 1.0 / 19.285746346634653) != num / 19.285746346634653;
         bad_div += chub_div_const(num, 26.10760370438271, 1.0 / 26.10760370438271) != num / 26.10760370438271;
+        // every literal / class divisor the hub section uses (csrc/chub_kernels.cu DIVC / chub_div_const)
+        static const double DS[] = {900.0, 2.02, 1000.0, 0.8, 119.6, 50.0, 5.0, 210.0, 92.0, 18.5, 70.0,
+                                    179440.0, 771589.0, 24.436 * 1000 * 60, 445000.0, 178000.0, 89000000.0,
+                                    364.47637939453125, 65.687164306640625, 0.05334155497008051};
+        {
+            double big = std::ldexp(U(g), (int) (40 * U(g)) - 10);
+            for (double Dv : DS) bad_div += chub_div_const(big, Dv, 1.0 / Dv) != big / Dv;
+        }
         double den = 0.5 + 40 * U(g);
         bad_div += chub_div(num, den) != num / den;
     }
