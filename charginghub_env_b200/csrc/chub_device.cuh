@@ -60,6 +60,7 @@ __device__ ChubLogEntry kLogTab[CHUB_LOG_N];  // reduction table of chub_log (gl
 
 // ---------------------------------------------------------------------------------------------
 // per-hub random streams (include/chub_rng.h)
+// @region rng/normals
 struct HubRng {
     uint32_t k0, k1, uctr, lcg;
 };
@@ -88,6 +89,20 @@ __device__ __forceinline__ double canon_d(uint32_t &lcg) {
     double q0 = sum * rD;
     double ret = fma(fma(-q0, D, sum), rD, q0);
     if (ret >= 1.0) ret = 0.99999999999999988898;
+    return ret;
+}
+// the same two, from states already drawn (the step kernel's add_car chain computes the states in parallel)
+__device__ __forceinline__ double canon_d_of(uint32_t s1, uint32_t s2) {
+    const double sum = (double) (s1 - 1u) + (double) (s2 - 1u) * 2147483646.0;
+    const double D = 4611686009837453312.0, rD = 1.0 / 4611686009837453312.0;
+    const double q0 = sum * rD;
+    double ret = fma(fma(-q0, D, sum), rD, q0);
+    if (ret >= 1.0) ret = 0.99999999999999988898;
+    return ret;
+}
+__device__ __forceinline__ float canon_f_of(uint32_t s1) {
+    float ret = (float) (s1 - 1u) * 4.656612873077392578125e-10f;
+    if (ret >= 1.0f) ret = 0.99999994f;
     return ret;
 }
 // generate_canonical<float,24>: one draw, divisor float(2147483646) = 2^31
@@ -150,6 +165,7 @@ __device__ __forceinline__ int rng_init_cars(HubRng &r, int mu) {  // CHS.hpp:83
 // ---------------------------------------------------------------------------------------------
 // charging curves.  Time unit = one 15-minute step.  fp32 in/out, fp64 inside.
 
+// @region slow curves
 // --- slow charger (CHS.hpp:495-588) ---
 __device__ __forceinline__ float slow_s2t(float s) {
     if (s < 0.0f) return 0.0f;
@@ -163,28 +179,27 @@ __device__ __forceinline__ float slow_s2t(float s) {
     }
     return 14.68f;
 }
-// time -> (soc, power) in one go: car_step needs both at the same time (CHS.hpp:901-905)
+// time -> (soc, power) in one go: car_step needs both at the same time (CHS.hpp:901-905).
+// The argument is always s2t(soc) + 1 >= 1, and the curve's breakpoints (2.33*4, 3.67*4 as doubles) are
+// not fp32 values, so "<" and "<=" select the same side and one segment index decides both outputs:
+//   SEG 0: t < 2.33*4 (quartics)      SEG 1: otherwise (log / rational, or the flat tail past 3.67*4)
+// The caller sorts piles by segment so that a warp runs ONE of the two bodies, not both.
+__device__ __forceinline__ int slow_seg(float t) { return (double) t < 2.33 * 4 ? 0 : 1; }
+template <int SEG>
 __device__ __forceinline__ void slow_step(float t, float &soc, float &power) {
-    double y = (double) (t * 0.25f);  // charge_time / 4 is exact in fp32
-    double td = (double) t;
+    const double y = (double) (t * 0.25f);  // charge_time / 4 is exact in fp32
     float ch;
-    if (td <= 0.0) {
-        ch = 0.0f;
-    } else if (td <= 2.33 * 4) {
+    if (SEG == 0) {
         ch = (float) (y * fma(fma(fma(fma(-0.0004112, y, 0.0023025), y, 0.03562 / 3), y, 0.011895), y, 6.007));
-    } else if (td <= 3.67 * 4) {
-        ch = (float) (-4.041 * y + 19.140115 * chub_log(fabs(y - 0.485), kLogTab) + 11.943306312699628);
-    } else {
-        ch = kC.slow_c2_end;
-    }
-    soc = (float) chub_div_const((double) (100.0f * ch), 19.285746346634653, 1.0 / 19.285746346634653);
-    if (td < 2.33 * 4) {
         power = (float) fma(fma(fma(fma(-0.002056, y, 0.00921), y, 0.03562), y, 0.02379), y, 6.007);
-    } else if (td < 3.67 * 4) {
+    } else if ((double) t <= 3.67 * 4) {
+        ch = (float) (-4.041 * y + 19.140115 * chub_log(fabs(y - 0.485), kLogTab) + 11.943306312699628);
         power = (float) chub_div(-4.041 * y + 21.1, y - 0.485);
     } else {
+        ch = kC.slow_c2_end;
         power = 0.0f;
     }
+    soc = (float) chub_div_const((double) (100.0f * ch), 19.285746346634653, 1.0 / 19.285746346634653);
 }
 __device__ __forceinline__ float slow_t2p(float t) {
     double y = (double) (t * 0.25f), td = (double) t;
@@ -193,6 +208,7 @@ __device__ __forceinline__ float slow_t2p(float t) {
     return 0.0f;
 }
 
+// @region fast curves
 // --- fast charger (CHS.hpp:621-725) ---
 __device__ __forceinline__ float fast_s2t(float s) {
     if (s <= 0.0f) return 0.0f;
@@ -209,27 +225,21 @@ __device__ __forceinline__ float fast_aa2(double x) {
     double p = x * fma(fma(fma(fma(0.0002253 / 5, x, -(0.03572 / 4)), x, 2.016 / 3), x, -(48.76 / 2)), x, 457.7);
     return (float) (p + (double) kC.fast_aa2_c);
 }
+// SEG 0: t < 28.7/15 (exponential part)   SEG 1: otherwise (polynomial part, or full past 51.2/15); t >= 1
+__device__ __forceinline__ int fast_seg(float t) { return (double) t < 28.7 / 15 ? 0 : 1; }
+template <int SEG>
 __device__ __forceinline__ void fast_step(float t, float &soc, float &power) {
-    float xf = t * 15.0f;
-    double x = (double) xf, td = (double) t;
-    double ex = 0.0;
-    if (td > 0.0 && td <= 28.7 / 15) ex = chub_exp(0.053 * x);
-    if (td <= 0.0) {
-        soc = 0.0f;
-    } else if (td <= 28.7 / 15) {
-        float a1 = (float) ((0.7194 / 0.053) * ex + 50.15 * x - (double) kC.fast_aa1_c);
+    const double x = (double) (t * 15.0f);
+    if (SEG == 0) {
+        const double ex = chub_exp(0.053 * x);
+        const float a1 = (float) ((0.7194 / 0.053) * ex + 50.15 * x - (double) kC.fast_aa1_c);
         soc = a1 * kC.fast_scale;
-    } else if (td <= 51.2 / 15) {
-        soc = fast_aa2(x) * kC.fast_scale;
-    } else {
-        soc = 100.0f;
-    }
-    if (td >= 0.0 && td < 28.7 / 15) {
-        if (td <= 0.0) ex = chub_exp(0.053 * x);
         power = (float) (0.7194 * ex + 47.78);
-    } else if (td >= 0.0 && td < 51.2 / 15) {
+    } else if ((double) t < 51.2 / 15) {
+        soc = fast_aa2(x) * kC.fast_scale;
         power = (float) fma(fma(fma(fma(0.0002253, x, -0.03572), x, 2.016), x, -48.76), x, 457.7);
     } else {
+        soc = 100.0f;
         power = 0.0f;
     }
 }
@@ -240,6 +250,7 @@ __device__ __forceinline__ float fast_t2p(float t) {
     return 0.0f;
 }
 
+// @region const/dispatch
 // --- constant-power variants (CHS.hpp:496-501, 514-521, 528-535, 622-627, 640-647, 662-669) ---
 __device__ __forceinline__ float const_s2t(float s, double tmax) {
     if (s <= 0.0f) return 0.0f;
@@ -265,14 +276,19 @@ __device__ __forceinline__ float curve_s2t(float s) {
     return TYPE == CHUB_SLOW ? slow_s2t(s) : fast_s2t(s);
 }
 template <int TYPE, int CP>
+__device__ __forceinline__ int curve_seg(float t) {
+    if (CP) return 0;
+    return TYPE == CHUB_SLOW ? slow_seg(t) : fast_seg(t);
+}
+template <int TYPE, int CP, int SEG>
 __device__ __forceinline__ void curve_step(float t, float &soc, float &power) {
     if (CP) {
         const_step(t, TYPE == CHUB_SLOW ? CHUB_SLOW_TMAX : CHUB_FAST_TMAX,
                    TYPE == CHUB_SLOW ? CHUB_SLOW_PCONST : CHUB_FAST_PCONST, soc, power);
     } else if (TYPE == CHUB_SLOW) {
-        slow_step(t, soc, power);
+        slow_step<SEG>(t, soc, power);
     } else {
-        fast_step(t, soc, power);
+        fast_step<SEG>(t, soc, power);
     }
 }
 template <int TYPE, int CP>

@@ -395,8 +395,8 @@ static int fill_params(chub_engine *e, ChubParams &P) {
     P.step_offset = 0; P.step_index = e->step_index;
     {   // experiment knobs (defaults are the measured best)
         const char *b = getenv("CHUB_BLOCK"), *y = getenv("CHUB_PHASE_SYNC");
-        P.block = b ? atoi(b) : 51202;
-        P.phase_sync = y ? atoi(y) : 0;
+        P.block = b ? atoi(b) : 0;
+        P.phase_sync = y ? atoi(y) : 1;
     }
     P.pile = e->pile; P.arrive = e->arrive; P.hubA = e->hubA; P.store = e->store; P.keys = e->keys; P.cls = e->cls;
     P.stats = e->stats; P.last_stats = e->last_stats; P.err = e->err; P.qsoc = e->qsoc;
@@ -433,7 +433,7 @@ extern "C" int chub_step(chub_engine *e, const float *actions_dev, void *stream)
     if (rc) return rc;
     P.actions = actions_dev;
     cudaStream_t s = (cudaStream_t) stream;
-    chub_launch_step(P, s);
+    CK(chub_launch_step(P, s));
     chub_launch_tick(e->step_index, 1, s);
     CK(cudaGetLastError());
     e->launches += 1;
@@ -608,7 +608,7 @@ extern "C" int chub_get_field(chub_engine *e, int32_t field, void *host_out) {
                     uint4 r = make_uint4(0, 0, 0, 0);
                     float arr = 0.f;
                     if (i < c.n[s]) {
-                        const size_t idx = (size_t) ((s ? e->S0 : 0) + i) * Hp + h;
+                        const size_t idx = chub_pile_index(h, (s ? e->S0 : 0) + i, e->S0 + e->S1);
                         r = pile[idx];
                         arr = arrive[idx];
                     }
@@ -667,7 +667,7 @@ extern "C" int chub_get_field(chub_engine *e, int32_t field, void *host_out) {
                 for (int s = 0; s < 2; ++s) {
                     int cnt = 0;
                     for (int i = 0; i < c.n[s]; ++i)
-                        cnt += (pile[(size_t) ((s ? e->S0 : 0) + i) * Hp + h].w & PW_CAR) ? 1 : 0;
+                        cnt += (pile[chub_pile_index(h, (s ? e->S0 : 0) + i, e->S0 + e->S1)].w & PW_CAR) ? 1 : 0;
                     oi[2 * h + s] = cnt;
                 }
                 break;

@@ -36,6 +36,7 @@ CHUB_FM double chub_u2d(uint64_t u) {
 #endif
 }
 
+// @region chub_log
 // log(x) for positive normal x.  Table-driven reduction (128 subintervals of [0.6875, 1.375)),
 // r = z*invc - 1 with |r| < 0.004, then log1p(r) by a degree-6 Taylor polynomial.
 CHUB_FM double chub_log(double x, const ChubLogEntry *tab) {
@@ -56,6 +57,7 @@ CHUB_FM double chub_log(double x, const ChubLogEntry *tab) {
     return hi + fma(r2, p, lo);
 }
 
+// @region chub_exp
 // exp(a) for |a| < 700 (no overflow / underflow handling).
 CHUB_FM double chub_exp(double a) {
     const double kd = rint(a * 0x1.71547652b82fep+0);  // a / ln2
@@ -79,6 +81,7 @@ CHUB_FM double chub_exp(double a) {
     return chub_u2d(chub_d2u(p) + ((uint64_t) k << 52));  // p * 2^k
 }
 
+// @region chub_div
 // n / d for normal operands whose quotient is normal: reciprocal by Newton from a hardware seed,
 // then one fma residual correction (Markstein).
 CHUB_FM double chub_div(double n, double d) {

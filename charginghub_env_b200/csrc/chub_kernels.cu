@@ -21,6 +21,7 @@ cudaError_t chub_upload_const(const ChubConst &c) {
     return cudaMemcpyToSymbol(kC, &c, sizeof(ChubConst));
 }
 
+// @region misc
 struct StationOut {
     float mn, mx, now;  // min_power, max_power, charge_power (CHS.hpp:1257-1259)
     int number;         // car_number
@@ -33,110 +34,256 @@ __device__ __forceinline__ float target_of(uint32_t tu) {  // uniform_rand(80, 1
     return (float) tu / 999.0f * 20.0f + 80.0f;
 }
 
-// One EV station of one hub.  RESET = false: evs_step(vector) (CHS.hpp:1188-1207 / 1499-1518);
-// RESET = true: evs_reset (CHS.hpp:1209-1231 / 1520-1542).
-//
-// Work is split so that the lanes of a warp (32 different hubs) execute the expensive code together:
-//   scan   : ascending read of the packed words only -> bit masks (occupied, charging, departing)
-//   loop A : each lane walks ITS OWN charging piles (car_step + urgency)            -- convergent fp64
-//   loop B : each lane walks ITS OWN newly assigned piles in ascending order (add_car, serial RNG)
-//   pass C : ascending coalesced sweep: non-charging bookkeeping (remove_car) and the station sums in
-//            the reference's fp32 summation order (calculate_output)
-// "First k empty piles" (assign_car / find_empty, CHS.hpp:417-451) is bit arithmetic on the occupancy mask.
-template <bool RESET, int TYPE, int CP>
-__device__ __forceinline__ StationOut station_pass(const ChubParams &P, int h, int slot0, int n, int t, int line,
-                                                   uint32_t act_bits, HubRng &rng, uint32_t &err) {
+// evs_reset of one EV station of one hub (CHS.hpp:1209-1231 / 1520-1542), one thread per hub: draw the
+// initial car count, fill the first piles in ascending order (add_car, serial E/U/E draws per car), clear the
+// rest, and form the station sums.  Runs once per hub per episode (reset kernel, fused auto-reset).
+// @region station_reset
+template <int TYPE, int CP>
+__device__ __forceinline__ StationOut station_reset(const ChubParams &P, int h, int slot0, int n, HubRng &rng,
+                                                    uint32_t &err) {
     StationOut o;
     o.incomplete = 0;
-    // ---- station-level draws of receive_car (CHS.hpp:1272-1306), before any per-car draw ----
-    int in_car;
-    if (RESET) {
-        in_car = rng_init_cars(rng, n / 2);
-        line = 0;
-    } else {
-        int N = (int) __ldg(&P.lut[t * 1000 + rng_u1000(rng)]);
-        in_car = (int) roundf((TYPE == CHUB_FAST ? 0.15f : 0.1f) * 0.2f * (float) N);
-    }
-    int kept = 0;
-    for (int w = 0; w < line; ++w) {  // reneging: keep if u > 0.1*logf(w+1)
-        float a = rng_u01(rng);
-        if (a > kC.renege[w]) kept += 1;
-    }
-    line = kept;
+    const int in_car = rng_init_cars(rng, n / 2);
     int true_in = 0;
-    for (int k = 0; k < in_car; ++k) {  // balking: stay if u <= expf(-0.01*(line+k)) and k <= n
+    for (int k = 0; k < in_car; ++k) {  // balking against an empty line (CHS.hpp:1294-1304)
         float a = rng_u01(rng);
-        if (a <= kC.balk[min(line + k, 63)] && k <= n) true_in += 1;
+        if (a <= kC.balk[min(k, 63)] && k <= n) true_in += 1;
     }
     o.flow = (TYPE == CHUB_SLOW) ? true_in : in_car;  // the slow/fast asymmetry, CHS.hpp:1306 vs 1617
-    const int want = line + o.flow;
+    const int assigned = min(o.flow, n);
+    o.line = min(o.flow - assigned, 10);
+    const size_t at0 = chub_pile_index(h, slot0, P.S0 + P.S1);
+    uint4 *row = P.pile + at0;
+    const size_t ld = 32;
+    const float *tlut = P.s2t_lut + (CP * 2 + TYPE) * 1000;
+    float mx = 0.0f, mn = 0.0f;
+    for (int i = 0; i < n; ++i) {
+        if (i >= assigned) {
+            row[i * ld] = make_uint4(0u, 0u, 0u, 0u);
+            continue;
+        }
+        const float arrive = rng_mk_soc(rng);                 // E
+        const uint32_t tu = (uint32_t) rng_u1000(rng);        // U  (target = u/999*20+80)
+        const float tsoc = curve_s2t<TYPE, CP>(arrive);
+        const float needed = __ldg(&tlut[tu]) - tsoc;
+        const int must_needed = (int) ceilf(needed);          // calculate_min_charging_time
+        int stay = must_needed + rng_late_time(rng);          // E
+        const float power = curve_t2p<TYPE, CP>(tsoc);
+        int cn = needed > 0.0f ? must_needed : 0;
+        if (stay > 63 || stay < 1 || cn > 31) {
+            err |= CHUB_HUBERR_COUNTER;
+            stay = min(max(stay, 1), 63);
+            cn = min(cn, 31);
+        }
+        const bool urgent = cn > 0 && stay <= cn;
+        row[i * ld] = make_uint4(__float_as_uint(arrive), __float_as_uint(tsoc), __float_as_uint(power),
+                                 (uint32_t) stay | PW_CAR | (urgent ? PW_URGENT : 0u) | ((uint32_t) cn << 15) | (tu << 20));
+        P.arrive[at0 + (size_t) i * ld] = arrive;
+        mx += power;
+        if (urgent) mn += power;
+    }
+    o.mn = mn; o.mx = mx; o.now = 0.0f; o.number = max(assigned, 0);
+    return o;
+}
 
-    uint4 *row = P.pile + (size_t) slot0 * P.Hpad + h;
-    const size_t ld = (size_t) P.Hpad;
-    const float *tlut = P.s2t_lut + (CP * 2 + TYPE) * 1000;  // s2t(target) for the 1000 possible targets
-    const uint32_t nmask = n >= 32 ? 0xffffffffu : ((1u << n) - 1u);
+__device__ __forceinline__ StationOut station_reset_any(const ChubParams &P, int h, int slot0, int n, int type, int cp,
+                                                        HubRng &rng, uint32_t &err) {
+    if (cp) {  // constant-power charging (constant_charging=True)
+        if (type == CHUB_SLOW) return station_reset<CHUB_SLOW, 1>(P, h, slot0, n, rng, err);
+        return station_reset<CHUB_FAST, 1>(P, h, slot0, n, rng, err);
+    }
+    if (type == CHUB_SLOW) return station_reset<CHUB_SLOW, 0>(P, h, slot0, n, rng, err);
+    return station_reset<CHUB_FAST, 0>(P, h, slot0, n, rng, err);
+}
 
-    // ---- scan ----
+// ---------------------------------------------------------------------------------------------
+// evs_step(vector) of one EV station (CHS.hpp:1188-1207 / 1499-1518) for the 32 hubs of a warp.
+//
+// A thread owns a hub, but the expensive per-car arithmetic is NOT done hub by hub: the number of
+// charging piles and of arriving cars differs from hub to hub, and a per-lane loop leaves most lanes
+// idle while the busiest hub finishes (measured: 18 of 32 lanes active).  Instead the warp pools the
+// work of its 32 hubs in shared memory and runs it 32 items at a time:
+//   scan     : lanes = hubs, ascending coalesced read of the pile rows.  Non-charging cars are finished on
+//              the spot (remove_car bookkeeping); charging piles are appended to one of two work lists,
+//              by the curve segment their new charge time falls in, so a batch runs ONE curve body.
+//   flat A   : whenever a list holds 32 items the warp executes car_step + urgency for them
+//              (lanes = piles of any hub), writes the pile records and posts power / urgency to the owner.
+//   chain    : the serial part of add_car -- only the minstd accept/reject walk of the two polar normals
+//              per car (the variates' values never influence how many draws are consumed) -- as a
+//              per-lane state machine, one ATTEMPT per iteration, recording the minstd state each accepted
+//              attempt started from.  The double-precision attempt is decided from an fp32 estimate of r2
+//              (exact evaluation only inside a +-4e-6 band around the accept boundary).
+//   flat B   : the variates themselves (log/sqrt), curves and record packing of the new cars, lanes = new cars
+//              of any hub.
+//   sums     : each owner adds its piles' power in the reference's ascending fp32 order (calculate_output).
+// Per-warp scratch lives in shared memory (WarpScratch); warps never synchronise with each other.
+// @region scratch
+#define LA_RING 64    // >= 31 waiting + 32 appended per scanned row; a batch is up to 32 items
+template <int Q>
+struct WarpScratch {
+    float am[2][32];                  // the two analog action entries of each hub, parked here during the stations
+    // ---- everything below doubles as the staging area of the warp's action rows ----
+    uint32_t inc_s[32];               // posted to the owner lane: incomplete departures found by a car_step batch
+    uint32_t la_t[2][LA_RING], la_w[2][LA_RING], la_id[2][LA_RING];  // car_step rings per curve segment: new charge time
+                                      // (f32 bits), packed pile word, lane | pile << 5
+    uint32_t pw[1][32];               // [pile][lane], max(S0, S1) rows in fact: power (f32 bits, >= 0) of the car now on that
+                                      // pile; sign bit = urgent
+};
+template <int Q>
+static size_t warp_scratch_bytes(int rows) { return offsetof(WarpScratch<Q>, pw) + (size_t) rows * 128; }
+#define PWB_URGENT 0x80000000u
+
+// @region flat A shell (car_step batch)
+template <int TYPE, int CP, int SEG, int Q>
+__device__ __forceinline__ void flat_car_step(const ChubParams &P, WarpScratch<Q> &S, const float *tlut, uint4 *pile0,
+                                              int head, int count) {
+    const int lane = threadIdx.x & 31;
+    __syncwarp();
+    if (lane < count) {
+        const int sl = (head + lane) & (LA_RING - 1);
+        const float tt = __uint_as_float(S.la_t[SEG][sl]);
+        const uint32_t w = S.la_w[SEG][sl];
+        const uint32_t id = S.la_id[SEG][sl], owner = id & 31u, i = id >> 5;
+        float soc, power;
+        curve_step<TYPE, CP, SEG>(tt, soc, power);            // car_step, CHS.hpp:900-905 / 1065-1070
+        const float tsoc = curve_s2t<TYPE, CP>(soc);
+        const uint32_t tu = PW_TU(w);
+        const float needed = __ldg(&tlut[tu]) - tsoc;         // calculate_needed, CHS.hpp:879-898
+        const int cn = needed > 0.0f ? (int) ceilf(needed) : 0;
+        const int left = (int) PW_STAY(w) - (int) PW_ALREADY(w) - 1;
+        uint4 r = make_uint4(0u, 0u, 0u, 0u);
+        if (left <= 0) {                                      // remove_car, CHS.hpp:912-930
+            if (ceilf(soc) < floorf(target_of(tu))) atomicAdd(&S.inc_s[owner], 1u);
+        } else {
+            const uint32_t urgent = (cn > 0 && left <= cn) ? 1u : 0u;
+            r = make_uint4(__float_as_uint(soc), __float_as_uint(tsoc), __float_as_uint(power),
+                           ((w + (1u << 6)) & 0xfffu) | PW_CAR | PW_CHARGE | (urgent << 14) | ((uint32_t) cn << 15) |
+                               (w & (0x3ffu << 20)));
+            (&S.pw[0][0])[i * 32u + owner] = __float_as_uint(power) | (urgent << 31);
+        }
+        pile0[i * 32u + owner] = r;
+    }
+    __syncwarp();
+}
+
+// All 32 lanes call this together.  `mine` = this lane's hub has a station of this (TYPE, CP) at this
+// position; the other lanes own no piles here but still work on the pooled items.
+// @region station prologue + receive_car draws
+template <int TYPE, int CP, int Q>
+__device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q> &S, const float *tl_s, bool mine, int h,
+                                          int slot0, int n_in, int t, int line_in, uint32_t act_bits, HubRng &rng,
+                                          uint32_t &err, StationOut &o) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int h0 = h - lane;
+    const int n = mine ? n_in : 0;
+    const float *tlut = P.s2t_lut + (CP * 2 + TYPE) * 1000;   // 4 KB, L1 resident
+    (void) tl_s;
+    S.inc_s[lane] = 0u;
+
+    // ---- station-level draws of receive_car (CHS.hpp:1272-1306), before any per-car draw ----
+    int want = 0, flow = 0;
+    if (mine) {
+        const int N = (int) __ldg(&P.lut[t * 1000 + rng_u1000(rng)]);
+        const int in_car = (int) roundf((TYPE == CHUB_FAST ? 0.15f : 0.1f) * 0.2f * (float) N);
+        int kept = 0;
+        for (int w = 0; w < line_in; ++w) {  // reneging: keep if u > 0.1*logf(w+1)
+            if (rng_u01(rng) > kC.renege[w]) kept += 1;
+        }
+        int true_in = 0;
+        for (int k = 0; k < in_car; ++k) {   // balking: stay if u <= expf(-0.01*(line+k)) and k <= n
+            if (rng_u01(rng) <= kC.balk[min(kept + k, 63)] && k <= n) true_in += 1;
+        }
+        flow = (TYPE == CHUB_SLOW) ? true_in : in_car;  // the slow/fast asymmetry, CHS.hpp:1306 vs 1617
+        want = kept + flow;
+    }
+    __syncwarp();
+
+// @region scan
+    // ---- scan + flat A ----
+    // Charging power is never negative (curves and constants, tests/test_host_logic.py), so the sign bit of the
+    // posted power carries the pile's urgency to the owner's summation.
+    const size_t tile0 = chub_pile_index(h0, slot0, P.S0 + P.S1);
+    uint4 *const pile0 = P.pile + tile0;             // the warp's tile of this station: [pile][32 hubs], contiguous
+    const int ld = 32;
+    const uint32_t lt = (1u << lane) - 1u;
     uint32_t car_mask = 0u, chg_mask = 0u, dep_mask = 0u;
-    if (!RESET) {
-#pragma unroll 4
-        for (int i = 0; i < n; ++i) {
-            const uint32_t w = row[i * ld].w;
-            const uint32_t bit = 1u << i;
-            if (w & PW_CAR) {
-                car_mask |= bit;
-                // judge_feasibility + assign_on_off_piece (CHS.hpp:1404-1413, 1364-1373)
-                if ((w & PW_URGENT) || (act_bits & bit)) chg_mask |= bit;
-                if ((int) PW_STAY(w) - ((int) PW_ALREADY(w) + 1) <= 0) dep_mask |= bit;  // remove_car
+    int incomplete = 0;
+    int tail0 = 0, tail1 = 0, head0 = 0, head1 = 0;  // warp-uniform ring positions (taken mod LA_RING); count = tail - head
+    const int nmax = __reduce_max_sync(full, n);
+    uint4 *rp = pile0 + lane;                        // walks down the rows
+    uint32_t *pwp = &S.pw[0][lane];
+    uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
+    if (0 < n) nxt = *rp;
+    for (int i = 0; i <= nmax; ++i, rp += ld, pwp += 32) {   // one extra turn flushes the rings
+        const uint4 r = nxt;
+        if (i + 1 < n) nxt = rp[ld];
+        int seg = -1;
+        float tt = 0.0f;
+        const uint32_t w = r.w, bit = 1u << (i & 31);
+        if (i < n && (w & PW_CAR)) {
+            car_mask |= bit;
+            const int left = (int) PW_STAY(w) - (int) PW_ALREADY(w) - 1;
+            if (left <= 0) dep_mask |= bit;
+            // judge_feasibility + assign_on_off_piece (CHS.hpp:1404-1413, 1364-1373)
+            if ((w & PW_URGENT) || (act_bits & bit)) {
+                chg_mask |= bit;
+                tt = __uint_as_float(r.y) + 1.0f;
+                seg = curve_seg<TYPE, CP>(tt);
+            } else if (left <= 0) {                            // remove_car of a car that is not charging
+                if (ceilf(__uint_as_float(r.x)) < floorf(target_of(PW_TU(w)))) incomplete += 1;
+                *rp = make_uint4(0u, 0u, 0u, 0u);
+            } else {
+                const int cn = PW_CN(w);
+                const uint32_t urgent = (cn > 0 && left <= cn) ? 1u : 0u;
+                rp->w = ((w & ~(PW_CHARGE | PW_URGENT)) + (1u << 6)) | (urgent << 14);
+                *pwp = r.z | (urgent << 31);
             }
         }
+        const uint32_t m0 = __ballot_sync(full, seg == 0), m1 = CP ? 0u : __ballot_sync(full, seg == 1);
+        if ((m0 | m1) == 0u && i != nmax) continue;   // nobody charges on this row: nothing to queue, nothing became due
+        if (seg >= 0) {
+            const int sl = seg * LA_RING + ((seg == 0 ? tail0 + __popc(m0 & lt) : tail1 + __popc(m1 & lt)) & (LA_RING - 1));
+            (&S.la_t[0][0])[sl] = __float_as_uint(tt);
+            (&S.la_w[0][0])[sl] = w;
+            (&S.la_id[0][0])[sl] = (uint32_t) lane | ((uint32_t) i << 5);
+        }
+        tail0 += __popc(m0);
+        tail1 += __popc(m1);
+        const int need = i == nmax ? 1 : 32;
+        if (tail0 - head0 >= need) {
+            const int c = min(tail0 - head0, 32);
+            flat_car_step<TYPE, CP, 0, Q>(P, S, tlut, pile0, head0, c);
+            head0 += c;
+        }
+        if (!CP && tail1 - head1 >= need) {
+            const int c = min(tail1 - head1, 32);
+            flat_car_step<TYPE, CP, 1, Q>(P, S, tlut, pile0, head1, c);
+            head1 += c;
+        }
     }
+
+// @region assign_car
+    // ---- assign_car, wait == true (CHS.hpp:417-451): the first `assigned` empty piles, ascending ----
+    const uint32_t nmask = n >= 32 ? 0xffffffffu : ((1u << n) - 1u);
     const uint32_t occ_after = car_mask & ~dep_mask;
     const int empties = n - __popc(occ_after);
-    const int assigned = min(want, empties);  // assign_car, wait == true (CHS.hpp:417-430); may be negative
-    o.line = min(want - assigned, 10);
+    const int assigned = min(want, empties);  // may be negative
     uint32_t add_mask = 0u;
     {
         uint32_t freeb = ~occ_after & nmask;
-        for (int k = 0; k < assigned; ++k) {  // the first `assigned` empty piles, ascending
-            uint32_t b = freeb & (0u - freeb);
+        for (int k = 0; k < assigned; ++k) {
+            const uint32_t b = freeb & (0u - freeb);
             add_mask |= b;
             freeb ^= b;
         }
     }
 
-    // ---- loop A: car_step for this hub's charging piles (CHS.hpp:900-905 / 1065-1070) ----
-    if (!RESET) {
-        uint32_t m = chg_mask;
-        uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
-        if (m) nxt = row[(__ffs(m) - 1) * ld];
-        while (m) {
-            const int i = __ffs(m) - 1;
-            m &= m - 1u;
-            uint4 r = nxt;
-            if (m) nxt = row[(__ffs(m) - 1) * ld];  // prefetch this lane's next charging pile
-            const uint32_t w = r.w;
-            float soc, power;
-            curve_step<TYPE, CP>(__uint_as_float(r.y) + 1.0f, soc, power);
-            const float tsoc = curve_s2t<TYPE, CP>(soc);
-            const uint32_t tu = PW_TU(w);
-            const float needed = __ldg(&tlut[tu]) - tsoc;
-            const int cn = needed > 0.0f ? (int) ceilf(needed) : 0;
-            const int stay = PW_STAY(w), already = PW_ALREADY(w) + 1;
-            if (stay - already <= 0) {
-                if (ceilf(soc) < floorf(target_of(tu))) o.incomplete += 1;
-                r = make_uint4(0u, 0u, 0u, 0u);
-            } else {
-                const bool urgent = cn > 0 && (stay - already) <= cn;
-                r = make_uint4(__float_as_uint(soc), __float_as_uint(tsoc), __float_as_uint(power),
-                               (uint32_t) stay | ((uint32_t) already << 6) | PW_CAR | PW_CHARGE |
-                                   (urgent ? PW_URGENT : 0u) | ((uint32_t) cn << 15) | (tu << 20));
-            }
-            row[i * ld] = r;
-        }
-    }
-    // ---- loop B: add_car for the newly assigned piles, ascending (CHS.hpp:864-877 / 1029-1042) ----
+// @region add_car (per-lane serial draws)
+    // ---- add_car for the newly assigned piles, ascending (CHS.hpp:864-877 / 1029-1042).  The E/U/E draws of a hub are
+    // a serial chain through its two streams, so this part stays one lane = one hub. ----
     {
+        float *const arrive0 = P.arrive + tile0 + lane;
         uint32_t m = add_mask;
         while (m) {
             const int i = __ffs(m) - 1;
@@ -154,61 +301,37 @@ __device__ __forceinline__ StationOut station_pass(const ChubParams &P, int h, i
                 stay = min(max(stay, 1), 63);
                 cn = min(cn, 31);
             }
-            const bool urgent = cn > 0 && stay <= cn;
-            row[i * ld] = make_uint4(__float_as_uint(arrive), __float_as_uint(tsoc), __float_as_uint(power),
-                                     (uint32_t) stay | PW_CAR | (urgent ? PW_URGENT : 0u) | ((uint32_t) cn << 15) |
-                                         (tu << 20));
-            P.arrive[(size_t) (slot0 + i) * ld + h] = arrive;
+            const uint32_t urgent = (cn > 0 && stay <= cn) ? 1u : 0u;
+            pile0[i * 32 + lane] = make_uint4(__float_as_uint(arrive), __float_as_uint(tsoc), __float_as_uint(power),
+                                              (uint32_t) stay | PW_CAR | (urgent << 14) | ((uint32_t) cn << 15) | (tu << 20));
+            arrive0[i * 32] = arrive;
+            (&S.pw[0][0])[i * 32 + lane] = __float_as_uint(power) | (urgent << 31);
         }
     }
-    // ---- pass C: remaining bookkeeping + calculate_output in ascending fp32 order (CHS.hpp:1233-1261) ----
-    float mn = 0.0f, mx = 0.0f, now = 0.0f;
-    int number = 0;
-    const uint32_t done_mask = chg_mask | add_mask;
-    for (int i = 0; i < n; ++i) {
-        const uint32_t bit = 1u << i;
-        if (RESET && !(add_mask & bit)) {
-            row[i * ld] = make_uint4(0u, 0u, 0u, 0u);
-            continue;
-        }
-        if (!RESET && !((car_mask | add_mask) & bit)) continue;  // stays empty: nothing to read
-        uint4 r = row[i * ld];
-        uint32_t w = r.w;
-        if (!(done_mask & bit)) {  // occupied, not charging this step: remove_car only
-            const int stay = PW_STAY(w), already = PW_ALREADY(w) + 1;
-            if (dep_mask & bit) {
-                if (ceilf(__uint_as_float(r.x)) < floorf(target_of(PW_TU(w)))) o.incomplete += 1;
-                w = 0u;
-                r = make_uint4(0u, 0u, 0u, 0u);
-            } else {
-                const int cn = PW_CN(w);
-                const bool urgent = cn > 0 && (stay - already) <= cn;
-                w = (w & ~(PW_CHARGE | PW_URGENT | (0x3fu << 6))) | ((uint32_t) already << 6) | (urgent ? PW_URGENT : 0u);
-                r.w = w;
-            }
-            row[i * ld] = r;
-        }
-        if (w & PW_CAR) {
-            const float power = __uint_as_float(r.z);
-            number += 1;
-            mx += power;
-            if (w & PW_URGENT) mn += power;
-            if (w & PW_CHARGE) now += power;
-        }
-    }
-    o.mn = mn; o.mx = mx; o.now = now; o.number = number;
-    return o;
-}
+    __syncwarp();
 
-template <bool RESET>
-__device__ __forceinline__ StationOut station_any(const ChubParams &P, int h, int slot0, int n, int type, int cp, int t,
-                                                  int line, uint32_t act_bits, HubRng &rng, uint32_t &err) {
-    if (cp) {  // constant-power charging (constant_charging=True): cold instantiations
-        if (type == CHUB_SLOW) return station_pass<RESET, CHUB_SLOW, 1>(P, h, slot0, n, t, line, act_bits, rng, err);
-        return station_pass<RESET, CHUB_FAST, 1>(P, h, slot0, n, t, line, act_bits, rng, err);
+// @region station sums
+    // ---- calculate_output in ascending fp32 order (CHS.hpp:1233-1261); adding +0.0f for a skipped pile is exact ----
+    const uint32_t present = occ_after | add_mask;
+    const uint32_t chg_after = chg_mask & ~dep_mask & ~add_mask;
+    float mn = 0.0f, mx = 0.0f, now = 0.0f;
+    pwp = &S.pw[0][lane];
+    for (int i = 0; i < n; ++i, pwp += 32) {
+        const uint32_t vb = *pwp;
+        const bool here = (present >> i) & 1u;
+        const float power = here ? __uint_as_float(vb & 0x7fffffffu) : 0.0f;
+        mx += power;
+        mn += (vb & PWB_URGENT) ? power : 0.0f;
+        now += ((chg_after >> i) & 1u) ? power : 0.0f;
     }
-    if (type == CHUB_SLOW) return station_pass<RESET, CHUB_SLOW, 0>(P, h, slot0, n, t, line, act_bits, rng, err);
-    return station_pass<RESET, CHUB_FAST, 0>(P, h, slot0, n, t, line, act_bits, rng, err);
+    if (mine) {
+        o.mn = mn; o.mx = mx; o.now = now;
+        o.number = __popc(present);
+        o.line = min(want - assigned, 10);
+        o.flow = flow;
+        o.incomplete = incomplete + (int) S.inc_s[lane];
+    }
+    __syncwarp();
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -218,6 +341,7 @@ __device__ __forceinline__ StationOut station_any(const ChubParams &P, int h, in
 // x / D for a literal D: exactly the IEEE quotient (Markstein correction), 3 instructions instead of ~25
 #define DIVC(x, D) chub_div_const((x), (D), 1.0 / (D))
 
+// @region hydrogen helpers
 __device__ __forceinline__ double py_max(double a, double b) { return b > a ? b : a; }  // Python max(a, b)
 __device__ __forceinline__ double py_min(double a, double b) { return b < a ? b : a; }  // Python min(a, b)
 
@@ -303,6 +427,7 @@ __device__ __noinline__ double fcev_general(const ChubParams &P, int h, int arri
     return total_mass;
 }
 
+// @region hub load/store/trace/obs
 struct HubVars {  // per-hub registers that live across the stages
     HubRng rng;
     int t, line0, line1, qn, fline, farr, flow0, flow1;
@@ -317,8 +442,7 @@ __device__ __forceinline__ void hub_load(const ChubParams &P, int h, HubVars &v)
     v.t = a.z & 0xff; v.line0 = (a.z >> 8) & 0xff; v.line1 = (a.z >> 16) & 0xff; v.qn = a.z >> 24;
     v.flow0 = (int) (a.w & 0xff) - 128; v.flow1 = (int) ((a.w >> 8) & 0xff) - 128;
     v.fline = (a.w >> 16) & 0xff; v.farr = a.w >> 24;
-    v.store = P.store[h];
-    v.err = 0u;
+    v.err = 0u;   // v.store is loaded after the stations (it is not needed before, and registers are scarce there)
 }
 __device__ __forceinline__ void hub_store(const ChubParams &P, int h, const HubVars &v) {
     uint32_t z = (uint32_t) v.t | ((uint32_t) v.line0 << 8) | ((uint32_t) v.line1 << 16) | ((uint32_t) v.qn << 24);
@@ -367,13 +491,15 @@ __device__ __forceinline__ void write_obs(const ChubParams &P, int h, const Chub
 // EvcsspManagerEnv_v6.reset (evcssp_manager.py:304-316) of one hub, from and to HBM: both stations
 // (evs_reset), hydrogen store, FCEV queue, episode statistics, first observation of the new episode.
 // Out of line on purpose: the step kernel calls it once per hub per 96 steps (fused auto-reset).
+// @region hub_reset_full
 __device__ __noinline__ void hub_reset_full(const ChubParams &P, int h, long long k_obs) {
     const int ci = P.cls ? __ldg(&P.cls[h]) : 0;
     const ChubClass &c = P.classes[ci];
     HubVars v;
     hub_load(P, h, v);
-    StationOut s0 = station_any<true>(P, h, 0, c.n[0], c.type[0], c.constant, 0, 0, 0u, v.rng, v.err);
-    StationOut s1 = station_any<true>(P, h, P.S0, c.n[1], c.type[1], c.constant, 0, 0, 0u, v.rng, v.err);
+    v.store = 0.0;
+    StationOut s0 = station_reset_any(P, h, 0, c.n[0], c.type[0], c.constant, v.rng, v.err);
+    StationOut s1 = station_reset_any(P, h, P.S0, c.n[1], c.type[1], c.constant, v.rng, v.err);
     v.t = 0;
     v.line0 = s0.line; v.line1 = s1.line;
     v.flow0 = s0.flow; v.flow1 = s1.flow;
@@ -392,86 +518,122 @@ __device__ __noinline__ void hub_reset_full(const ChubParams &P, int h, long lon
 }
 
 // ---------------------------------------------------------------------------------------------
-// Cooperative read of the warp's 32 action rows.  Each row is loaded with coalesced 128-byte
-// requests (lane = column) and binarised exactly like action_to_real on a float32 vector
-// (evcssp_manager.py:384-404): on iff (a + 1)/2 >= 0.5 in fp32.  __ballot_sync packs a row into
-// masks that lane r keeps; the two analog entries come back by shuffle.
-__device__ __forceinline__ void load_actions(const ChubParams &P, int h, bool active, int na,
-                                             unsigned long long &bits, float &a_m2, float &a_m1) {
-    const unsigned full = 0xffffffffu;
+// The warp's 32 action rows are one contiguous block of the row-major [H][stride] matrix a policy
+// emits.  It is copied into shared memory with coalesced 128-bit loads and each lane then reads ITS
+// row from there (stride odd -> conflict free), binarising exactly like action_to_real on a float32
+// vector (evcssp_manager.py:384-404): on iff (a + 1)/2 >= 0.5 in fp32.  fl(a + 1) >= 1 holds exactly
+// for a >= -2^-25 (the tie at 1 - 2^-25 rounds to even = 1.0), so the test is a single compare
+// (tests/test_host_logic.py checks the equivalence around the boundary).  Rows that cannot be staged
+// (partial last warp, very wide or misaligned matrices) are read straight from global memory.
+// @region load_actions
+__device__ __forceinline__ void load_actions(const ChubParams &P, float *stage, int stage_floats, int h, bool active,
+                                             int na, unsigned long long &bits, float &a_m2, float &a_m1) {
+    // a_m2 / a_m1 are returned in registers; the caller parks them in shared memory after the final __syncwarp
     const int lane = threadIdx.x & 31;
     const int h0 = h - lane;
+    const int stride = P.action_stride;
     bits = 0ull; a_m2 = 0.0f; a_m1 = 0.0f;
-    const int my_na = active ? na : -2;  // -2: no hub in this lane -> every column predicate is false
-    // eight rows per batch: all their loads are issued before the first value is used, so the warp
-    // pays four memory round trips for its 32 rows instead of one per row and chunk
-    for (int r0 = 0; r0 < 32; r0 += 8) {
-        float v[8][3];
-        int rna[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            rna[j] = __shfl_sync(full, my_na, r0 + j);
-            const float *rowp = P.actions + (size_t) (h0 + r0 + j) * P.action_stride;
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                const int idx = c * 32 + lane;
-                v[j][c] = (idx < rna[j] + 2) ? __ldg(rowp + idx) : -1.0f;
-            }
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int n = rna[j];
-            const unsigned m0 = __ballot_sync(full, lane < n && (v[j][0] + 1.0f) / 2.0f >= 0.5f);
-            const unsigned m1 = __ballot_sync(full, 32 + lane < n && (v[j][1] + 1.0f) / 2.0f >= 0.5f);
-            const int c2 = n >> 5, c1 = (n + 1) >> 5;  // chunks holding action[-2] and action[-1]
-            const float t2 = c2 == 0 ? v[j][0] : (c2 == 1 ? v[j][1] : v[j][2]);
-            const float t1 = c1 == 0 ? v[j][0] : (c1 == 1 ? v[j][1] : v[j][2]);
-            const float e2 = __shfl_sync(full, t2, n & 31);
-            const float e1 = __shfl_sync(full, t1, (n + 1) & 31);
-            if (lane == r0 + j) {
-                bits = (unsigned long long) m0 | ((unsigned long long) m1 << 32);
-                a_m2 = e2;  // action[-2] -> electrolyser set-point (the reference swaps the last two)
-                a_m1 = e1;  // action[-1] -> fuel-cell set-point
-            }
-        }
+    const bool staged = (h0 + 32 <= P.H) && (32 * stride <= stage_floats) &&
+                        ((reinterpret_cast<uintptr_t>(P.actions) & 15u) == 0);
+    const float *src = P.actions + (size_t) h * stride;
+    if (staged) {
+        const uint4 *g = reinterpret_cast<const uint4 *>(P.actions + (size_t) h0 * stride);
+        uint4 *d = reinterpret_cast<uint4 *>(stage);
+        for (int c = lane; c < 8 * stride; c += 32) d[c] = __ldcs(g + c);
+        __syncwarp();
+        src = stage + lane * stride;
     }
+    if (active) {
+        for (int j = 0; j < na; ++j) {
+            if (src[j] >= -0x1p-25f) bits |= 1ull << j;
+        }
+        a_m2 = src[na];      // action[-2] -> electrolyser set-point (the reference swaps the last two)
+        a_m1 = src[na + 1];  // action[-1] -> fuel-cell set-point
+    }
+    __syncwarp();  // the staging area is reused as the stations' scratch
 }
 
-template <int BLOCK, int MINB>
-__global__ void __launch_bounds__(BLOCK, MINB) chub_step_kernel(const __grid_constant__ ChubParams P) {
-    const int h = blockIdx.x * blockDim.x + threadIdx.x;
+// constant-power stations (constant_charging=True) are rare: one shared out-of-line copy per type.  State
+// travels by value so that the caller's copies stay in registers.
+// @region kernel head
+struct StationIO {
+    HubRng rng;
+    uint32_t err;
+    StationOut o;
+};
+template <int TYPE, int Q>
+__device__ __noinline__ StationIO station_step_cp(const ChubParams &P, WarpScratch<Q> &S, const float *tl_s, bool mine, int h,
+                                                  int slot0, int n, int t, int line, uint32_t act_bits, StationIO io) {
+    station_step<TYPE, 1, Q>(P, S, tl_s, mine, h, slot0, n, t, line, act_bits, io.rng, io.err, io.o);
+    return io;
+}
+
+template <int WARPS, int MINB, int Q>
+__global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __grid_constant__ ChubParams P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const float *tl_s = nullptr;
+    WarpScratch<Q> &S = *reinterpret_cast<WarpScratch<Q> *>(smem + (threadIdx.x >> 5) * P.ws_bytes);
+
+    const unsigned full = 0xffffffffu;
+    const int h = blockIdx.x * (WARPS * 32) + threadIdx.x;
     const bool active = h < P.H;
     const int ci = (active && P.cls) ? __ldg(&P.cls[h]) : 0;
     const ChubClass &c = P.classes[ci];
     const int n0 = c.n[0], n1 = c.n[1];
     unsigned long long bits;
-    float a_m2, a_m1;
-    load_actions(P, h, active, n0 + n1, bits, a_m2, a_m1);
+    {
+        float a_m2, a_m1;
+        load_actions(P, reinterpret_cast<float *>(&S.inc_s[0]), (P.ws_bytes - (int) offsetof(WarpScratch<Q>, inc_s)) / 4, h,
+                     active, n0 + n1, bits, a_m2, a_m1);
+        S.am[0][threadIdx.x & 31] = a_m2;
+        S.am[1][threadIdx.x & 31] = a_m1;
+    }
 
     HubVars v;
     v.err = 0u; v.t = 0; v.line0 = v.line1 = 0;
+    v.rng.k0 = v.rng.k1 = v.rng.uctr = 0u; v.rng.lcg = 1u;
     if (active) hub_load(P, h, v);
-    const long long k = *P.step_index + P.step_offset;
-    double pv_t = 0.0, wd_t = 0.0, pr_t = 0.0;
-    if (active) trace_at(P, h, k, pv_t, wd_t, pr_t);
-
-    // ---- the two EV stations, station 0 first (Aggregator_Simple.py:141-142) ----
-    // phase_sync keeps the warps of a block inside the same code region (instruction-cache locality)
-    StationOut s0 = {}, s1 = {};
-    if (P.phase_sync & 1) __syncthreads();
-    if (active && !(P.phase_sync & 2)) s0 = station_any<false>(P, h, 0, n0, c.type[0], c.constant, v.t, v.line0, (uint32_t) bits, v.rng, v.err);
-    if (P.phase_sync & 1) __syncthreads();
-    if (active && !(P.phase_sync & 4)) s1 = station_any<false>(P, h, P.S0, n1, c.type[1], c.constant, v.t, v.line1,
-                                        (uint32_t) (bits >> n0), v.rng, v.err);
-    if (P.phase_sync & 1) __syncthreads();
-    if (!active) return;
-    if (P.phase_sync & 8) {  // timing ablation only: stations without the hub section
-        hub_store(P, h, v);
-        return;
+    if (active && (P.phase_sync & 4)) {   // start the warp's pile rows on their way from HBM to L2: the scan then waits on L2, not on DRAM
+        const uint4 *q = P.pile + chub_pile_index(h, 0, P.S0 + P.S1);
+        for (int i = 0; i < n0; ++i) asm volatile("prefetch.global.L2 [%0];" ::"l"(q + i * 32));
+        q += P.S0 * 32;
+        for (int i = 0; i < n1; ++i) asm volatile("prefetch.global.L2 [%0];" ::"l"(q + i * 32));
     }
+
+    // ---- the two EV stations, station 0 first (Aggregator_Simple.py:141-142); the whole warp takes part ----
+    StationOut s0 = {}, s1 = {};
+#pragma unroll 1
+    for (int s = 0; s < 2; ++s) {
+        const int type = c.type[s], n = s ? n1 : n0, slot0 = s ? P.S0 : 0, line = s ? v.line1 : v.line0;
+        const uint32_t abits = s ? (uint32_t) (bits >> n0) : (uint32_t) bits;
+        const bool curve = active && !c.constant;
+        StationOut o = {};
+        if (P.phase_sync & 1) __syncthreads();   // keep the block's warps in the same code region (instruction cache)
+        const bool m_slow = curve && type == CHUB_SLOW, m_fast = curve && type == CHUB_FAST;
+        if (__any_sync(full, m_fast)) station_step<CHUB_FAST, 0, Q>(P, S, tl_s, m_fast, h, slot0, n, v.t, line, abits, v.rng, v.err, o);
+        if (__any_sync(full, m_slow)) station_step<CHUB_SLOW, 0, Q>(P, S, tl_s, m_slow, h, slot0, n, v.t, line, abits, v.rng, v.err, o);
+        const bool c_slow = active && c.constant && type == CHUB_SLOW, c_fast = active && c.constant && type == CHUB_FAST;
+        if (__any_sync(full, c_fast || c_slow)) {
+            StationIO io;
+            io.rng = v.rng; io.err = v.err; io.o = o;
+            if (__any_sync(full, c_fast)) io = station_step_cp<CHUB_FAST, Q>(P, S, tl_s, c_fast, h, slot0, n, v.t, line, abits, io);
+            if (__any_sync(full, c_slow)) io = station_step_cp<CHUB_SLOW, Q>(P, S, tl_s, c_slow, h, slot0, n, v.t, line, abits, io);
+            v.rng = io.rng; v.err = io.err; o = io.o;
+        }
+        if (s == 0) s0 = o; else s1 = o;
+    }
+    if (P.phase_sync & 2) __syncthreads();
+    if (!active) return;
+    // what only the hub section needs is fetched now: store mass, exogenous traces, the two analog actions
+    v.store = P.store[h];
+    const long long k = *P.step_index + P.step_offset;
+    double pv_t, wd_t, pr_t;
+    trace_at(P, h, k, pv_t, wd_t, pr_t);
+    const float a_m2 = S.am[0][threadIdx.x & 31], a_m1 = S.am[1][threadIdx.x & 31];
     v.line0 = s0.line; v.line1 = s1.line;
     v.flow0 = s0.flow; v.flow1 = s1.flow;
 
+// @region hub section
     // ---- electrolyser set-point under the grid limit (evcssp_manager.py:157-180) ----
     const double cp0 = (double) s0.now, cp1 = (double) s1.now;
     const double charging = 0.0 + cp0 + cp1;
@@ -615,6 +777,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) chub_step_kernel(const __grid_con
     }
 }
 
+// @region other kernels
 __global__ void __launch_bounds__(128) chub_reset_kernel(const __grid_constant__ ChubParams P) {
     const int h = blockIdx.x * blockDim.x + threadIdx.x;
     if (h >= P.H) return;
@@ -641,19 +804,32 @@ void chub_launch_s2t_lut(float *out, cudaStream_t s) { chub_s2t_lut_kernel<<<(40
 
 __global__ void chub_tick_kernel(long long *step_index, int n) { *step_index += n; }
 
-#define CHUB_LAUNCH(B, M) chub_step_kernel<B, M><<<(p.H + (B) - 1) / (B), B, 0, s>>>(p)
-void chub_launch_step(const ChubParams &p, cudaStream_t s) {
-    switch (p.block) {  // block size * 100 + min blocks per SM (register budget = 65536 / (block * minb))
-        case 12808: CHUB_LAUNCH(128, 8); break;
-        case 12810: CHUB_LAUNCH(128, 10); break;
-        case 12812: CHUB_LAUNCH(128, 12); break;
-        case 25604: CHUB_LAUNCH(256, 4); break;
-        case 25605: CHUB_LAUNCH(256, 5); break;
-        case 25606: CHUB_LAUNCH(256, 6); break;
-        case 51203: CHUB_LAUNCH(512, 3); break;
-        case 102401: CHUB_LAUNCH(1024, 1); break;
-        case 76801: CHUB_LAUNCH(768, 1); break;
-        default: CHUB_LAUNCH(512, 2); break;
+template <int WARPS, int MINB, int Q>
+static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s) {
+    ChubParams p = p0;
+    p.ws_bytes = (int) warp_scratch_bytes<Q>(p.S0 > p.S1 ? p.S0 : p.S1);
+    // room to stage the warp's 32 action rows behind the parked analog entries, when that stays small
+    const int stage_bytes = (int) offsetof(WarpScratch<Q>, inc_s) + 128 * p.action_stride;
+    if (stage_bytes > p.ws_bytes && stage_bytes <= 10240) p.ws_bytes = stage_bytes;
+    const size_t smem = (size_t) WARPS * p.ws_bytes;
+    auto kern = chub_step_kernel<WARPS, MINB, Q>;
+    // per device and cheap; set on every launch so that engines on several devices of one process all get it
+    cudaError_t r = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+    if (r != cudaSuccess) return r;
+    const int block = WARPS * 32;
+    kern<<<(p.H + block - 1) / block, block, smem, s>>>(p);
+    return cudaSuccess;
+}
+cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s) {
+    switch (p.block) {  // warps per block * 100 + min blocks per SM * 10 + cars per lane per add_car round
+        case 1620: return launch_step_variant<16, 2, 0>(p, s);
+        case 840: return launch_step_variant<8, 4, 0>(p, s);
+        case 1220: return launch_step_variant<12, 2, 0>(p, s);
+        case 830: return launch_step_variant<8, 3, 0>(p, s);
+        case 820: return launch_step_variant<8, 2, 0>(p, s);
+        case 2410: return launch_step_variant<24, 1, 0>(p, s);
+        case 3210: return launch_step_variant<32, 1, 0>(p, s);
+        default: return launch_step_variant<16, 2, 0>(p, s);
     }
 }
 void chub_launch_reset(const ChubParams &p, cudaStream_t s) {

@@ -2,9 +2,11 @@
 #pragma once
 #include "chub_device.cuh"
 
-// HBM layout (SoA, hub index fastest so a warp of 32 hubs touches one contiguous row):
-//   pile[(slot) * Hpad + h]   uint4 {soc f32, s2t(soc) f32, power f32, packed}  slot = station0 piles, then station1 piles
-//   arrive[(slot) * Hpad + h] float  arrival SOC ("init_soc" column; written once per car, never read by the step)
+// HBM layout.  Pile state is tiled by warp: the S = S0 + S1 pile rows of 32 consecutive hubs are one contiguous
+// block of S * 512 bytes (a few DRAM pages, a handful of TLB entries per warp instead of one 8 MB-strided row each):
+//   pile[chub_pile_index(h, slot, S)]   uint4 {soc f32, s2t(soc) f32, power f32, packed}  slot = station0 piles, then station1 piles
+//   arrive[chub_pile_index(h, slot, S)] float  arrival SOC ("init_soc" column; written once per car, never read by the step)
+// Per-hub arrays are plain [Hpad] (a warp reads 32 consecutive elements):
 //   hubA[h]                   uint4 {minstd state, U counter, packed1, packed2}
 //   store[h]                  double hydrogen store mass in grams
 //   keys[h]                   uint2  U-stream keys (read only)
@@ -22,11 +24,18 @@
 #define PW_CN(w) (((w) >> 15) & 0x1fu)
 #define PW_TU(w) (((w) >> 20) & 0x3ffu)
 
+
+// element index of pile `slot` of hub `h`: [h / 32][slot][h % 32]
+__host__ __device__ inline size_t chub_pile_index(int h, int slot, int S) {
+    return ((size_t) (h >> 5) * (size_t) S + (size_t) slot) * 32 + (size_t) (h & 31);
+}
+
 struct ChubParams {
     int H, Hpad, S0, S1;
     int n_classes, action_stride, auto_reset, diagnostics;
     int trace_len, trace_per_hub;
-    int block, phase_sync;            // launch shape of the step kernel
+    int block, phase_sync;            // launch shape of the step kernel (see chub_launch_step); phase_sync: block barriers between code regions
+    int ws_bytes;                     // bytes of shared-memory scratch per warp (set by chub_launch_step)
     int step_offset;                  // added to *step_index (graph-captured rollouts bake 0..n-1)
     const long long *step_index;      // device: absolute step index of the state being left
     uint4 *pile;
@@ -52,7 +61,7 @@ struct ChubParams {
     const uint8_t *reset_mask;        // reset kernel only
 };
 
-void chub_launch_step(const ChubParams &p, cudaStream_t s);
+cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s);
 void chub_launch_reset(const ChubParams &p, cudaStream_t s);
 void chub_launch_s2t_lut(float *out, cudaStream_t s);
 void chub_launch_tick(long long *step_index, int n, cudaStream_t s);

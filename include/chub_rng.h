@@ -40,6 +40,19 @@ CHUB_HD uint32_t chub_minstd_next(uint32_t x) {
     return r >= 2147483647u ? r - 2147483647u : r;
 }
 
+/* k steps at once: x * (16807^k mod (2^31-1)) mod (2^31-1) for a precomputed multiplier A < 2^31.
+ * The product has up to 62 bits, so the fold is applied twice.  Lets a caller compute the next
+ * few states independently of each other instead of as a dependent chain. */
+#define CHUB_MINSTD_A2 282475249u
+#define CHUB_MINSTD_A3 1622650073u
+#define CHUB_MINSTD_A4 984943658u
+CHUB_HD uint32_t chub_minstd_jump(uint32_t x, uint32_t A) {
+    uint64_t p = (uint64_t) x * (uint64_t) A;
+    uint32_t r = (uint32_t) (p & 0x7fffffffull) + (uint32_t) (p >> 31);   /* < 2^32 */
+    r = (r & 0x7fffffffu) + (r >> 31);                                    /* <= 2^31 */
+    return r >= 2147483647u ? r - 2147483647u : r;
+}
+
 CHUB_HD uint64_t chub_splitmix64(uint64_t z) {
     z += 0x9E3779B97F4A7C15ull;
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;

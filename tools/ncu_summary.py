@@ -40,24 +40,28 @@ print("warp-inst (first launch)", tot, "stall samples", tots)
 for n, w, t, f, ln, text in sorted(recs, key=lambda x: -x[0])[:topn]:
     print("%5.2f%% inst %5.2f%% stall lanes %4.1f | %s:%d %s" % (100.0 * n / tot, 100.0 * w / tots, (t / n) if n else 0, f[:14], ln, text))
 
-# ---- per-region totals: (file, first line, last line, label); lines of inlined device functions are
-# attributed to their own file:line, whatever the caller
-REGIONS = [("chub_kernels.cu", 47, 78, "station: receive_car draws"), ("chub_kernels.cu", 79, 107, "station: scan+assign"),
-           ("chub_kernels.cu", 108, 137, "station: loop A shell"), ("chub_kernels.cu", 138, 163, "station: loop B shell"),
-           ("chub_kernels.cu", 164, 201, "station: pass C"), ("chub_kernels.cu", 214, 304, "hydrogen helpers"),
-           ("chub_kernels.cu", 306, 336, "hub load/store/trace"), ("chub_kernels.cu", 337, 366, "write_obs"),
-           ("chub_kernels.cu", 367, 393, "hub_reset_full"), ("chub_kernels.cu", 394, 439, "load_actions"),
-           ("chub_kernels.cu", 440, 472, "kernel head"), ("chub_kernels.cu", 473, 616, "hub section"),
-           ("chub_device.cuh", 60, 149, "rng/normals"), ("chub_device.cuh", 150, 195, "slow curves"),
-           ("chub_device.cuh", 196, 242, "fast curves"), ("chub_device.cuh", 243, 300, "const/dispatch"),
-           ("chub_fastmath.h", 39, 57, "chub_log"), ("chub_fastmath.h", 58, 80, "chub_exp"),
-           ("chub_fastmath.h", 81, 104, "chub_div"), ("chub_rng.h", 0, 999, "rng primitives")]
+# ---- per-region totals.  Regions are declared in the sources themselves: a comment "@region <label>" starts a
+# region that runs to the next marker of that file.  Lines of inlined device functions are attributed to their
+# own file:line, whatever the caller.
+import glob, os, re
+REGIONS = []
+_csrc = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
+for path in glob.glob(os.path.join(_csrc, "charginghub_env_b200", "csrc", "*")) + glob.glob(os.path.join(_csrc, "include", "*.h")):
+    if not path.endswith((".cu", ".cuh", ".h")):
+        continue
+    marks = [(k + 1, m.group(1).strip()) for k, line in enumerate(open(path, errors="ignore"))
+             for m in [re.search(r"@region\s+(.*)", line)] if m]
+    base = os.path.basename(path)
+    if not marks:
+        REGIONS.append((base, 0, 10 ** 9, base))
+    for j, (ln, lab) in enumerate(marks):
+        REGIONS.append((base, ln, marks[j + 1][0] - 1 if j + 1 < len(marks) else 10 ** 9, lab))
 if "--regions" in sys.argv:
     agg = collections.OrderedDict()
     for n, w, t, f, ln, text in recs:
         lab = "other " + f
         for rf, a, b, l in REGIONS:
-            if f.startswith(rf[:14]) and a <= ln <= b:
+            if rf.startswith(f[:14]) and f[:14] == rf[:14] and a <= ln <= b:
                 lab = l
                 break
         x = agg.setdefault(lab, [0, 0, 0])
