@@ -117,12 +117,29 @@ __device__ __forceinline__ float canon_f(uint32_t &lcg) {
 // Marsaglia polar, second variate discarded (bits/random.tcc:1811-1844) -- clamped and mapped to an SOC.
 // Returns {soc bits, new minstd state}.
 __device__ __noinline__ uint2 draw_mk_soc(uint32_t lcg) {
-    double x, y, r2;
-    do {
-        x = 2.0 * canon_d(lcg) - 1.0;
-        y = 2.0 * canon_d(lcg) - 1.0;
-        r2 = x * x + y * y;
-    } while (r2 > 1.0 || r2 == 0.0);
+    // The accept/reject walk only needs to know whether x^2 + y^2 <= 1.  With c = (lo + hi (2^31 - 2)) / (2^31 - 2)^2
+    // = hi / (2^31 - 2) to within 5e-10 (hi = the second state of the pair, minus 1), an fp32 estimate of r2 is good
+    // to ~1e-6; the attempt is evaluated exactly, like the reference, only inside a +-4e-6 band around the boundary.
+    // Rejected attempts (21 %) then cost a few fp32 operations instead of two fp64 canonical variates.
+    uint32_t s0;
+    for (;;) {
+        s0 = lcg;
+        const uint32_t s2 = chub_minstd_jump(s0, CHUB_MINSTD_A2), s4 = chub_minstd_jump(s0, CHUB_MINSTD_A4);
+        lcg = s4;
+        const float xa = fmaf((float) (s2 - 1u), 9.31322575e-10f, -1.0f), ya = fmaf((float) (s4 - 1u), 9.31322575e-10f, -1.0f);
+        const float r2a = fmaf(xa, xa, ya * ya);
+        bool ok = r2a < 1.0f;
+        if (fabsf(r2a - 1.0f) < 4e-6f || r2a < 4e-6f) {
+            const double xe = 2.0 * canon_d_of(chub_minstd_next(s0), s2) - 1.0;
+            const double ye = 2.0 * canon_d_of(chub_minstd_jump(s0, CHUB_MINSTD_A3), s4) - 1.0;
+            const double r2e = xe * xe + ye * ye;
+            ok = !(r2e > 1.0 || r2e == 0.0);
+        }
+        if (ok) break;
+    }
+    const double x = 2.0 * canon_d_of(chub_minstd_next(s0), chub_minstd_jump(s0, CHUB_MINSTD_A2)) - 1.0;
+    const double y = 2.0 * canon_d_of(chub_minstd_jump(s0, CHUB_MINSTD_A3), lcg) - 1.0;
+    const double r2 = x * x + y * y;
     double mult = sqrt(chub_div(-2.0 * chub_log(r2, kLogTab), r2));
     float de = (float) ((y * mult) * 3.0 + 7.0);
     de = fminf(fmaxf(de, 1.0f), 10.0f);

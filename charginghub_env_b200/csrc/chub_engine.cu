@@ -37,7 +37,7 @@ struct chub_engine {
     ChubParams P;
     // device
     uint4 *pile = nullptr; float *arrive = nullptr; uint4 *hubA = nullptr; double *store = nullptr;
-    uint2 *keys = nullptr; int *cls = nullptr; float4 *stats = nullptr, *last_stats = nullptr;
+    uint2 *keys = nullptr, *occ = nullptr; int *cls = nullptr; float4 *stats = nullptr, *last_stats = nullptr;
     uint32_t *err = nullptr; float *qsoc = nullptr; ChubClass *d_classes = nullptr; double *d_el = nullptr;
     uint16_t *lut = nullptr; float *s2t_lut = nullptr; double *pv = nullptr, *wd = nullptr, *price_tr = nullptr;
     float *obs = nullptr, *reward = nullptr; uint8_t *done = nullptr; double *diag = nullptr; float *st_power = nullptr;
@@ -58,7 +58,7 @@ static void engine_free(chub_engine *e) {
     cudaSetDevice(e->cfg.device);
     if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
     if (e->graph) cudaGraphDestroy(e->graph);
-    void *ptrs[] = {e->pile, e->arrive, e->hubA, e->store, e->keys, e->cls, e->stats, e->last_stats, e->err, e->qsoc,
+    void *ptrs[] = {e->pile, e->arrive, e->hubA, e->store, e->keys, e->occ, e->cls, e->stats, e->last_stats, e->err, e->qsoc,
                     e->d_classes, e->d_el, e->lut, e->s2t_lut, e->pv, e->wd, e->price_tr, e->obs, e->reward, e->done, e->diag,
                     e->st_power, e->step_index, e->actions_stage};
     for (void *p : ptrs)
@@ -93,7 +93,7 @@ extern "C" int chub_create(const chub_config *cfg, chub_engine **out) {
     const size_t Hp = (size_t) e->Hpad;
     cudaError_t r = cudaSuccess;
     auto A = [&](cudaError_t x) { if (r == cudaSuccess) r = x; };
-    A(dalloc(&e->hubA, Hp)); A(dalloc(&e->store, Hp)); A(dalloc(&e->keys, Hp));
+    A(dalloc(&e->hubA, Hp)); A(dalloc(&e->store, Hp)); A(dalloc(&e->keys, Hp)); A(dalloc(&e->occ, Hp));
     A(dalloc(&e->stats, Hp)); A(dalloc(&e->last_stats, Hp)); A(dalloc(&e->err, Hp));
     A(dalloc(&e->qsoc, Hp * CHUB_FCEV_QCAP)); A(dalloc(&e->lut, (size_t) 96 * 1000)); A(dalloc(&e->s2t_lut, (size_t) 4000));
     A(dalloc(&e->obs, Hp * CHUB_OBS_DIM)); A(dalloc(&e->reward, Hp)); A(dalloc(&e->done, Hp));
@@ -396,9 +396,9 @@ static int fill_params(chub_engine *e, ChubParams &P) {
     {   // experiment knobs (defaults are the measured best)
         const char *b = getenv("CHUB_BLOCK"), *y = getenv("CHUB_PHASE_SYNC");
         P.block = b ? atoi(b) : 0;
-        P.phase_sync = y ? atoi(y) : 1;
+        P.phase_sync = y ? atoi(y) : 0;
     }
-    P.pile = e->pile; P.arrive = e->arrive; P.hubA = e->hubA; P.store = e->store; P.keys = e->keys; P.cls = e->cls;
+    P.pile = e->pile; P.arrive = e->arrive; P.hubA = e->hubA; P.store = e->store; P.keys = e->keys; P.occ = e->occ; P.cls = e->cls;
     P.stats = e->stats; P.last_stats = e->last_stats; P.err = e->err; P.qsoc = e->qsoc;
     P.classes = e->d_classes; P.el_table = e->d_el; P.lut = e->lut; P.s2t_lut = e->s2t_lut;
     P.pv = e->pv; P.wd = e->wd; P.price_tr = e->price_tr;
@@ -688,7 +688,7 @@ struct Seg { void *p; size_t bytes; };
 static std::vector<Seg> state_segments(chub_engine *e) {
     const size_t Hp = e->Hpad, slots = (size_t) (e->S0 + e->S1) * Hp;
     return {{e->pile, slots * sizeof(uint4)}, {e->arrive, slots * sizeof(float)}, {e->hubA, Hp * sizeof(uint4)},
-            {e->store, Hp * sizeof(double)}, {e->keys, Hp * sizeof(uint2)}, {e->stats, Hp * sizeof(float4)},
+            {e->store, Hp * sizeof(double)}, {e->keys, Hp * sizeof(uint2)}, {e->occ, Hp * sizeof(uint2)}, {e->stats, Hp * sizeof(float4)},
             {e->last_stats, Hp * sizeof(float4)}, {e->err, Hp * sizeof(uint32_t)},
             {e->qsoc, Hp * CHUB_FCEV_QCAP * sizeof(float)}, {e->step_index, sizeof(long long)}};
 }

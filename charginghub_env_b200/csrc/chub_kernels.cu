@@ -28,6 +28,7 @@ struct StationOut {
     int line;           // queue length after assign_car
     int flow;           // flow_in_number.back()
     int incomplete;     // departures below target (the reference prints, CHS.hpp:916-921)
+    uint32_t occ;       // occupancy mask after the call
 };
 
 __device__ __forceinline__ float target_of(uint32_t tu) {  // uniform_rand(80, 100), CHS.hpp:41-42, 867
@@ -83,6 +84,7 @@ __device__ __forceinline__ StationOut station_reset(const ChubParams &P, int h, 
         if (urgent) mn += power;
     }
     o.mn = mn; o.mx = mx; o.now = 0.0f; o.number = max(assigned, 0);
+    o.occ = assigned >= 32 ? 0xffffffffu : ((1u << max(assigned, 0)) - 1u);
     return o;
 }
 
@@ -123,6 +125,7 @@ template <int Q>
 struct WarpScratch {
     float am[2][32];                  // the two analog action entries of each hub, parked here during the stations
     // ---- everything below doubles as the staging area of the warp's action rows ----
+    uint32_t park[2][5][32];          // the stations' outputs, parked until the hub section (registers are scarce)
     uint32_t inc_s[32];               // posted to the owner lane: incomplete departures found by a car_step batch
     uint32_t la_t[2][LA_RING], la_w[2][LA_RING], la_id[2][LA_RING];  // car_step rings per curve segment: new charge time
                                       // (f32 bits), packed pile word, lane | pile << 5
@@ -171,8 +174,8 @@ __device__ __forceinline__ void flat_car_step(const ChubParams &P, WarpScratch<Q
 // @region station prologue + receive_car draws
 template <int TYPE, int CP, int Q>
 __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q> &S, const float *tl_s, bool mine, int h,
-                                          int slot0, int n_in, int t, int line_in, uint32_t act_bits, HubRng &rng,
-                                          uint32_t &err, StationOut &o) {
+                                          int slot0, int n_in, int t, int line_in, uint32_t act_bits, uint32_t occ_in,
+                                          HubRng &rng, uint32_t &err, StationOut &o) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int h0 = h - lane;
@@ -205,23 +208,31 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
     // posted power carries the pile's urgency to the owner's summation.
     const size_t tile0 = chub_pile_index(h0, slot0, P.S0 + P.S1);
     uint4 *const pile0 = P.pile + tile0;             // the warp's tile of this station: [pile][32 hubs], contiguous
-    const int ld = 32;
     const uint32_t lt = (1u << lane) - 1u;
     uint32_t car_mask = 0u, chg_mask = 0u, dep_mask = 0u;
     int incomplete = 0;
     int tail0 = 0, tail1 = 0, head0 = 0, head1 = 0;  // warp-uniform ring positions (taken mod LA_RING); count = tail - head
-    const int nmax = __reduce_max_sync(full, n);
-    uint4 *rp = pile0 + lane;                        // walks down the rows
-    uint32_t *pwp = &S.pw[0][lane];
+    // Only rows on which some hub of the warp has a car are visited, and a lane only loads the piles its own
+    // occupancy mask names: the traffic of a quiet hour is proportional to the cars, not to the pile count.
+    const uint32_t occ = mine ? occ_in : 0u;
+    uint32_t rows = __reduce_or_sync(full, occ);
+    uint4 *rp = pile0 + lane;
+    asm volatile("" : "+l"(rp));                     // keep the tile pointer in a register pair instead of re-deriving it
+    uint32_t *const pwp = &S.pw[0][lane];
+    int inext = __ffs(rows) - 1;
     uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
-    if (0 < n) nxt = *rp;
-    for (int i = 0; i <= nmax; ++i, rp += ld, pwp += 32) {   // one extra turn flushes the rings
+    if (rows && ((occ >> inext) & 1u)) nxt = rp[inext * 32];
+    while (rows) {
         const uint4 r = nxt;
-        if (i + 1 < n) nxt = rp[ld];
+        const int i = inext;
+        rows &= rows - 1u;
+        inext = __ffs(rows) - 1;
+        nxt = make_uint4(0u, 0u, 0u, 0u);
+        if (rows && ((occ >> inext) & 1u)) nxt = rp[inext * 32];
         int seg = -1;
         float tt = 0.0f;
-        const uint32_t w = r.w, bit = 1u << (i & 31);
-        if (i < n && (w & PW_CAR)) {
+        const uint32_t w = r.w, bit = 1u << i;
+        if (w & PW_CAR) {                            // piles this lane did not load read as w == 0
             car_mask |= bit;
             const int left = (int) PW_STAY(w) - (int) PW_ALREADY(w) - 1;
             if (left <= 0) dep_mask |= bit;
@@ -232,34 +243,35 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
                 seg = curve_seg<TYPE, CP>(tt);
             } else if (left <= 0) {                            // remove_car of a car that is not charging
                 if (ceilf(__uint_as_float(r.x)) < floorf(target_of(PW_TU(w)))) incomplete += 1;
-                *rp = make_uint4(0u, 0u, 0u, 0u);
+                rp[i * 32] = make_uint4(0u, 0u, 0u, 0u);
             } else {
                 const int cn = PW_CN(w);
                 const uint32_t urgent = (cn > 0 && left <= cn) ? 1u : 0u;
-                rp->w = ((w & ~(PW_CHARGE | PW_URGENT)) + (1u << 6)) | (urgent << 14);
-                *pwp = r.z | (urgent << 31);
+                rp[i * 32].w = ((w & ~(PW_CHARGE | PW_URGENT)) + (1u << 6)) | (urgent << 14);
+                pwp[i * 32] = r.z | (urgent << 31);
             }
         }
         const uint32_t m0 = __ballot_sync(full, seg == 0), m1 = CP ? 0u : __ballot_sync(full, seg == 1);
-        if ((m0 | m1) == 0u && i != nmax) continue;   // nobody charges on this row: nothing to queue, nothing became due
-        if (seg >= 0) {
-            const int sl = seg * LA_RING + ((seg == 0 ? tail0 + __popc(m0 & lt) : tail1 + __popc(m1 & lt)) & (LA_RING - 1));
-            (&S.la_t[0][0])[sl] = __float_as_uint(tt);
-            (&S.la_w[0][0])[sl] = w;
-            (&S.la_id[0][0])[sl] = (uint32_t) lane | ((uint32_t) i << 5);
-        }
-        tail0 += __popc(m0);
-        tail1 += __popc(m1);
-        const int need = i == nmax ? 1 : 32;
-        if (tail0 - head0 >= need) {
-            const int c = min(tail0 - head0, 32);
-            flat_car_step<TYPE, CP, 0, Q>(P, S, tlut, pile0, head0, c);
-            head0 += c;
-        }
-        if (!CP && tail1 - head1 >= need) {
-            const int c = min(tail1 - head1, 32);
-            flat_car_step<TYPE, CP, 1, Q>(P, S, tlut, pile0, head1, c);
-            head1 += c;
+        const int need = rows ? 32 : 1;              // the last occupied row also flushes the rings
+        if ((m0 | m1) != 0u || need == 1) {          // otherwise nobody charges on this row: nothing to queue
+            if (seg >= 0) {
+                const int sl = seg * LA_RING + ((seg == 0 ? tail0 + __popc(m0 & lt) : tail1 + __popc(m1 & lt)) & (LA_RING - 1));
+                (&S.la_t[0][0])[sl] = __float_as_uint(tt);
+                (&S.la_w[0][0])[sl] = w;
+                (&S.la_id[0][0])[sl] = (uint32_t) lane | ((uint32_t) i << 5);
+            }
+            tail0 += __popc(m0);
+            tail1 += __popc(m1);
+            while (tail0 - head0 >= need) {
+                const int c = min(tail0 - head0, 32);
+                flat_car_step<TYPE, CP, 0, Q>(P, S, tlut, pile0, head0, c);
+                head0 += c;
+            }
+            while (!CP && tail1 - head1 >= need) {
+                const int c = min(tail1 - head1, 32);
+                flat_car_step<TYPE, CP, 1, Q>(P, S, tlut, pile0, head1, c);
+                head1 += c;
+            }
         }
     }
 
@@ -315,9 +327,9 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
     const uint32_t present = occ_after | add_mask;
     const uint32_t chg_after = chg_mask & ~dep_mask & ~add_mask;
     float mn = 0.0f, mx = 0.0f, now = 0.0f;
-    pwp = &S.pw[0][lane];
-    for (int i = 0; i < n; ++i, pwp += 32) {
-        const uint32_t vb = *pwp;
+    for (uint32_t prow = __reduce_or_sync(full, present); prow; prow &= prow - 1u) {
+        const int i = __ffs(prow) - 1;
+        const uint32_t vb = pwp[i * 32];
         const bool here = (present >> i) & 1u;
         const float power = here ? __uint_as_float(vb & 0x7fffffffu) : 0.0f;
         mx += power;
@@ -330,6 +342,7 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
         o.line = min(want - assigned, 10);
         o.flow = flow;
         o.incomplete = incomplete + (int) S.inc_s[lane];
+        o.occ = present;
     }
     __syncwarp();
 }
@@ -431,6 +444,7 @@ __device__ __noinline__ double fcev_general(const ChubParams &P, int h, int arri
 struct HubVars {  // per-hub registers that live across the stages
     HubRng rng;
     int t, line0, line1, qn, fline, farr, flow0, flow1;
+    uint32_t occ0, occ1;
     double store;
     uint32_t err;
 };
@@ -442,6 +456,8 @@ __device__ __forceinline__ void hub_load(const ChubParams &P, int h, HubVars &v)
     v.t = a.z & 0xff; v.line0 = (a.z >> 8) & 0xff; v.line1 = (a.z >> 16) & 0xff; v.qn = a.z >> 24;
     v.flow0 = (int) (a.w & 0xff) - 128; v.flow1 = (int) ((a.w >> 8) & 0xff) - 128;
     v.fline = (a.w >> 16) & 0xff; v.farr = a.w >> 24;
+    const uint2 oc = P.occ[h];
+    v.occ0 = oc.x; v.occ1 = oc.y;
     v.err = 0u;   // v.store is loaded after the stations (it is not needed before, and registers are scarce there)
 }
 __device__ __forceinline__ void hub_store(const ChubParams &P, int h, const HubVars &v) {
@@ -449,6 +465,7 @@ __device__ __forceinline__ void hub_store(const ChubParams &P, int h, const HubV
     uint32_t w = (uint32_t) ((v.flow0 + 128) & 0xff) | ((uint32_t) ((v.flow1 + 128) & 0xff) << 8) |
                  ((uint32_t) (v.fline & 0xff) << 16) | ((uint32_t) (v.farr & 0xff) << 24);
     P.hubA[h] = make_uint4(v.rng.lcg, v.rng.uctr, z, w);
+    P.occ[h] = make_uint2(v.occ0, v.occ1);
     P.store[h] = v.store;
     if (v.err) P.err[h] |= v.err;
 }
@@ -503,6 +520,7 @@ __device__ __noinline__ void hub_reset_full(const ChubParams &P, int h, long lon
     v.t = 0;
     v.line0 = s0.line; v.line1 = s1.line;
     v.flow0 = s0.flow; v.flow1 = s1.flow;
+    v.occ0 = s0.occ; v.occ1 = s1.occ;
     v.qn = 0; v.fline = 0; v.farr = 0;
     v.store = c.init_mass;
     P.stats[h] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -563,8 +581,8 @@ struct StationIO {
 };
 template <int TYPE, int Q>
 __device__ __noinline__ StationIO station_step_cp(const ChubParams &P, WarpScratch<Q> &S, const float *tl_s, bool mine, int h,
-                                                  int slot0, int n, int t, int line, uint32_t act_bits, StationIO io) {
-    station_step<TYPE, 1, Q>(P, S, tl_s, mine, h, slot0, n, t, line, act_bits, io.rng, io.err, io.o);
+                                                  int slot0, int n, int t, int line, uint32_t act_bits, uint32_t occ_in, StationIO io) {
+    station_step<TYPE, 1, Q>(P, S, tl_s, mine, h, slot0, n, t, line, act_bits, occ_in, io.rng, io.err, io.o);
     return io;
 }
 
@@ -583,17 +601,26 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     unsigned long long bits;
     {
         float a_m2, a_m1;
-        load_actions(P, reinterpret_cast<float *>(&S.inc_s[0]), (P.ws_bytes - (int) offsetof(WarpScratch<Q>, inc_s)) / 4, h,
+        load_actions(P, reinterpret_cast<float *>(&S.park[0][0][0]), (P.ws_bytes - (int) offsetof(WarpScratch<Q>, park)) / 4, h,
                      active, n0 + n1, bits, a_m2, a_m1);
         S.am[0][threadIdx.x & 31] = a_m2;
         S.am[1][threadIdx.x & 31] = a_m1;
     }
 
-    HubVars v;
-    v.err = 0u; v.t = 0; v.line0 = v.line1 = 0;
-    v.rng.k0 = v.rng.k1 = v.rng.uctr = 0u; v.rng.lcg = 1u;
-    if (active) hub_load(P, h, v);
-    if (active && (P.phase_sync & 4)) {   // start the warp's pile rows on their way from HBM to L2: the scan then waits on L2, not on DRAM
+    // During the stations only the random streams, the time slot and the two queue lengths are needed; the rest of
+    // the hub record stays packed (registers are the scarce resource there) and is unpacked afterwards.
+    HubRng rng;
+    rng.k0 = rng.k1 = rng.uctr = 0u; rng.lcg = 1u;
+    uint32_t az = 0u, aw = 0u, err = 0u;
+    uint2 occ = make_uint2(0u, 0u);
+    if (active) {
+        const uint4 a = P.hubA[h];
+        const uint2 key = __ldg(&P.keys[h]);
+        occ = P.occ[h];
+        rng.k0 = key.x; rng.k1 = key.y; rng.lcg = a.x; rng.uctr = a.y;
+        az = a.z; aw = a.w;
+    }
+    if (active && (P.phase_sync & 4)) {   // optional: start the warp's pile rows on their way from HBM to L2
         const uint4 *q = P.pile + chub_pile_index(h, 0, P.S0 + P.S1);
         for (int i = 0; i < n0; ++i) asm volatile("prefetch.global.L2 [%0];" ::"l"(q + i * 32));
         q += P.S0 * 32;
@@ -601,37 +628,54 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     }
 
     // ---- the two EV stations, station 0 first (Aggregator_Simple.py:141-142); the whole warp takes part ----
-    StationOut s0 = {}, s1 = {};
+    const int lane_ = threadIdx.x & 31;
 #pragma unroll 1
     for (int s = 0; s < 2; ++s) {
-        const int type = c.type[s], n = s ? n1 : n0, slot0 = s ? P.S0 : 0, line = s ? v.line1 : v.line0;
-        const uint32_t abits = s ? (uint32_t) (bits >> n0) : (uint32_t) bits;
+        const int type = c.type[s], n = s ? n1 : n0, slot0 = s ? P.S0 : 0, line = (az >> (8 + 8 * s)) & 0xff, t = az & 0xff;
+        const uint32_t abits = s ? (uint32_t) (bits >> n0) : (uint32_t) bits, occ_s = s ? occ.y : occ.x;
         const bool curve = active && !c.constant;
         StationOut o = {};
         if (P.phase_sync & 1) __syncthreads();   // keep the block's warps in the same code region (instruction cache)
         const bool m_slow = curve && type == CHUB_SLOW, m_fast = curve && type == CHUB_FAST;
-        if (__any_sync(full, m_fast)) station_step<CHUB_FAST, 0, Q>(P, S, tl_s, m_fast, h, slot0, n, v.t, line, abits, v.rng, v.err, o);
-        if (__any_sync(full, m_slow)) station_step<CHUB_SLOW, 0, Q>(P, S, tl_s, m_slow, h, slot0, n, v.t, line, abits, v.rng, v.err, o);
+        if (__any_sync(full, m_fast)) station_step<CHUB_FAST, 0, Q>(P, S, tl_s, m_fast, h, slot0, n, t, line, abits, occ_s, rng, err, o);
+        if (__any_sync(full, m_slow)) station_step<CHUB_SLOW, 0, Q>(P, S, tl_s, m_slow, h, slot0, n, t, line, abits, occ_s, rng, err, o);
         const bool c_slow = active && c.constant && type == CHUB_SLOW, c_fast = active && c.constant && type == CHUB_FAST;
         if (__any_sync(full, c_fast || c_slow)) {
             StationIO io;
-            io.rng = v.rng; io.err = v.err; io.o = o;
-            if (__any_sync(full, c_fast)) io = station_step_cp<CHUB_FAST, Q>(P, S, tl_s, c_fast, h, slot0, n, v.t, line, abits, io);
-            if (__any_sync(full, c_slow)) io = station_step_cp<CHUB_SLOW, Q>(P, S, tl_s, c_slow, h, slot0, n, v.t, line, abits, io);
-            v.rng = io.rng; v.err = io.err; o = io.o;
+            io.rng = rng; io.err = err; io.o = o;
+            if (__any_sync(full, c_fast)) io = station_step_cp<CHUB_FAST, Q>(P, S, tl_s, c_fast, h, slot0, n, t, line, abits, occ_s, io);
+            if (__any_sync(full, c_slow)) io = station_step_cp<CHUB_SLOW, Q>(P, S, tl_s, c_slow, h, slot0, n, t, line, abits, occ_s, io);
+            rng = io.rng; err = io.err; o = io.o;
         }
-        if (s == 0) s0 = o; else s1 = o;
+        // the station's outputs wait in shared memory for the hub section
+        S.park[s][0][lane_] = __float_as_uint(o.mn); S.park[s][1][lane_] = __float_as_uint(o.mx);
+        S.park[s][2][lane_] = __float_as_uint(o.now); S.park[s][3][lane_] = o.occ;
+        S.park[s][4][lane_] = (uint32_t) (o.line & 0xff) | ((uint32_t) (o.flow & 0xff) << 8) | ((uint32_t) o.incomplete << 16);
     }
     if (P.phase_sync & 2) __syncthreads();
     if (!active) return;
-    // what only the hub section needs is fetched now: store mass, exogenous traces, the two analog actions
+    // what only the hub section needs is fetched or unpacked now: store mass, exogenous traces, the two analog actions
+    HubVars v;
+    v.rng = rng; v.err = err;
+    v.t = az & 0xff; v.qn = az >> 24; v.fline = (aw >> 16) & 0xff; v.farr = aw >> 24;
+    StationOut s0, s1;
+    {
+        const uint32_t p0 = S.park[0][4][lane_], p1 = S.park[1][4][lane_];
+        s0.mn = __uint_as_float(S.park[0][0][lane_]); s0.mx = __uint_as_float(S.park[0][1][lane_]);
+        s0.now = __uint_as_float(S.park[0][2][lane_]); s0.occ = S.park[0][3][lane_];
+        s0.line = p0 & 0xff; s0.flow = (int) (signed char) ((p0 >> 8) & 0xff); s0.incomplete = p0 >> 16; s0.number = __popc(s0.occ);
+        s1.mn = __uint_as_float(S.park[1][0][lane_]); s1.mx = __uint_as_float(S.park[1][1][lane_]);
+        s1.now = __uint_as_float(S.park[1][2][lane_]); s1.occ = S.park[1][3][lane_];
+        s1.line = p1 & 0xff; s1.flow = (int) (signed char) ((p1 >> 8) & 0xff); s1.incomplete = p1 >> 16; s1.number = __popc(s1.occ);
+    }
     v.store = P.store[h];
     const long long k = *P.step_index + P.step_offset;
     double pv_t, wd_t, pr_t;
     trace_at(P, h, k, pv_t, wd_t, pr_t);
-    const float a_m2 = S.am[0][threadIdx.x & 31], a_m1 = S.am[1][threadIdx.x & 31];
+    const float a_m2 = S.am[0][lane_], a_m1 = S.am[1][lane_];
     v.line0 = s0.line; v.line1 = s1.line;
     v.flow0 = s0.flow; v.flow1 = s1.flow;
+    v.occ0 = s0.occ; v.occ1 = s1.occ;
 
 // @region hub section
     // ---- electrolyser set-point under the grid limit (evcssp_manager.py:157-180) ----
@@ -809,7 +853,7 @@ static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s) {
     ChubParams p = p0;
     p.ws_bytes = (int) warp_scratch_bytes<Q>(p.S0 > p.S1 ? p.S0 : p.S1);
     // room to stage the warp's 32 action rows behind the parked analog entries, when that stays small
-    const int stage_bytes = (int) offsetof(WarpScratch<Q>, inc_s) + 128 * p.action_stride;
+    const int stage_bytes = (int) offsetof(WarpScratch<Q>, park) + 128 * p.action_stride;
     if (stage_bytes > p.ws_bytes && stage_bytes <= 10240) p.ws_bytes = stage_bytes;
     const size_t smem = (size_t) WARPS * p.ws_bytes;
     auto kern = chub_step_kernel<WARPS, MINB, Q>;
@@ -829,7 +873,7 @@ cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s) {
         case 820: return launch_step_variant<8, 2, 0>(p, s);
         case 2410: return launch_step_variant<24, 1, 0>(p, s);
         case 3210: return launch_step_variant<32, 1, 0>(p, s);
-        default: return launch_step_variant<16, 2, 0>(p, s);
+        default: return launch_step_variant<24, 1, 0>(p, s);
     }
 }
 void chub_launch_reset(const ChubParams &p, cudaStream_t s) {

@@ -10,6 +10,7 @@
 //   hubA[h]                   uint4 {minstd state, U counter, packed1, packed2}
 //   store[h]                  double hydrogen store mass in grams
 //   keys[h]                   uint2  U-stream keys (read only)
+//   occ[h]                    uint2  occupancy masks of the two stations: the step only touches pile rows that hold a car
 //   stats[h], last_stats[h]   float4 {episode return, income, grid energy, incomplete departures}
 //   qsoc[(j) * Hpad + h]      float  FCEV backlog arrival SOCs (cold; touched only when a backlog exists)
 // packed pile word : bits 0-5 stay_time, 6-11 already_stay_time, 12 car, 13 charge, 14 urgent,
@@ -43,6 +44,7 @@ struct ChubParams {
     uint4 *hubA;
     double *store;
     const uint2 *keys;
+    uint2 *occ;                       // per hub: occupancy bit mask of station 0 / station 1 piles (bit i = a car on pile i)
     const int *cls;                   // NULL when n_classes == 1
     float4 *stats, *last_stats;
     uint32_t *err;
