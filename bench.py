@@ -259,6 +259,8 @@ def main():
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_value = H * world * KE / float(te.item())
     err = eng.counters()["error_or"]
+    per = -(-(-(-H // 8)) // 1024) * 1024  # chub_step_host cuts the batch into <= 8 hub ranges of whole blocks
+    host_chunks = -(-H // per)
 
     if rank == 0:
         peak, peak_src = measured_peak()
@@ -278,8 +280,8 @@ def main():
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(H * S * 4),
                     "d2h_bytes_per_step": int(H * (13 * 4 + 4 + 1)), "steps": KE,
-                    "api": "chub_step_host: pinned host actions -> device, step, obs/reward/done -> pinned host"},
-            "gpu_launches": int(launches) * 2 + KE * 2,
+                    "api": "chub_step_host: pinned host actions -> device, step, obs/reward/done -> pinned host, pipelined over %d hub ranges" % host_chunks},
+            "gpu_launches": int(launches) * 2 + KE * (host_chunks + 1),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_hub_step": bytes_per_hub,
                          "kernel": "chub_step_kernel", "kernel_ms": kernel_ms},

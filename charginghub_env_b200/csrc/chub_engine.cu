@@ -43,6 +43,8 @@ struct chub_engine {
     float *obs = nullptr, *reward = nullptr; uint8_t *done = nullptr; double *diag = nullptr; float *st_power = nullptr;
     long long *step_index = nullptr;
     float *actions_stage = nullptr;  // device copy target of chub_step_host
+    cudaStream_t host_streams[3] = {nullptr, nullptr, nullptr};  // chub_step_host pipeline: copy in, step, copy out
+    cudaEvent_t host_events[2 * 16 + 2] = {};
     int trace_len = 0, trace_per_hub = 0;
     bool have_tables = false, have_classes = false, have_traces = false, have_seed = false;
     long long launches = 0;
@@ -58,6 +60,10 @@ static void engine_free(chub_engine *e) {
     cudaSetDevice(e->cfg.device);
     if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
     if (e->graph) cudaGraphDestroy(e->graph);
+    for (cudaStream_t st : e->host_streams)
+        if (st) cudaStreamDestroy(st);
+    for (cudaEvent_t ev : e->host_events)
+        if (ev) cudaEventDestroy(ev);
     void *ptrs[] = {e->pile, e->arrive, e->hubA, e->store, e->keys, e->occ, e->cls, e->stats, e->last_stats, e->err, e->qsoc,
                     e->d_classes, e->d_el, e->lut, e->s2t_lut, e->pv, e->wd, e->price_tr, e->obs, e->reward, e->done, e->diag,
                     e->st_power, e->step_index, e->actions_stage};
@@ -389,6 +395,7 @@ static int fill_params(chub_engine *e, ChubParams &P) {
     if (!e->have_seed) return fail(CHUB_ERR_STATE, "call chub_seed first");
     memset(&P, 0, sizeof P);
     P.H = e->H; P.Hpad = e->Hpad; P.S0 = e->S0; P.S1 = e->S1;
+    P.h_begin = 0; P.h_end = e->H;
     P.n_classes = (int) e->classes.size(); P.action_stride = e->cfg.action_stride;
     P.auto_reset = e->cfg.auto_reset; P.diagnostics = e->cfg.diagnostics;
     P.trace_len = e->trace_len; P.trace_per_hub = e->trace_per_hub;
@@ -440,18 +447,55 @@ extern "C" int chub_step(chub_engine *e, const float *actions_dev, void *stream)
     return CHUB_OK;
 }
 
+// Host-buffer step.  The batch is cut into hub ranges that flow through three streams -- actions host->device,
+// step kernel, obs/reward/done device->host -- so the two PCIe directions and the kernel overlap; hubs are
+// independent, so stepping them range by range is the same computation as one launch.
+#define CHUB_HOST_CHUNKS 8
 extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *obs_host, float *reward_host,
                               uint8_t *done_host, void *stream) {
     if (!e || !actions_host) return fail(CHUB_ERR_ARG, "chub_step_host: null argument");
     CK(cudaSetDevice(e->cfg.device));
     cudaStream_t s = (cudaStream_t) stream;
-    CK(cudaMemcpyAsync(e->actions_stage, actions_host, sizeof(float) * (size_t) e->H * e->cfg.action_stride,
-                       cudaMemcpyHostToDevice, s));
-    int rc = chub_step(e, e->actions_stage, stream);
+    ChubParams P;
+    int rc = fill_params(e, P);
     if (rc) return rc;
-    if (obs_host) CK(cudaMemcpyAsync(obs_host, e->obs, sizeof(float) * (size_t) e->H * CHUB_OBS_DIM, cudaMemcpyDeviceToHost, s));
-    if (reward_host) CK(cudaMemcpyAsync(reward_host, e->reward, sizeof(float) * (size_t) e->H, cudaMemcpyDeviceToHost, s));
-    if (done_host) CK(cudaMemcpyAsync(done_host, e->done, (size_t) e->H, cudaMemcpyDeviceToHost, s));
+    P.actions = e->actions_stage;
+    if (!e->host_streams[0]) {
+        for (int i = 0; i < 3; ++i) CK(cudaStreamCreateWithFlags(&e->host_streams[i], cudaStreamNonBlocking));
+        for (int i = 0; i < 2 * CHUB_HOST_CHUNKS + 2; ++i) CK(cudaEventCreateWithFlags(&e->host_events[i], cudaEventDisableTiming));
+    }
+    cudaStream_t s_in = e->host_streams[0], s_k = e->host_streams[1], s_out = e->host_streams[2];
+    cudaEvent_t *ev_in = e->host_events, *ev_k = e->host_events + CHUB_HOST_CHUNKS;
+    cudaEvent_t ev_fork = e->host_events[2 * CHUB_HOST_CHUNKS], ev_join = e->host_events[2 * CHUB_HOST_CHUNKS + 1];
+    CK(cudaEventRecord(ev_fork, s));           // everything queued on the caller's stream comes first
+    CK(cudaStreamWaitEvent(s_in, ev_fork, 0));
+    CK(cudaStreamWaitEvent(s_k, ev_fork, 0));
+    CK(cudaStreamWaitEvent(s_out, ev_fork, 0));
+    const int A = e->cfg.action_stride;
+    int per = (e->H + CHUB_HOST_CHUNKS - 1) / CHUB_HOST_CHUNKS;
+    per = (per + 1023) / 1024 * 1024;           // whole warps (and whole blocks of any launch shape)
+    for (int c = 0, b = 0; b < e->H; ++c, b += per) {
+        const int n = (b + per <= e->H ? per : e->H - b);
+        CK(cudaMemcpyAsync(e->actions_stage + (size_t) b * A, actions_host + (size_t) b * A, sizeof(float) * (size_t) n * A,
+                           cudaMemcpyHostToDevice, s_in));
+        CK(cudaEventRecord(ev_in[c], s_in));
+        CK(cudaStreamWaitEvent(s_k, ev_in[c], 0));
+        P.h_begin = b; P.h_end = b + n;
+        CK(chub_launch_step(P, s_k));
+        CK(cudaEventRecord(ev_k[c], s_k));
+        CK(cudaStreamWaitEvent(s_out, ev_k[c], 0));
+        if (obs_host) CK(cudaMemcpyAsync(obs_host + (size_t) b * CHUB_OBS_DIM, e->obs + (size_t) b * CHUB_OBS_DIM,
+                                         sizeof(float) * (size_t) n * CHUB_OBS_DIM, cudaMemcpyDeviceToHost, s_out));
+        if (reward_host) CK(cudaMemcpyAsync(reward_host + b, e->reward + b, sizeof(float) * (size_t) n, cudaMemcpyDeviceToHost, s_out));
+        if (done_host) CK(cudaMemcpyAsync(done_host + b, e->done + b, (size_t) n, cudaMemcpyDeviceToHost, s_out));
+    }
+    chub_launch_tick(e->step_index, 1, s_k);    // after the last range: every launch above read the same step index
+    CK(cudaGetLastError());
+    e->launches += 1;
+    CK(cudaEventRecord(ev_join, s_k));
+    CK(cudaStreamWaitEvent(s, ev_join, 0));
+    CK(cudaEventRecord(ev_join, s_out));
+    CK(cudaStreamWaitEvent(s, ev_join, 0));
     CK(cudaStreamSynchronize(s));
     return CHUB_OK;
 }

@@ -551,7 +551,7 @@ __device__ __forceinline__ void load_actions(const ChubParams &P, float *stage, 
     const int h0 = h - lane;
     const int stride = P.action_stride;
     bits = 0ull; a_m2 = 0.0f; a_m1 = 0.0f;
-    const bool staged = (h0 + 32 <= P.H) && (32 * stride <= stage_floats) &&
+    const bool staged = (h0 + 32 <= P.h_end) && (32 * stride <= stage_floats) &&
                         ((reinterpret_cast<uintptr_t>(P.actions) & 15u) == 0);
     const float *src = P.actions + (size_t) h * stride;
     if (staged) {
@@ -593,8 +593,8 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     WarpScratch<Q> &S = *reinterpret_cast<WarpScratch<Q> *>(smem + (threadIdx.x >> 5) * P.ws_bytes);
 
     const unsigned full = 0xffffffffu;
-    const int h = blockIdx.x * (WARPS * 32) + threadIdx.x;
-    const bool active = h < P.H;
+    const int h = P.h_begin + blockIdx.x * (WARPS * 32) + threadIdx.x;
+    const bool active = h < P.h_end;
     const int ci = (active && P.cls) ? __ldg(&P.cls[h]) : 0;
     const ChubClass &c = P.classes[ci];
     const int n0 = c.n[0], n1 = c.n[1];
@@ -861,7 +861,7 @@ static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s) {
     cudaError_t r = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
     if (r != cudaSuccess) return r;
     const int block = WARPS * 32;
-    kern<<<(p.H + block - 1) / block, block, smem, s>>>(p);
+    kern<<<(p.h_end - p.h_begin + block - 1) / block, block, smem, s>>>(p);
     return cudaSuccess;
 }
 cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s) {

@@ -33,6 +33,7 @@ __host__ __device__ inline size_t chub_pile_index(int h, int slot, int S) {
 
 struct ChubParams {
     int H, Hpad, S0, S1;
+    int h_begin, h_end;               // hub range of this launch (h_begin a multiple of 32); the whole batch by default
     int n_classes, action_stride, auto_reset, diagnostics;
     int trace_len, trace_per_hub;
     int block, phase_sync;            // launch shape of the step kernel (see chub_launch_step); phase_sync: block barriers between code regions

@@ -136,3 +136,34 @@ def test_masked_reset(tables):
     torch.cuda.synchronize()
     C.compare_state(eng, orc, 0, mm, C.SCALE)
     assert not mm, str(mm)
+
+
+@pytest.mark.parametrize("stride,offset,H", [(47, 0, 100), (100, 0, 96), (47, 1, 64), (49, 3, 33)])
+def test_action_row_layouts(tables, stride, offset, H):
+    """The warp stages its 32 action rows in shared memory when it can; a partial last warp, a matrix too wide to
+    stage and a base pointer that is not 16-byte aligned take the direct path.  All must read the same actions."""
+    import torch
+    from charginghub_env_b200 import HubEngine
+    from oracle import oracle as O
+    rs = np.random.RandomState(11)
+    T = 12
+    eng = HubEngine(H, [C.DEFAULT_KW], device=0, diagnostics=True, tables=tables, seed=77, action_stride=stride)
+    pv, wd, price = C.synth_traces(tables, T + 1, rs, None)
+    eng.set_traces(pv, wd, price)
+    orc = O.Oracle(H, [C.DEFAULT_KW], tables=C.oracle_tables(tables))
+    orc.seed_base(77, 0)
+    eng.reset()
+    orc.reset(pv[0], wd[0], price[0])
+    buf = torch.empty(H * stride + 8, device="cuda", dtype=torch.float32)
+    mm = C.Mismatch()
+    for t in range(T):
+        a = rs.uniform(-1, 1, (H, stride)).astype(np.float32)
+        view = buf[offset:offset + H * stride].view(H, stride)
+        view.copy_(torch.from_numpy(a))
+        obs, rew, done = eng.step(view)
+        orc.step(a, pv[t + 1], wd[t + 1], price[t + 1])
+        torch.cuda.synchronize()
+        C.compare_state(eng, orc, t + 1, mm, C.SCALE, obs=obs.cpu().numpy(), reward=rew.cpu().numpy(),
+                        done=done.cpu().numpy())
+    assert not mm, str(mm)
+    assert eng.counters()["error_or"] == 0

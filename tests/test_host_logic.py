@@ -64,3 +64,51 @@ def test_packaged_tables(tables):
     cdf = tables["arrival_cdf"]
     assert (np.diff(cdf, axis=1) >= -1e-6).all() and cdf.max() <= 1.0 + 1e-6  # rows are CDFs
     assert abs(tables["price_mean"] - tables["price"].mean()) < 1e-15
+
+
+# ---- arithmetic facts the step kernel relies on (charginghub_env_b200/csrc/chub_kernels.cu) ----
+
+def test_action_binarisation_is_a_single_compare():
+    """action_to_real on float32: on iff (a + 1) / 2 >= 0.5 (evcssp_manager.py:384-404).  The kernel tests
+    a >= -2^-25 instead; the two agree on every float32, checked here around the boundary and on specials."""
+    edge = np.float32(-2.0 ** -25)
+    xs = [edge]
+    for _ in range(64):
+        xs.append(np.nextafter(xs[-1], np.float32(-1), dtype=np.float32))
+    up = edge
+    for _ in range(64):
+        up = np.nextafter(up, np.float32(1), dtype=np.float32)
+        xs.append(up)
+    xs += [np.float32(v) for v in (0.0, -0.0, 1.0, -1.0, 1e-30, -1e-30, 3e38, -3e38, np.inf, -np.inf, np.nan, -1e-8, -3e-8)]
+    rs = np.random.RandomState(0)
+    xs = np.concatenate([np.array(xs, np.float32), rs.uniform(-1, 1, 200000).astype(np.float32),
+                         (rs.uniform(-1, 1, 200000) * 1e-7).astype(np.float32)])
+    with np.errstate(invalid="ignore", over="ignore"):
+        ref = ((xs + np.float32(1.0)) / np.float32(2.0)) >= np.float32(0.5)
+        fast = xs >= np.float32(-2.0 ** -25)
+    assert np.array_equal(ref, fast)
+
+
+def test_curve_breakpoints_are_not_float32_values():
+    """The curves' segment tests mix '<' and '<=' against double constants (CHS.hpp:503-509, 559-578, 629-635,
+    649-657).  None of the constants is a float32 value, so both comparisons pick the same side for every float32
+    time and one segment index decides soc and power together (slow_seg / fast_seg in chub_device.cuh)."""
+    for v in (2.33 * 4, 3.67 * 4, 28.7 / 15, 51.2 / 15):
+        assert float(np.float32(v)) != v
+
+
+def test_charging_power_is_never_negative():
+    """The sign bit of the posted pile power carries the urgency flag to the station sums, which is only sound
+    if no curve ever returns a negative power (or -0.0).  Checked on the oracle's curves over every time the
+    step can produce: t = s2t(soc) + 1 in [1, t_max + 1], and t = s2t(arrival soc) for add_car."""
+    for which, tmax in ((0, 14.68), (3, 51.2 / 15)):
+        t = np.linspace(0.0, tmax + 1.5, 2000001).astype(np.float32)
+        for cp in (False, True):
+            p = O.curve_batch(which, t, constant_power=cp)
+            assert not np.signbit(p).any() and np.isfinite(p).all()
+
+
+def test_minstd_jump_ahead_constants():
+    """chub_minstd_jump(x, A_k) == k plain steps (include/chub_rng.h), checked through a pure-Python mirror."""
+    m, a = 2147483647, 16807
+    assert (a * a) % m == 282475249 and pow(a, 3, m) == 1622650073 and pow(a, 4, m) == 984943658
