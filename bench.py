@@ -214,8 +214,15 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def gather_stats():  # the one collective of the path: episode statistics gathered once per rollout
+        if world > 1:
+            stats = eng.tensor("last_stats")
+            gathered = [torch.empty_like(stats) for _ in range(world)] if rank == 0 else None
+            dist.gather(stats, gathered, dst=0)
+
     for i in range(W):
         eng.step(pool[i % npool])
+    gather_stats()  # warm-up includes the collective: NCCL sets its channels up on first use
     barrier()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -226,10 +233,7 @@ def main():
     ev0.record()
     for i in range(K):
         eng.step(pool[i % npool])
-    if world > 1:  # the one collective of the path: episode statistics gathered once per rollout
-        stats = eng.tensor("last_stats")
-        gathered = [torch.empty_like(stats) for _ in range(world)] if rank == 0 else None
-        dist.gather(stats, gathered, dst=0)
+    gather_stats()
     ev1.record()
     barrier()
     ms = ev0.elapsed_time(ev1)
