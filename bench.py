@@ -110,6 +110,19 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_traffic(workload, H):
+    """DRAM bytes of one step-kernel launch from the committed ncu capture (profiles/), or None."""
+    p = os.path.join(ROOT, "profiles", "r01f_traffic.json")
+    try:
+        d = json.load(open(p))
+        if d["workload"] == workload and d["hubs"] == H:
+            return d["busy_hour_bytes"], {"busy_hour": d["busy_hour_bytes"], "quiet_hour": d["quiet_hour_bytes"],
+                                          "source": "profiles/r01f_traffic.json (ncu --set full, one launch)"}
+    except Exception:
+        pass
+    return None, None
+
+
 def cpu_port_rate(tabs, classes, hub_class, H, T, threads, stride):
     """hub-steps/s of the C restatement (oracle/) on `threads` host threads; a bounded sample."""
     from oracle import oracle as O
@@ -271,6 +284,7 @@ def main():
         bytes_per_hub = eng.algorithmic_bytes(0) if len(wl["classes"]) == 1 else float(
             np.mean([2 * (16 * sum(c["station_list"]) + 80) + 4 * (sum(c["station_list"]) + 2) + 57
                      for c in wl["classes"]]))
+        traffic, traffic_detail = measured_traffic(args.workload, H)
         kernel_ms = ms / K  # this rank's average step duration (step kernel + 1-thread tick), CUDA events
         achieved = bytes_per_hub * H / (kernel_ms * 1e-3) / 1e9
         line = {
@@ -287,7 +301,7 @@ def main():
                     "api": "chub_step_host: pinned host actions -> device, step, obs/reward/done -> pinned host, pipelined over %d hub ranges" % host_chunks},
             "gpu_launches": int(launches) * 2 + KE * (host_chunks + 1),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_hub_step": bytes_per_hub,
+                         "traffic": traffic, "traffic_detail": traffic_detail, "peak_source": peak_src, "algorithmic_bytes_per_hub_step": bytes_per_hub,
                          "kernel": "chub_step_kernel", "kernel_ms": kernel_ms},
             "hub_error_bits": int(err),
         }
