@@ -21,6 +21,9 @@
 struct ChubConst {
     float renege[16];      // (float)(0.1 * logf(i + 1))            CHS.hpp:1287
     float balk[64];        // expf((float)-(0.01 * k))               CHS.hpp:1299
+    // the same two tests on the integer draw r = rand() % 1000 (u = r / 999.f is increasing in r):
+    //   u >  renege[w]  <=>  r >  renege_k[w]        u <= balk[j]  <=>  r <= balk_k[j]
+    short renege_k[16], balk_k[64];
     double price[96];      // price_after_MAD_96                     Aggregator_Simple.py:9-15
     double time_sin[96];   // sin(2 pi t / 96)                       evcssp_manager.py:319-320
     double price_mean, price_std, r_price_std;
@@ -56,7 +59,15 @@ struct ChubClass {
 
 #ifdef CHUB_KERNEL_TU  // device code below is compiled only into chub_kernels.cu
 __constant__ ChubConst kC;
-__device__ ChubLogEntry kLogTab[CHUB_LOG_N];  // reduction table of chub_log (global memory: lanes index it divergently)
+__device__ ChubLogEntry kLogTab[CHUB_LOG_N];  // reduction table of chub_log (lanes index it divergently)
+// The step kernel keeps a copy at the start of its dynamic shared memory (a 16-byte gather from there is two
+// instructions and a short-scoreboard wait); the reset kernel reads the global copy.  LT selects which.
+extern __shared__ __align__(16) unsigned char chub_smem[];
+template <int LT>
+__device__ __forceinline__ const ChubLogEntry *log_tab() {
+    if (LT) return reinterpret_cast<const ChubLogEntry *>(chub_smem);
+    return kLogTab;
+}
 
 // ---------------------------------------------------------------------------------------------
 // per-hub random streams (include/chub_rng.h)
@@ -116,6 +127,7 @@ __device__ __forceinline__ float canon_f(uint32_t &lcg) {
 // mk_soc (CHS.hpp:804-814): std::normal_distribution<double>(7, 3)(e) on a FRESH distribution object --
 // Marsaglia polar, second variate discarded (bits/random.tcc:1811-1844) -- clamped and mapped to an SOC.
 // Returns {soc bits, new minstd state}.
+template <int LT>
 __device__ __noinline__ uint2 draw_mk_soc(uint32_t lcg) {
     // The accept/reject walk only needs to know whether x^2 + y^2 <= 1.  With c = (lo + hi (2^31 - 2)) / (2^31 - 2)^2
     // = hi / (2^31 - 2) to within 5e-10 (hi = the second state of the pair, minus 1), an fp32 estimate of r2 is good
@@ -140,7 +152,7 @@ __device__ __noinline__ uint2 draw_mk_soc(uint32_t lcg) {
     const double x = 2.0 * canon_d_of(chub_minstd_next(s0), chub_minstd_jump(s0, CHUB_MINSTD_A2)) - 1.0;
     const double y = 2.0 * canon_d_of(chub_minstd_jump(s0, CHUB_MINSTD_A3), lcg) - 1.0;
     const double r2 = x * x + y * y;
-    double mult = sqrt(chub_div(-2.0 * chub_log(r2, kLogTab), r2));
+    double mult = sqrt(chub_div(-2.0 * chub_log(r2, log_tab<LT>()), r2));
     float de = (float) ((y * mult) * 3.0 + 7.0);
     de = fminf(fmaxf(de, 1.0f), 10.0f);
     return make_uint2(__float_as_uint((float) (75.0 - 5.0 * (double) de)), lcg);
@@ -148,6 +160,7 @@ __device__ __noinline__ uint2 draw_mk_soc(uint32_t lcg) {
 // float normal with unit-free (mean, sd) (CHS.hpp:819-820, 833-834).  logf is taken as the correctly
 // rounded fp32 log (fp64 log narrowed), which is what glibc's logf returns except on rare hard cases.
 // Returns {value bits, new minstd state}.
+template <int LT>
 __device__ __noinline__ uint2 draw_normal_f(uint32_t lcg, float mean, float sd) {
     float x, y, r2;
     do {
@@ -155,25 +168,27 @@ __device__ __noinline__ uint2 draw_normal_f(uint32_t lcg, float mean, float sd) 
         y = 2.0f * canon_f(lcg) - 1.0f;
         r2 = x * x + y * y;
     } while (r2 > 1.0f || r2 == 0.0f);
-    float lg = (float) chub_log((double) r2, kLogTab);
+    float lg = (float) chub_log((double) r2, log_tab<LT>());
     float mult = sqrtf(-2.0f * lg / r2);
     float ret = y * mult;
     return make_uint2(__float_as_uint(ret * sd + mean), lcg);
 }
 
+template <int LT = 0>
 __device__ __forceinline__ float rng_mk_soc(HubRng &r) {
-    uint2 v = draw_mk_soc(r.lcg);
+    uint2 v = draw_mk_soc<LT>(r.lcg);
     r.lcg = v.y;
     return __uint_as_float(v.x);
 }
+template <int LT = 0>
 __device__ __forceinline__ int rng_late_time(HubRng &r) {  // CHS.hpp:816-830 ("slow" for both pile types)
-    uint2 v = draw_normal_f(r.lcg, 2.0f, 2.0f);
+    uint2 v = draw_normal_f<LT>(r.lcg, 2.0f, 2.0f);
     r.lcg = v.y;
     int d = (int) roundf(__uint_as_float(v.x));
     return d > 0 ? d : 0;
 }
 __device__ __forceinline__ int rng_init_cars(HubRng &r, int mu) {  // CHS.hpp:832-842, theta 3
-    uint2 v = draw_normal_f(r.lcg, (float) mu, 1.0f);
+    uint2 v = draw_normal_f<0>(r.lcg, (float) mu, 1.0f);
     r.lcg = v.y;
     int t = (int) roundf(__uint_as_float(v.x));
     return min(max(t, mu - 3), mu + 3);
@@ -201,7 +216,9 @@ __device__ __forceinline__ float slow_s2t(float s) {
 // not fp32 values, so "<" and "<=" select the same side and one segment index decides both outputs:
 //   SEG 0: t < 2.33*4 (quartics)      SEG 1: otherwise (log / rational, or the flat tail past 3.67*4)
 // The caller sorts piles by segment so that a warp runs ONE of the two bodies, not both.
-__device__ __forceinline__ int slow_seg(float t) { return (double) t < 2.33 * 4 ? 0 : 1; }
+// (double) t < 2.33 * 4 for a float t is t < the smallest float above that double (tests/test_host_logic.py)
+#define CHUB_SLOW_SEG_THR 0x1.2a3d72p+3f
+__device__ __forceinline__ int slow_seg(float t) { return t < CHUB_SLOW_SEG_THR ? 0 : 1; }
 template <int SEG>
 __device__ __forceinline__ void slow_step(float t, float &soc, float &power) {
     const double y = (double) (t * 0.25f);  // charge_time / 4 is exact in fp32
@@ -210,7 +227,7 @@ __device__ __forceinline__ void slow_step(float t, float &soc, float &power) {
         ch = (float) (y * fma(fma(fma(fma(-0.0004112, y, 0.0023025), y, 0.03562 / 3), y, 0.011895), y, 6.007));
         power = (float) fma(fma(fma(fma(-0.002056, y, 0.00921), y, 0.03562), y, 0.02379), y, 6.007);
     } else if ((double) t <= 3.67 * 4) {
-        ch = (float) (-4.041 * y + 19.140115 * chub_log(fabs(y - 0.485), kLogTab) + 11.943306312699628);
+        ch = (float) (-4.041 * y + 19.140115 * chub_log(fabs(y - 0.485), log_tab<1>()) + 11.943306312699628);
         power = (float) chub_div(-4.041 * y + 21.1, y - 0.485);
     } else {
         ch = kC.slow_c2_end;
@@ -230,7 +247,10 @@ __device__ __forceinline__ float slow_t2p(float t) {
 __device__ __forceinline__ float fast_s2t(float s) {
     if (s <= 0.0f) return 0.0f;
     if (s >= 100.0f) return (float) (51.2 / 15);
-    float zf = (s - 61.43f) / 31.48f;  // norm_soc: fp32 arithmetic
+    // norm_soc: fp32 arithmetic.  a / 31.48f as two fmas with the rounded reciprocal: equal to the IEEE quotient for
+    // every float |a| in [2^-60, 128] (tools/verify_divf.c, exhaustive); a = s - 61.43f is 0 or >= 2^-19 in magnitude
+    const float za = s - 61.43f, zq = za * (1.0f / 31.48f);
+    const float zf = fmaf(fmaf(-zq, 31.48f, za), 1.0f / 31.48f, zq);
     double z = (double) zf, z2 = z * z;
     // p4*x and q3*x are fp32 products in the reference (float locals times a float argument)
     double p4z = (double) (-62.97f * zf), q3z = (double) (-50.12f * zf);
@@ -243,7 +263,8 @@ __device__ __forceinline__ float fast_aa2(double x) {
     return (float) (p + (double) kC.fast_aa2_c);
 }
 // SEG 0: t < 28.7/15 (exponential part)   SEG 1: otherwise (polynomial part, or full past 51.2/15); t >= 1
-__device__ __forceinline__ int fast_seg(float t) { return (double) t < 28.7 / 15 ? 0 : 1; }
+#define CHUB_FAST_SEG_THR 0x1.e9d038p+0f
+__device__ __forceinline__ int fast_seg(float t) { return t < CHUB_FAST_SEG_THR ? 0 : 1; }
 template <int SEG>
 __device__ __forceinline__ void fast_step(float t, float &soc, float &power) {
     const double x = (double) (t * 15.0f);

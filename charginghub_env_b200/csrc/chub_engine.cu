@@ -267,6 +267,19 @@ extern "C" int chub_set_tables(chub_engine *e, const chub_tables *t) {
     memset(&c, 0, sizeof c);
     for (int i = 0; i < 16; ++i) c.renege[i] = (float) (0.1 * logf((float) (i + 1)));
     for (int k = 0; k < 64; ++k) c.balk[k] = expf((float) -(0.01 * k));
+    {   // integer thresholds: the largest r in 0..999 with uniform_rand(0,1) = r/999.f*(1-0)+0 <= table value (-1 if none)
+        auto thr = [](float v) {
+            int best = -1;
+            for (int r = 0; r < 1000; ++r) {
+                volatile float tr = (float) r / 999.0f;
+                volatile float u = tr * 1.0f + 0.0f;
+                if (u <= v) best = r;
+            }
+            return (short) best;
+        };
+        for (int i = 0; i < 16; ++i) c.renege_k[i] = thr(c.renege[i]);
+        for (int k = 0; k < 64; ++k) c.balk_k[k] = thr(c.balk[k]);
+    }
     memcpy(c.price, t->price, sizeof c.price);
     memcpy(c.time_sin, t->time_sin, sizeof c.time_sin);
     c.price_mean = t->price_mean;

@@ -47,8 +47,7 @@ __device__ __forceinline__ StationOut station_reset(const ChubParams &P, int h, 
     const int in_car = rng_init_cars(rng, n / 2);
     int true_in = 0;
     for (int k = 0; k < in_car; ++k) {  // balking against an empty line (CHS.hpp:1294-1304)
-        float a = rng_u01(rng);
-        if (a <= kC.balk[min(k, 63)] && k <= n) true_in += 1;
+        if (rng_u1000(rng) <= (int) kC.balk_k[min(k, 63)] && k <= n) true_in += 1;
     }
     o.flow = (TYPE == CHUB_SLOW) ? true_in : in_car;  // the slow/fast asymmetry, CHS.hpp:1306 vs 1617
     const int assigned = min(o.flow, n);
@@ -191,11 +190,11 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
         const int in_car = (int) roundf((TYPE == CHUB_FAST ? 0.15f : 0.1f) * 0.2f * (float) N);
         int kept = 0;
         for (int w = 0; w < line_in; ++w) {  // reneging: keep if u > 0.1*logf(w+1)
-            if (rng_u01(rng) > kC.renege[w]) kept += 1;
+            if (rng_u1000(rng) > (int) kC.renege_k[w]) kept += 1;
         }
         int true_in = 0;
         for (int k = 0; k < in_car; ++k) {   // balking: stay if u <= expf(-0.01*(line+k)) and k <= n
-            if (rng_u01(rng) <= kC.balk[min(kept + k, 63)] && k <= n) true_in += 1;
+            if (rng_u1000(rng) <= (int) kC.balk_k[min(kept + k, 63)] && k <= n) true_in += 1;
         }
         flow = (TYPE == CHUB_SLOW) ? true_in : in_car;  // the slow/fast asymmetry, CHS.hpp:1306 vs 1617
         want = kept + flow;
@@ -227,12 +226,11 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
         const int i = inext;
         rows &= rows - 1u;
         inext = __ffs(rows) - 1;
-        nxt = make_uint4(0u, 0u, 0u, 0u);
         if (rows && ((occ >> inext) & 1u)) nxt = rp[inext * 32];
         int seg = -1;
         float tt = 0.0f;
         const uint32_t w = r.w, bit = 1u << i;
-        if (w & PW_CAR) {                            // piles this lane did not load read as w == 0
+        if (occ & bit) {                             // a car is on this pile of my hub (else r is stale: not loaded)
             car_mask |= bit;
             const int left = (int) PW_STAY(w) - (int) PW_ALREADY(w) - 1;
             if (left <= 0) dep_mask |= bit;
@@ -300,12 +298,12 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
         while (m) {
             const int i = __ffs(m) - 1;
             m &= m - 1u;
-            const float arrive = rng_mk_soc(rng);                 // E
+            const float arrive = rng_mk_soc<1>(rng);              // E
             const uint32_t tu = (uint32_t) rng_u1000(rng);        // U  (target = u/999*20+80)
             const float tsoc = curve_s2t<TYPE, CP>(arrive);
             const float needed = __ldg(&tlut[tu]) - tsoc;
             const int must_needed = (int) ceilf(needed);          // calculate_min_charging_time
-            int stay = must_needed + rng_late_time(rng);          // E
+            int stay = must_needed + rng_late_time<1>(rng);       // E
             const float power = curve_t2p<TYPE, CP>(tsoc);
             int cn = needed > 0.0f ? must_needed : 0;
             if (stay > 63 || stay < 1 || cn > 31) {
@@ -588,9 +586,13 @@ __device__ __noinline__ StationIO station_step_cp(const ChubParams &P, WarpScrat
 
 template <int WARPS, int MINB, int Q>
 __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __grid_constant__ ChubParams P) {
-    extern __shared__ __align__(16) unsigned char smem[];
+    unsigned char *const smem = chub_smem;
     const float *tl_s = nullptr;
-    WarpScratch<Q> &S = *reinterpret_cast<WarpScratch<Q> *>(smem + (threadIdx.x >> 5) * P.ws_bytes);
+    // the first 2 KB of shared memory hold the log table (chub_device.cuh log_tab<1>), then one scratch area per warp
+    for (int i = threadIdx.x; i < CHUB_LOG_N * 4; i += WARPS * 32)
+        reinterpret_cast<uint32_t *>(smem)[i] = reinterpret_cast<const uint32_t *>(kLogTab)[i];
+    __syncthreads();
+    WarpScratch<Q> &S = *reinterpret_cast<WarpScratch<Q> *>(smem + CHUB_LOG_N * 16 + (threadIdx.x >> 5) * P.ws_bytes);
 
     const unsigned full = 0xffffffffu;
     const int h = P.h_begin + blockIdx.x * (WARPS * 32) + threadIdx.x;
@@ -855,7 +857,7 @@ static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s) {
     // room to stage the warp's 32 action rows behind the parked analog entries, when that stays small
     const int stage_bytes = (int) offsetof(WarpScratch<Q>, park) + 128 * p.action_stride;
     if (stage_bytes > p.ws_bytes && stage_bytes <= 10240) p.ws_bytes = stage_bytes;
-    const size_t smem = (size_t) WARPS * p.ws_bytes;
+    const size_t smem = CHUB_LOG_N * 16 + (size_t) WARPS * p.ws_bytes;
     auto kern = chub_step_kernel<WARPS, MINB, Q>;
     // per device and cheap; set on every launch so that engines on several devices of one process all get it
     cudaError_t r = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);

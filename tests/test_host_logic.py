@@ -112,3 +112,16 @@ def test_minstd_jump_ahead_constants():
     """chub_minstd_jump(x, A_k) == k plain steps (include/chub_rng.h), checked through a pure-Python mirror."""
     m, a = 2147483647, 16807
     assert (a * a) % m == 282475249 and pow(a, 3, m) == 1622650073 and pow(a, 4, m) == 984943658
+
+
+def test_segment_thresholds_as_float32():
+    """slow_seg / fast_seg compare the float time with a float constant; it must order every float exactly as the
+    reference's double comparison does (CHUB_*_SEG_THR in csrc/chub_device.cuh)."""
+    import os, re
+    src = open(os.path.join(os.path.dirname(__file__), "..", "charginghub_env_b200", "csrc", "chub_device.cuh")).read()
+    for name, dbl in (("CHUB_SLOW_SEG_THR", 2.33 * 4), ("CHUB_FAST_SEG_THR", 28.7 / 15)):
+        lit = re.search(r"#define %s (\S+)f\b" % name, src).group(1)
+        thr = np.float32(float.fromhex(lit))
+        assert float(thr) == float.fromhex(lit)           # the literal is a float32 value
+        below = np.nextafter(thr, np.float32(-np.inf))
+        assert float(thr) >= dbl and float(below) < dbl     # smallest float not below the double
