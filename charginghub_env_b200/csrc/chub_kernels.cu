@@ -120,6 +120,7 @@ __device__ __forceinline__ StationOut station_reset_any(const ChubParams &P, int
 // Per-warp scratch lives in shared memory (WarpScratch); warps never synchronise with each other.
 // @region scratch
 #define LA_RING 64    // >= 31 waiting + 32 appended per scanned row; a batch is up to 32 items
+#define CHUB_SMEM_TABLES (CHUB_LOG_N * 16 + 8000)   // log table + s2t(target) tables ahead of the warps' scratch
 template <int Q>
 struct WarpScratch {
     float am[2][32];                  // the two analog action entries of each hub, parked here during the stations
@@ -150,7 +151,7 @@ __device__ __forceinline__ void flat_car_step(const ChubParams &P, WarpScratch<Q
         curve_step<TYPE, CP, SEG>(tt, soc, power);            // car_step, CHS.hpp:900-905 / 1065-1070
         const float tsoc = curve_s2t<TYPE, CP>(soc);
         const uint32_t tu = PW_TU(w);
-        const float needed = __ldg(&tlut[tu]) - tsoc;         // calculate_needed, CHS.hpp:879-898
+        const float needed = tlut[tu] - tsoc;                 // calculate_needed, CHS.hpp:879-898
         const int cn = needed > 0.0f ? (int) ceilf(needed) : 0;
         const int left = (int) PW_STAY(w) - (int) PW_ALREADY(w) - 1;
         uint4 r = make_uint4(0u, 0u, 0u, 0u);
@@ -179,8 +180,8 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
     const int lane = threadIdx.x & 31;
     const int h0 = h - lane;
     const int n = mine ? n_in : 0;
-    const float *tlut = P.s2t_lut + (CP * 2 + TYPE) * 1000;   // 4 KB, L1 resident
-    (void) tl_s;
+    // s2t(target) of the 1000 possible targets: shared-memory copy for curve charging, global (L1) for constant power
+    const float *tlut = CP ? P.s2t_lut + (2 + TYPE) * 1000 : tl_s + TYPE * 1000;
     S.inc_s[lane] = 0u;
 
     // ---- station-level draws of receive_car (CHS.hpp:1272-1306), before any per-car draw ----
@@ -210,7 +211,7 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
     const uint32_t lt = (1u << lane) - 1u;
     uint32_t car_mask = 0u, chg_mask = 0u, dep_mask = 0u;
     int incomplete = 0;
-    int tail0 = 0, tail1 = 0, head0 = 0, head1 = 0;  // warp-uniform ring positions (taken mod LA_RING); count = tail - head
+    int cnt0 = 0, cnt1 = 0, head0 = 0, head1 = 0;    // warp-uniform ring state: first waiting slot (mod LA_RING), items waiting
     // Only rows on which some hub of the warp has a car are visited, and a lane only loads the piles its own
     // occupancy mask names: the traffic of a quiet hour is proportional to the cars, not to the pile count.
     const uint32_t occ = mine ? occ_in : 0u;
@@ -253,22 +254,22 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
         const int need = rows ? 32 : 1;              // the last occupied row also flushes the rings
         if ((m0 | m1) != 0u || need == 1) {          // otherwise nobody charges on this row: nothing to queue
             if (seg >= 0) {
-                const int sl = seg * LA_RING + ((seg == 0 ? tail0 + __popc(m0 & lt) : tail1 + __popc(m1 & lt)) & (LA_RING - 1));
+                const int sl = seg * LA_RING + ((seg == 0 ? head0 + cnt0 + __popc(m0 & lt) : head1 + cnt1 + __popc(m1 & lt)) & (LA_RING - 1));
                 (&S.la_t[0][0])[sl] = __float_as_uint(tt);
                 (&S.la_w[0][0])[sl] = w;
                 (&S.la_id[0][0])[sl] = (uint32_t) lane | ((uint32_t) i << 5);
             }
-            tail0 += __popc(m0);
-            tail1 += __popc(m1);
-            while (tail0 - head0 >= need) {
-                const int c = min(tail0 - head0, 32);
+            cnt0 += __popc(m0);
+            cnt1 += __popc(m1);
+            while (cnt0 >= need) {
+                const int c = min(cnt0, 32);
                 flat_car_step<TYPE, CP, 0, Q>(P, S, tlut, pile0, head0, c);
-                head0 += c;
+                head0 += c; cnt0 -= c;
             }
-            while (!CP && tail1 - head1 >= need) {
-                const int c = min(tail1 - head1, 32);
+            while (!CP && cnt1 >= need) {
+                const int c = min(cnt1, 32);
                 flat_car_step<TYPE, CP, 1, Q>(P, S, tlut, pile0, head1, c);
-                head1 += c;
+                head1 += c; cnt1 -= c;
             }
         }
     }
@@ -301,7 +302,7 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
             const float arrive = rng_mk_soc<1>(rng);              // E
             const uint32_t tu = (uint32_t) rng_u1000(rng);        // U  (target = u/999*20+80)
             const float tsoc = curve_s2t<TYPE, CP>(arrive);
-            const float needed = __ldg(&tlut[tu]) - tsoc;
+            const float needed = tlut[tu] - tsoc;
             const int must_needed = (int) ceilf(needed);          // calculate_min_charging_time
             int stay = must_needed + rng_late_time<1>(rng);       // E
             const float power = curve_t2p<TYPE, CP>(tsoc);
@@ -587,12 +588,14 @@ __device__ __noinline__ StationIO station_step_cp(const ChubParams &P, WarpScrat
 template <int WARPS, int MINB, int Q>
 __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __grid_constant__ ChubParams P) {
     unsigned char *const smem = chub_smem;
-    const float *tl_s = nullptr;
+    const float *tl_s = reinterpret_cast<const float *>(chub_smem + CHUB_LOG_N * 16);
     // the first 2 KB of shared memory hold the log table (chub_device.cuh log_tab<1>), then one scratch area per warp
     for (int i = threadIdx.x; i < CHUB_LOG_N * 4; i += WARPS * 32)
         reinterpret_cast<uint32_t *>(smem)[i] = reinterpret_cast<const uint32_t *>(kLogTab)[i];
+    float *const tl_w = reinterpret_cast<float *>(smem + CHUB_LOG_N * 16);   // then the two curve-charging s2t(target) tables
+    for (int i = threadIdx.x; i < 2000; i += WARPS * 32) tl_w[i] = __ldg(&P.s2t_lut[i]);
     __syncthreads();
-    WarpScratch<Q> &S = *reinterpret_cast<WarpScratch<Q> *>(smem + CHUB_LOG_N * 16 + (threadIdx.x >> 5) * P.ws_bytes);
+    WarpScratch<Q> &S = *reinterpret_cast<WarpScratch<Q> *>(smem + CHUB_SMEM_TABLES + (threadIdx.x >> 5) * P.ws_bytes);
 
     const unsigned full = 0xffffffffu;
     const int h = P.h_begin + blockIdx.x * (WARPS * 32) + threadIdx.x;
@@ -857,7 +860,7 @@ static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s) {
     // room to stage the warp's 32 action rows behind the parked analog entries, when that stays small
     const int stage_bytes = (int) offsetof(WarpScratch<Q>, park) + 128 * p.action_stride;
     if (stage_bytes > p.ws_bytes && stage_bytes <= 10240) p.ws_bytes = stage_bytes;
-    const size_t smem = CHUB_LOG_N * 16 + (size_t) WARPS * p.ws_bytes;
+    const size_t smem = CHUB_SMEM_TABLES + (size_t) WARPS * p.ws_bytes;
     auto kern = chub_step_kernel<WARPS, MINB, Q>;
     // per device and cheap; set on every launch so that engines on several devices of one process all get it
     cudaError_t r = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
