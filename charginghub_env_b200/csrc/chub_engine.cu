@@ -42,6 +42,7 @@ struct chub_engine {
     uint16_t *lut = nullptr; float *s2t_lut = nullptr; double *pv = nullptr, *wd = nullptr, *price_tr = nullptr;
     float *obs = nullptr, *reward = nullptr; uint8_t *done = nullptr; double *diag = nullptr; float *st_power = nullptr;
     long long *step_index = nullptr;
+    int num_sms = 0;
     float *actions_stage = nullptr;  // device copy target of chub_step_host
     cudaStream_t host_streams[3] = {nullptr, nullptr, nullptr};  // chub_step_host pipeline: copy in, step, copy out
     cudaEvent_t host_events[2 * 16 + 2] = {};
@@ -96,6 +97,8 @@ extern "C" int chub_create(const chub_config *cfg, chub_engine **out) {
     e->cfg = *cfg;
     e->H = cfg->n_hubs;
     e->Hpad = (cfg->n_hubs + 31) / 32 * 32;
+    cudaDeviceGetAttribute(&e->num_sms, cudaDevAttrMultiProcessorCount, cfg->device);
+    if (e->num_sms <= 0) e->num_sms = 148;
     const size_t Hp = (size_t) e->Hpad;
     cudaError_t r = cudaSuccess;
     auto A = [&](cudaError_t x) { if (r == cudaSuccess) r = x; };
@@ -412,7 +415,7 @@ static int fill_params(chub_engine *e, ChubParams &P) {
     P.n_classes = (int) e->classes.size(); P.action_stride = e->cfg.action_stride;
     P.auto_reset = e->cfg.auto_reset; P.diagnostics = e->cfg.diagnostics;
     P.trace_len = e->trace_len; P.trace_per_hub = e->trace_per_hub;
-    P.step_offset = 0; P.step_index = e->step_index;
+    P.step_offset = 0; P.step_index = e->step_index; P.num_sms = e->num_sms;
     {   // experiment knobs (defaults are the measured best)
         const char *b = getenv("CHUB_BLOCK"), *y = getenv("CHUB_PHASE_SYNC");
         P.block = b ? atoi(b) : 0;

@@ -853,13 +853,18 @@ void chub_launch_s2t_lut(float *out, cudaStream_t s) { chub_s2t_lut_kernel<<<(40
 
 __global__ void chub_tick_kernel(long long *step_index, int n) { *step_index += n; }
 
+template <int Q>
+static int step_scratch_bytes(const ChubParams &p) {
+    int ws = (int) warp_scratch_bytes<Q>(p.S0 > p.S1 ? p.S0 : p.S1);
+    // room to stage the warp's 32 action rows behind the parked analog entries, when that stays small
+    const int stage_bytes = (int) offsetof(WarpScratch<Q>, park) + 128 * p.action_stride;
+    if (stage_bytes > ws && stage_bytes <= 10240) ws = stage_bytes;
+    return ws;
+}
 template <int WARPS, int MINB, int Q>
 static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s) {
     ChubParams p = p0;
-    p.ws_bytes = (int) warp_scratch_bytes<Q>(p.S0 > p.S1 ? p.S0 : p.S1);
-    // room to stage the warp's 32 action rows behind the parked analog entries, when that stays small
-    const int stage_bytes = (int) offsetof(WarpScratch<Q>, park) + 128 * p.action_stride;
-    if (stage_bytes > p.ws_bytes && stage_bytes <= 10240) p.ws_bytes = stage_bytes;
+    p.ws_bytes = step_scratch_bytes<Q>(p);
     const size_t smem = CHUB_SMEM_TABLES + (size_t) WARPS * p.ws_bytes;
     auto kern = chub_step_kernel<WARPS, MINB, Q>;
     // per device and cheap; set on every launch so that engines on several devices of one process all get it
@@ -869,16 +874,38 @@ static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s) {
     kern<<<(p.h_end - p.h_begin + block - 1) / block, block, smem, s>>>(p);
     return cudaSuccess;
 }
+// Launch shape.  One block per SM; the step's duration is (rounds of blocks over the SMs) x (warps per block) to
+// within a few per cent for 16..28 warps (measured), so the block size is chosen to waste the least of the last
+// round: 524,288 hubs are 3.95 rounds of 28-warp blocks but 4.6 of 24-warp ones.  CHUB_BLOCK overrides.
 cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s) {
-    switch (p.block) {  // warps per block * 100 + min blocks per SM * 10 + cars per lane per add_car round
+    int shape = p.block;
+    if (shape == 0) {
+        const int ws = step_scratch_bytes<0>(p), sms = p.num_sms > 0 ? p.num_sms : 148;
+        const int NC = 6;
+        const int cand[NC] = {28, 24, 20, 16, 8, 4};                         // small blocks spread a small batch over the SMs
+        const double cost_per_warp[NC] = {1.00, 1.005, 1.085, 1.12, 1.2, 1.3};  // relative, from the measured sweeps
+        double best = 1e300;
+        for (int k = 0; k < NC; ++k) {
+            if (CHUB_SMEM_TABLES + cand[k] * ws + 1024 > 227 * 1024) continue;
+            const long long blocks = ((long long) (p.h_end - p.h_begin) + cand[k] * 32 - 1) / (cand[k] * 32);
+            const long long rounds = (blocks + sms - 1) / sms;
+            const double cost = (double) rounds * cand[k] * cost_per_warp[k];
+            if (cost < best) { best = cost; shape = cand[k] * 100 + 10; }
+        }
+        if (shape == 0) shape = 1220;
+    }
+    switch (shape) {  // warps per block * 100 + min blocks per SM * 10
         case 1620: return launch_step_variant<16, 2, 0>(p, s);
-        case 840: return launch_step_variant<8, 4, 0>(p, s);
         case 1220: return launch_step_variant<12, 2, 0>(p, s);
         case 830: return launch_step_variant<8, 3, 0>(p, s);
-        case 820: return launch_step_variant<8, 2, 0>(p, s);
+        case 410: return launch_step_variant<4, 1, 0>(p, s);
+        case 810: return launch_step_variant<8, 1, 0>(p, s);
+        case 1610: return launch_step_variant<16, 1, 0>(p, s);
+        case 2010: return launch_step_variant<20, 1, 0>(p, s);
         case 2410: return launch_step_variant<24, 1, 0>(p, s);
+        case 2810: return launch_step_variant<28, 1, 0>(p, s);
         case 3210: return launch_step_variant<32, 1, 0>(p, s);
-        default: return launch_step_variant<24, 1, 0>(p, s);
+        default: return launch_step_variant<12, 2, 0>(p, s);
     }
 }
 void chub_launch_reset(const ChubParams &p, cudaStream_t s) {

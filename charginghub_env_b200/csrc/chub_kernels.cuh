@@ -37,6 +37,7 @@ struct ChubParams {
     int n_classes, action_stride, auto_reset, diagnostics;
     int trace_len, trace_per_hub;
     int block, phase_sync;            // launch shape of the step kernel (see chub_launch_step); phase_sync: block barriers between code regions
+    int num_sms;                      // SMs of the device (launch-shape choice)
     int ws_bytes;                     // bytes of shared-memory scratch per warp (set by chub_launch_step)
     int step_offset;                  // added to *step_index (graph-captured rollouts bake 0..n-1)
     const long long *step_index;      // device: absolute step index of the state being left
