@@ -157,6 +157,62 @@ __device__ __noinline__ uint2 draw_mk_soc(uint32_t lcg) {
     de = fminf(fmaxf(de, 1.0f), 10.0f);
     return make_uint2(__float_as_uint((float) (75.0 - 5.0 * (double) de)), lcg);
 }
+// The serial part of the two polar normals, alone: walk the minstd stream to the attempt that is accepted and
+// return {state that attempt started from, state after it}.  The variate itself is a pure function of the
+// start state and can be evaluated later, by any lane (mk_soc_from / late_time_from).
+__device__ __noinline__ uint2 walk_polar_d(uint32_t lcg) {
+    uint32_t s0;
+    for (;;) {
+        s0 = lcg;
+        const uint32_t s2 = chub_minstd_jump(s0, CHUB_MINSTD_A2), s4 = chub_minstd_jump(s0, CHUB_MINSTD_A4);
+        lcg = s4;
+        const float xa = fmaf((float) (s2 - 1u), 9.31322575e-10f, -1.0f), ya = fmaf((float) (s4 - 1u), 9.31322575e-10f, -1.0f);
+        const float r2a = fmaf(xa, xa, ya * ya);
+        bool ok = r2a < 1.0f;
+        if (fabsf(r2a - 1.0f) < 4e-6f || r2a < 4e-6f) {   // too close to call in fp32: decide like the reference
+            const double xe = 2.0 * canon_d_of(chub_minstd_next(s0), s2) - 1.0;
+            const double ye = 2.0 * canon_d_of(chub_minstd_jump(s0, CHUB_MINSTD_A3), s4) - 1.0;
+            const double r2e = xe * xe + ye * ye;
+            ok = !(r2e > 1.0 || r2e == 0.0);
+        }
+        if (ok) break;
+    }
+    return make_uint2(s0, lcg);
+}
+__device__ __noinline__ uint2 walk_polar_f(uint32_t lcg) {
+    uint32_t s0;
+    for (;;) {
+        s0 = lcg;
+        const uint32_t s1 = chub_minstd_next(s0), s2 = chub_minstd_jump(s0, CHUB_MINSTD_A2);
+        lcg = s2;
+        const float x = 2.0f * canon_f_of(s1) - 1.0f, y = 2.0f * canon_f_of(s2) - 1.0f;
+        const float r2 = x * x + y * y;
+        if (!(r2 > 1.0f || r2 == 0.0f)) break;
+    }
+    return make_uint2(s0, lcg);
+}
+// mk_soc (CHS.hpp:804-814) from the start state of its accepted attempt
+template <int LT>
+__device__ __forceinline__ float mk_soc_from(uint32_t s0) {
+    const double x = 2.0 * canon_d_of(chub_minstd_next(s0), chub_minstd_jump(s0, CHUB_MINSTD_A2)) - 1.0;
+    const double y = 2.0 * canon_d_of(chub_minstd_jump(s0, CHUB_MINSTD_A3), chub_minstd_jump(s0, CHUB_MINSTD_A4)) - 1.0;
+    const double r2 = x * x + y * y;
+    const double mult = sqrt(chub_div(-2.0 * chub_log(r2, log_tab<LT>()), r2));
+    float de = (float) ((y * mult) * 3.0 + 7.0);
+    de = fminf(fmaxf(de, 1.0f), 10.0f);
+    return (float) (75.0 - 5.0 * (double) de);
+}
+// mk_late_time (CHS.hpp:816-830) from the start state of its accepted attempt
+template <int LT>
+__device__ __forceinline__ int late_time_from(uint32_t s0) {
+    const float x = 2.0f * canon_f_of(chub_minstd_next(s0)) - 1.0f, y = 2.0f * canon_f_of(chub_minstd_jump(s0, CHUB_MINSTD_A2)) - 1.0f;
+    const float r2 = x * x + y * y;
+    const float lg = (float) chub_log((double) r2, log_tab<LT>());
+    const float v = (y * sqrtf(-2.0f * lg / r2)) * 2.0f + 2.0f;
+    const int d = (int) roundf(v);
+    return d > 0 ? d : 0;
+}
+
 // float normal with unit-free (mean, sd) (CHS.hpp:819-820, 833-834).  logf is taken as the correctly
 // rounded fp32 log (fp64 log narrowed), which is what glibc's logf returns except on rare hard cases.
 // Returns {value bits, new minstd state}.

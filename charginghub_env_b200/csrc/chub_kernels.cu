@@ -126,7 +126,7 @@ struct WarpScratch {
     float am[2][32];                  // the two analog action entries of each hub, parked here during the stations
     // ---- everything below doubles as the staging area of the warp's action rows ----
     uint32_t park[2][5][32];          // the stations' outputs, parked until the hub section (registers are scarce)
-    uint32_t inc_s[32];               // posted to the owner lane: incomplete departures found by a car_step batch
+    uint32_t inc_s[32], err_s[32];    // posted to the owner lane: incomplete departures found by a car_step batch, error bits
     uint32_t la_t[2][LA_RING], la_w[2][LA_RING], la_id[2][LA_RING];  // car_step rings per curve segment: new charge time
                                       // (f32 bits), packed pile word, lane | pile << 5
     uint32_t pw[1][32];               // [pile][lane], max(S0, S1) rows in fact: power (f32 bits, >= 0) of the car now on that
@@ -169,6 +169,40 @@ __device__ __forceinline__ void flat_car_step(const ChubParams &P, WarpScratch<Q
     __syncwarp();
 }
 
+// @region flat B shell (add_car batch)
+// add_car (CHS.hpp:864-877 / 1029-1042) for up to 128 new cars of the warp's hubs, lanes = cars of any hub.  The
+// owners have walked their streams (which attempt of each polar normal is accepted, which target draw); the
+// variates, the curves and the pile record are computed here.  Items sit in the (idle) car_step rings:
+// la_t = start state of the mk_soc attempt, la_w = of the mk_late_time attempt, la_id = lane | pile << 5 | u << 10.
+template <int TYPE, int CP, int Q>
+__device__ __forceinline__ void flat_add_car(WarpScratch<Q> &S, const float *tlut, uint4 *pile0, float *arrive0, int total) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t *const sd = &S.la_t[0][0], *const sf = &S.la_w[0][0], *const sx = &S.la_id[0][0];
+    for (int j = lane; j < total; j += 32) {
+        const uint32_t x = sx[j], owner = x & 31u, i = (x >> 5) & 31u, tu = x >> 10;
+        const float arrive = mk_soc_from<1>(sd[j]);
+        const int late = late_time_from<1>(sf[j]);
+        const float tsoc = curve_s2t<TYPE, CP>(arrive);
+        const float needed = tlut[tu] - tsoc;
+        const int must_needed = (int) ceilf(needed);          // calculate_min_charging_time
+        int stay = must_needed + late;
+        const float power = curve_t2p<TYPE, CP>(tsoc);
+        int cn = needed > 0.0f ? must_needed : 0;
+        if (stay > 63 || stay < 1 || cn > 31) {
+            atomicOr(&S.err_s[owner], (uint32_t) CHUB_HUBERR_COUNTER);
+            stay = min(max(stay, 1), 63);
+            cn = min(cn, 31);
+        }
+        const uint32_t urgent = (cn > 0 && stay <= cn) ? 1u : 0u;
+        const uint32_t at = i * 32u + owner;
+        pile0[at] = make_uint4(__float_as_uint(arrive), __float_as_uint(tsoc), __float_as_uint(power),
+                               (uint32_t) stay | PW_CAR | (urgent << 14) | ((uint32_t) cn << 15) | (tu << 20));
+        arrive0[at] = arrive;
+        (&S.pw[0][0])[at] = __float_as_uint(power) | (urgent << 31);
+    }
+    __syncwarp();
+}
+
 // All 32 lanes call this together.  `mine` = this lane's hub has a station of this (TYPE, CP) at this
 // position; the other lanes own no piles here but still work on the pooled items.
 // @region station prologue + receive_car draws
@@ -182,7 +216,7 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
     const int n = mine ? n_in : 0;
     // s2t(target) of the 1000 possible targets: shared-memory copy for curve charging, global (L1) for constant power
     const float *tlut = CP ? P.s2t_lut + (2 + TYPE) * 1000 : tl_s + TYPE * 1000;
-    S.inc_s[lane] = 0u;
+    S.inc_s[lane] = 0u; S.err_s[lane] = 0u;
 
     // ---- station-level draws of receive_car (CHS.hpp:1272-1306), before any per-car draw ----
     int want = 0, flow = 0;
@@ -290,36 +324,39 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
         }
     }
 
-// @region add_car (per-lane serial draws)
-    // ---- add_car for the newly assigned piles, ascending (CHS.hpp:864-877 / 1029-1042).  The E/U/E draws of a hub are
-    // a serial chain through its two streams, so this part stays one lane = one hub. ----
+// @region add_car (per-lane stream walk)
+    // ---- add_car for the newly assigned piles, ascending (CHS.hpp:864-877 / 1029-1042).  Per car the E stream serves
+    // mk_soc then mk_late_time and the U stream the target draw in between.  Which attempt of each polar normal is
+    // accepted is a serial walk through the hub's stream: one lane = one hub, four cars per round.  Everything else is
+    // pooled over the warp (flat_add_car). ----
     {
-        float *const arrive0 = P.arrive + tile0 + lane;
-        uint32_t m = add_mask;
-        while (m) {
-            const int i = __ffs(m) - 1;
-            m &= m - 1u;
-            const float arrive = rng_mk_soc<1>(rng);              // E
-            const uint32_t tu = (uint32_t) rng_u1000(rng);        // U  (target = u/999*20+80)
-            const float tsoc = curve_s2t<TYPE, CP>(arrive);
-            const float needed = tlut[tu] - tsoc;
-            const int must_needed = (int) ceilf(needed);          // calculate_min_charging_time
-            int stay = must_needed + rng_late_time<1>(rng);       // E
-            const float power = curve_t2p<TYPE, CP>(tsoc);
-            int cn = needed > 0.0f ? must_needed : 0;
-            if (stay > 63 || stay < 1 || cn > 31) {
-                err |= CHUB_HUBERR_COUNTER;
-                stay = min(max(stay, 1), 63);
-                cn = min(cn, 31);
+        const int a = max(assigned, 0);
+        uint32_t rem = add_mask;
+        for (int kb = 0; __any_sync(full, kb < a); kb += 4) {
+            const int q = min(max(a - kb, 0), 4);
+            int incl = q;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int v = __shfl_up_sync(full, incl, d);
+                if (lane >= d) incl += v;
             }
-            const uint32_t urgent = (cn > 0 && stay <= cn) ? 1u : 0u;
-            pile0[i * 32 + lane] = make_uint4(__float_as_uint(arrive), __float_as_uint(tsoc), __float_as_uint(power),
-                                              (uint32_t) stay | PW_CAR | (urgent << 14) | ((uint32_t) cn << 15) | (tu << 20));
-            arrive0[i * 32] = arrive;
-            (&S.pw[0][0])[i * 32 + lane] = __float_as_uint(power) | (urgent << 31);
+            const int total = __shfl_sync(full, incl, 31);
+            int slot = incl - q;
+            for (int k = 0; k < q; ++k, ++slot) {
+                const uint2 wd = walk_polar_d(rng.lcg);           // E
+                const uint32_t tu = (uint32_t) rng_u1000(rng);    // U  (target = u/999*20+80)
+                const uint2 wf = walk_polar_f(wd.y);              // E
+                rng.lcg = wf.y;
+                const uint32_t i = (uint32_t) __ffs(rem) - 1u;
+                rem &= rem - 1u;
+                (&S.la_t[0][0])[slot] = wd.x;
+                (&S.la_w[0][0])[slot] = wf.x;
+                (&S.la_id[0][0])[slot] = (uint32_t) lane | (i << 5) | (tu << 10);
+            }
+            __syncwarp();
+            flat_add_car<TYPE, CP, Q>(S, tlut, pile0, P.arrive + tile0, total);
         }
     }
-    __syncwarp();
 
 // @region station sums
     // ---- calculate_output in ascending fp32 order (CHS.hpp:1233-1261); adding +0.0f for a skipped pile is exact ----
@@ -341,6 +378,7 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
         o.line = min(want - assigned, 10);
         o.flow = flow;
         o.incomplete = incomplete + (int) S.inc_s[lane];
+        err |= S.err_s[lane];
         o.occ = present;
     }
     __syncwarp();
