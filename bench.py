@@ -187,6 +187,8 @@ def main():
     ap.add_argument("--hubs", type=int, default=0, help="override hubs per GPU")
     ap.add_argument("--e2e-steps", type=int, default=24)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--exogenous", default="traces", choices=["traces", "device"],
+                    help="traces: shared synthetic year (default); device: the on-device PV/wind/price generator")
     args = ap.parse_args()
 
     from charginghub_env_b200 import load_tables
@@ -215,7 +217,11 @@ def main():
     eng = HubEngine(H, wl["classes"], hub_class=wl["hub_class"], device=local, hub_id_base=rank * H,
                     action_stride=S, auto_reset=wl["auto_reset"], diagnostics=False, tables=tabs, seed=0x5EED)
     L = 35040 + 1
-    eng.set_traces(*year_traces(tabs, L))
+    if args.exogenous == "device":
+        eng.set_exogenous_generator(tabs, 0.0, 0.0)
+        wl["desc"] += ", exogenous inputs generated on the device"
+    else:
+        eng.set_traces(*year_traces(tabs, L))
     gen = torch.Generator(device="cuda").manual_seed(1234 + rank)
     npool = 4  # rotating action matrices; state + actions per step exceed the 126 MB L2 for config5/config3
     pool = [torch.rand((H, S), device="cuda", generator=gen) * 2 - 1 for _ in range(npool)]

@@ -72,6 +72,7 @@ SYMBOLS = {
     "chub_get_class_table": (ctypes.c_int, [_vp, _i32, _vp]),
     "chub_set_traces": (ctypes.c_int, [_vp, _vp, _vp, _vp, _i32, _i32]),
     "chub_poke_trace": (ctypes.c_int, [_vp, _i32, ctypes.c_double, ctypes.c_double, ctypes.c_double, _vp]),
+    "chub_set_exogenous_generator": (ctypes.c_int, [_vp, _vp, _i32, _vp, _i32, ctypes.c_double, ctypes.c_double]),
     "chub_seed": (ctypes.c_int, [_vp, _u64]),
     "chub_seed_explicit": (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp]),
     "chub_reset": (ctypes.c_int, [_vp, _vp, _i64, _vp]),

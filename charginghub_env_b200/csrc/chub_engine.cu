@@ -44,6 +44,10 @@ struct chub_engine {
     long long *step_index = nullptr;
     int num_sms = 0;
     float *actions_stage = nullptr;  // device copy target of chub_step_host
+    int exo_mode = 0, n_pv_days = 0, n_wd_days = 0;
+    double exo_renew_gain = 1.0, exo_price_gain = 1.0;
+    double *exo_d = nullptr, *pv_days = nullptr, *wd_days = nullptr;
+    uint2 *exo_i = nullptr;
     cudaStream_t host_streams[3] = {nullptr, nullptr, nullptr};  // chub_step_host pipeline: copy in, step, copy out
     cudaEvent_t host_events[2 * 16 + 2] = {};
     int trace_len = 0, trace_per_hub = 0;
@@ -67,7 +71,7 @@ static void engine_free(chub_engine *e) {
         if (ev) cudaEventDestroy(ev);
     void *ptrs[] = {e->pile, e->arrive, e->hubA, e->store, e->keys, e->occ, e->cls, e->stats, e->last_stats, e->err, e->qsoc,
                     e->d_classes, e->d_el, e->lut, e->s2t_lut, e->pv, e->wd, e->price_tr, e->obs, e->reward, e->done, e->diag,
-                    e->st_power, e->step_index, e->actions_stage};
+                    e->st_power, e->step_index, e->actions_stage, e->exo_d, e->exo_i, e->pv_days, e->wd_days};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     delete e;
@@ -351,6 +355,34 @@ extern "C" int chub_set_traces(chub_engine *e, const double *pv, const double *w
     e->trace_len = length;
     e->trace_per_hub = per_hub ? 1 : 0;
     e->have_traces = true;
+    e->exo_mode = 0;
+    return CHUB_OK;
+}
+
+extern "C" int chub_set_exogenous_generator(chub_engine *e, const double *pv_days, int32_t n_pv, const double *wd_days,
+                                            int32_t n_wd, double renew_fluctuate, double price_fluctuate) {
+    if (!e || !pv_days || !wd_days || n_pv < 1 || n_wd < 1 || n_pv > 1023 || n_wd > 1023)
+        return fail(CHUB_ERR_ARG, "chub_set_exogenous_generator: bad argument (1..1023 days per table)");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    for (double **p : {&e->pv_days, &e->wd_days, &e->exo_d})
+        if (*p) { cudaFree(*p); *p = nullptr; }
+    if (e->exo_i) { cudaFree(e->exo_i); e->exo_i = nullptr; }
+    CK(dalloc(&e->pv_days, (size_t) n_pv * 96));
+    CK(dalloc(&e->wd_days, (size_t) n_wd * 96));
+    CK(cudaMemcpy(e->pv_days, pv_days, sizeof(double) * 96 * n_pv, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(e->wd_days, wd_days, sizeof(double) * 96 * n_wd, cudaMemcpyHostToDevice));
+    CK(dalloc(&e->exo_d, (size_t) 7 * e->Hpad));   // zeroed: OU states start at their mean, like OU_Noise.reset
+    CK(dalloc(&e->exo_i, (size_t) e->Hpad));
+    e->n_pv_days = n_pv; e->n_wd_days = n_wd;
+    e->exo_renew_gain = 1 + renew_fluctuate; e->exo_price_gain = 1 + price_fluctuate;
+    e->exo_mode = 1;
+    if (!e->have_traces) {   // the kernels take the trace pointers unconditionally: give them one slot
+        const double z = 0.0;
+        int rc = chub_set_traces(e, &z, &z, &z, 1, 0);
+        if (rc) return rc;
+        e->exo_mode = 1;
+    }
     return CHUB_OK;
 }
 
@@ -369,6 +401,10 @@ extern "C" int chub_poke_trace(chub_engine *e, int32_t slot, double pv, double w
 static int upload_streams(chub_engine *e, const std::vector<uint2> &keys, const std::vector<uint4> &hubA) {
     CK(cudaMemcpy(e->keys, keys.data(), sizeof(uint2) * e->H, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(e->hubA, hubA.data(), sizeof(uint4) * e->H, cudaMemcpyHostToDevice));
+    if (e->exo_d) {   // a new seed restarts the generator's streams and noise processes
+        CK(cudaMemset(e->exo_d, 0, sizeof(double) * 7 * e->Hpad));
+        CK(cudaMemset(e->exo_i, 0, sizeof(uint2) * e->Hpad));
+    }
     e->have_seed = true;
     return CHUB_OK;
 }
@@ -425,6 +461,9 @@ static int fill_params(chub_engine *e, ChubParams &P) {
     P.stats = e->stats; P.last_stats = e->last_stats; P.err = e->err; P.qsoc = e->qsoc;
     P.classes = e->d_classes; P.el_table = e->d_el; P.lut = e->lut; P.s2t_lut = e->s2t_lut;
     P.pv = e->pv; P.wd = e->wd; P.price_tr = e->price_tr;
+    P.exo_mode = e->exo_mode; P.n_pv_days = e->n_pv_days; P.n_wd_days = e->n_wd_days;
+    P.exo_renew_gain = e->exo_renew_gain; P.exo_price_gain = e->exo_price_gain;
+    P.exo_d = e->exo_d; P.exo_i = e->exo_i; P.pv_days = e->pv_days; P.wd_days = e->wd_days;
     P.actions = nullptr; P.obs = e->obs; P.reward = e->reward; P.done = e->done;
     P.diag = e->diag; P.st_power = e->st_power; P.reset_mask = nullptr;
     return CHUB_OK;
@@ -747,10 +786,15 @@ extern "C" int chub_get_field(chub_engine *e, int32_t field, void *host_out) {
 struct Seg { void *p; size_t bytes; };
 static std::vector<Seg> state_segments(chub_engine *e) {
     const size_t Hp = e->Hpad, slots = (size_t) (e->S0 + e->S1) * Hp;
-    return {{e->pile, slots * sizeof(uint4)}, {e->arrive, slots * sizeof(float)}, {e->hubA, Hp * sizeof(uint4)},
+    std::vector<Seg> v = {{e->pile, slots * sizeof(uint4)}, {e->arrive, slots * sizeof(float)}, {e->hubA, Hp * sizeof(uint4)},
             {e->store, Hp * sizeof(double)}, {e->keys, Hp * sizeof(uint2)}, {e->occ, Hp * sizeof(uint2)}, {e->stats, Hp * sizeof(float4)},
             {e->last_stats, Hp * sizeof(float4)}, {e->err, Hp * sizeof(uint32_t)},
             {e->qsoc, Hp * CHUB_FCEV_QCAP * sizeof(float)}, {e->step_index, sizeof(long long)}};
+    if (e->exo_d) {   // generator state travels with the checkpoint
+        v.push_back({e->exo_d, 7 * Hp * sizeof(double)});
+        v.push_back({e->exo_i, Hp * sizeof(uint2)});
+    }
+    return v;
 }
 extern "C" int64_t chub_state_bytes(chub_engine *e) {
     if (!e || !e->have_classes) return -1;

@@ -18,6 +18,9 @@
 #include <math.h>
 
 struct ChubLogEntry { double invc, logc; };  // 1/c rounded, and -log(invc)
+#if !defined(__cplusplus)
+typedef struct ChubLogEntry ChubLogEntry;
+#endif
 #define CHUB_LOG_N 128
 #define CHUB_LOG_OFF 0x3fe6000000000000ull  // 0.6875: z = x * 2^-k lands in [0.6875, 1.375)
 

@@ -12,6 +12,7 @@
 // running count inside the single ascending pass; no list is built.
 #define CHUB_KERNEL_TU
 #include "chub_kernels.cuh"
+#include "../../include/chub_exo.h"
 
 cudaError_t chub_upload_const(const ChubConst &c) {
     ChubLogEntry tab[CHUB_LOG_N];
@@ -513,6 +514,62 @@ __device__ __forceinline__ void trace_at(const ChubParams &P, int h, long long k
     pv = __ldg(&P.pv[i]); wd = __ldg(&P.wd[i]); pr = __ldg(&P.price_tr[i]);
 }
 
+// ---------------------------------------------------------------------------------------------
+// on-device exogenous generator (chub_set_exogenous_generator): the reference's ReNew / OU_Noise / make_state
+// arithmetic on the hub's X stream (include/chub_exo.h)
+struct ExoState {
+    double ou_pv, ou_wd, ou_pr, hold;
+    uint32_t days, ctr;   // pv_day | wd_day << 10 | (price_count mod 4) << 20
+};
+__device__ __forceinline__ void exo_load(const ChubParams &P, int h, ExoState &g) {
+    const size_t s = (size_t) P.Hpad;
+    g.ou_pv = P.exo_d[h]; g.ou_wd = P.exo_d[s + h]; g.ou_pr = P.exo_d[2 * s + h]; g.hold = P.exo_d[3 * s + h];
+    const uint2 w = P.exo_i[h];
+    g.days = w.x; g.ctr = w.y;
+}
+__device__ __forceinline__ void exo_store(const ChubParams &P, int h, const ExoState &g, double pv, double wd, double pr) {
+    const size_t s = (size_t) P.Hpad;
+    P.exo_d[h] = g.ou_pv; P.exo_d[s + h] = g.ou_wd; P.exo_d[2 * s + h] = g.ou_pr; P.exo_d[3 * s + h] = g.hold;
+    P.exo_d[4 * s + h] = pv; P.exo_d[5 * s + h] = wd; P.exo_d[6 * s + h] = pr;
+    P.exo_i[h] = make_uint2(g.days, g.ctr);
+}
+__device__ __forceinline__ void exo_current(const ChubParams &P, int h, double &pv, double &wd, double &pr) {
+    const size_t s = (size_t) P.Hpad;
+    pv = P.exo_d[4 * s + h]; wd = P.exo_d[5 * s + h]; pr = P.exo_d[6 * s + h];
+}
+// OU_Noise.sample (renewable.py:71-76): dx = theta (mu - x) + sigma N(0,1), mu = 0
+__device__ __forceinline__ double exo_ou(double &x, double theta, double sigma, uint32_t k0, uint32_t k1, uint32_t &ctr) {
+    const double dx = theta * (0.0 - x) + sigma * chub_xnormal(k0, k1, &ctr, kLogTab);
+    x = x + dx;
+    return x;
+}
+// the exogenous part of make_state(time) (evcssp_manager.py:344-361, renewable.py:37-49): out of line, once per hub-step
+__device__ __noinline__ void exo_values(const ChubParams &P, ExoState &g, uint32_t k0, uint32_t k1, int time,
+                                        double last_table_price, double &pv, double &wd, double &pr) {
+    const int pv_day = g.days & 1023u, wd_day = (g.days >> 10) & 1023u;
+    uint32_t pcount = (g.days >> 20) & 3u;
+    double temp = __ldg(&P.pv_days[pv_day * 96 + time]);
+    if (temp > 0.0 && (pv_day & 1) == 0) temp += exo_ou(g.ou_pv, 0.01, 1.0, k0, k1, g.ctr) * P.exo_renew_gain;
+    pv = (temp > 0.0 ? temp : 0.0) * 5.0;
+    temp = __ldg(&P.wd_days[wd_day * 96 + time]);
+    temp += exo_ou(g.ou_wd, 0.01, 1.5, k0, k1, g.ctr) * P.exo_renew_gain;
+    wd = (temp > 0.0 ? temp : 0.0) * 1.0;
+    if (pcount == 0u) g.hold = exo_ou(g.ou_pr, 0.1, 0.005, k0, k1, g.ctr) * P.exo_price_gain;
+    pr = last_table_price + g.hold;
+    pcount = (pcount + 1u) & 3u;
+    g.days = (g.days & 0xfffffu) | (pcount << 20);
+}
+// reset(): renew_reset, make_state(0), price_count = 0 (evcssp_manager.py:304-316)
+__device__ __forceinline__ void exo_reset(const ChubParams &P, ExoState &g, uint32_t k0, uint32_t k1, double &pv, double &wd,
+                                          double &pr) {
+    const uint32_t pd = chub_xrand31(k0, k1, g.ctr) % (uint32_t) P.n_pv_days;
+    const uint32_t wdd = chub_xrand31(k0, k1, g.ctr + 1u) % (uint32_t) P.n_wd_days;
+    g.ctr += 2u;
+    g.days = pd | (wdd << 10) | (g.days & (3u << 20));
+    exo_values(P, g, k0, k1, 0, kC.price[95], pv, wd, pr);
+    g.days &= 0xfffffu;
+}
+
 // observation, evcssp_manager.py:318-342 (state_norm) over make_state's real_state
 __device__ __forceinline__ void write_obs(const ChubParams &P, int h, const ChubClass &c, int t, const StationOut &s0,
                                           const StationOut &s1, double store_soc, double pv, double wd, double pr) {
@@ -562,7 +619,14 @@ __device__ __noinline__ void hub_reset_full(const ChubParams &P, int h, long lon
     v.store = c.init_mass;
     P.stats[h] = make_float4(0.f, 0.f, 0.f, 0.f);
     double pv, wd, pr;
-    trace_at(P, h, k_obs, pv, wd, pr);
+    if (P.exo_mode) {
+        ExoState g;
+        exo_load(P, h, g);
+        exo_reset(P, g, v.rng.k0, v.rng.k1, pv, wd, pr);
+        exo_store(P, h, g, pv, wd, pr);
+    } else {
+        trace_at(P, h, k_obs, pv, wd, pr);
+    }
     write_obs(P, h, c, 0, s0, s1, c.init_soc, pv, wd, pr);
     if (P.diag) {
         const size_t s = (size_t) P.Hpad;
@@ -714,7 +778,8 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     v.store = P.store[h];
     const long long k = *P.step_index + P.step_offset;
     double pv_t, wd_t, pr_t;
-    trace_at(P, h, k, pv_t, wd_t, pr_t);
+    if (P.exo_mode) exo_current(P, h, pv_t, wd_t, pr_t);
+    else trace_at(P, h, k, pv_t, wd_t, pr_t);
     const float a_m2 = S.am[0][lane_], a_m1 = S.am[1][lane_];
     v.line0 = s0.line; v.line1 = s1.line;
     v.flow0 = s0.flow; v.flow1 = s1.flow;
@@ -855,11 +920,18 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     P.reward[h] = (float) reward;
     P.done[h] = done ? 1 : 0;
     hub_store(P, h, v);
+    double pv_n = 0.0, wd_n = 0.0, pr_n = 0.0;
+    if (P.exo_mode) {   // make_state(time_next) of this step: the price list's last entry is table[time just left]
+        ExoState g;
+        exo_load(P, h, g);
+        exo_values(P, g, v.rng.k0, v.rng.k1, v.t, kC.price[(v.t + CHUB_DAY - 1) % CHUB_DAY], pv_n, wd_n, pr_n);
+        exo_store(P, h, g, pv_n, wd_n, pr_n);
+    } else if (!(done && P.auto_reset)) {
+        trace_at(P, h, k + 1, pv_n, wd_n, pr_n);
+    }
     if (done && P.auto_reset) {  // fused auto-reset: the returned obs is the first one of the next episode
         hub_reset_full(P, h, k + 1);
     } else {
-        double pv_n, wd_n, pr_n;
-        trace_at(P, h, k + 1, pv_n, wd_n, pr_n);
         write_obs(P, h, c, v.t, s0, s1, store_soc, pv_n, wd_n, pr_n);
     }
 }

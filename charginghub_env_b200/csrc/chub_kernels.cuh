@@ -56,6 +56,12 @@ struct ChubParams {
     const uint16_t *lut;              // [96][1000] traffic count for u = r/999.f (CHS.hpp:731-743)
     const float *s2t_lut;             // [2 constant][2 type][1000] soc_to_time(target(u))
     const double *pv, *wd, *price_tr;
+    // on-device exogenous generator (exo_mode != 0): per-hub state and the day tables
+    int exo_mode, n_pv_days, n_wd_days;
+    double exo_renew_gain, exo_price_gain;   // 1 + renew_fluctuate, 1 + price_fluctuate
+    double *exo_d;                    // [7][Hpad]: OU states pv, wd, price; held price noise; current pv, wd, price
+    uint2 *exo_i;                     // [Hpad]: {pv_day | wd_day << 10 | price_count mod 4 << 20, X-stream counter}
+    const double *pv_days, *wd_days;  // [n][96]
     const float *actions;
     float *obs;
     float *reward;

@@ -157,6 +157,17 @@ class HubEngine(object):
                 raise ValueError("trace shape %s, expected %s" % (x.shape, want))
         check(self.lib.chub_set_traces(self.h, _dptr(a[0]), _dptr(a[1]), _dptr(a[2]), a[0].shape[0], int(per_hub)))
 
+    def set_exogenous_generator(self, tables=None, renew_fluctuate=0.0, price_fluctuate=0.0):
+        """Generate PV / wind / price on the device (per hub: random days at every reset + OU noise, the reference's
+        ReNew / OU_Noise / make_state on the hub's X stream) instead of reading traces."""
+        tabs = tables if tables is not None else load_tables()
+        pv = np.ascontiguousarray(tabs["pv_days"], np.float64)
+        wd = np.ascontiguousarray(tabs["wd_days"], np.float64)
+        if pv.ndim != 2 or wd.ndim != 2 or pv.shape[1] != 96 or wd.shape[1] != 96:
+            raise ValueError("pv_days / wd_days must be [n_days, 96]")
+        check(self.lib.chub_set_exogenous_generator(self.h, _dptr(pv), pv.shape[0], _dptr(wd), wd.shape[0],
+                                                    float(renew_fluctuate), float(price_fluctuate)))
+
     def poke_trace(self, slot, pv, wd, price, stream=0):
         check(self.lib.chub_poke_trace(self.h, int(slot), float(pv), float(wd), float(price), ctypes.c_void_p(int(stream))))
 

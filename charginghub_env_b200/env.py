@@ -174,20 +174,27 @@ class EvcsspManagerEnv_v6(_EnvBase):
 
 
 class BatchedHubEnv(object):
-    """H hubs, torch in / torch out.  step() returns views of engine memory (zero copy through DLPack)."""
+    """H hubs, torch in / torch out.  step() returns views of engine memory (zero copy through DLPack).
+    traces: (pv, wd, price) arrays, None for the shared synthetic year, or "device" for the on-device generator."""
 
     def __init__(self, n_hubs, env_kwargs=None, classes=None, hub_class=None, device=0, hub_id_base=0,
                  auto_reset=True, seed=0, traces=None, action_stride=None, diagnostics=False):
         if classes is None:
             classes = [dict(env_kwargs or {})]
+        fluct = [(c.get("renew_fluctuate", 0) or 0, c.get("price_fluctuate", 0) or 0) for c in classes]
         classes = [{k: v for k, v in c.items() if k not in ("seed_rand", "use_lagrange", "renew_fluctuate",
                                                               "price_fluctuate")} for c in classes]
         self.tables = load_tables()
         self.engine = HubEngine(n_hubs, classes, hub_class=hub_class, device=device, hub_id_base=hub_id_base,
                                 auto_reset=auto_reset, diagnostics=diagnostics, tables=self.tables, seed=seed,
                                 action_stride=action_stride)
-        pv, wd, price = traces if traces is not None else synthetic_year(self.tables)
-        self.engine.set_traces(pv, wd, price, per_hub=np.ndim(pv) == 2)
+        if isinstance(traces, str) and traces == "device":
+            # the reference's own exogenous model, generated per hub inside the step kernel (random PV / wind days at
+            # every reset, OU noise on both and on the price; renew_fluctuate / price_fluctuate of the first class)
+            self.engine.set_exogenous_generator(self.tables, fluct[0][0], fluct[0][1])
+        else:
+            pv, wd, price = traces if traces is not None else synthetic_year(self.tables)
+            self.engine.set_traces(pv, wd, price, per_hub=np.ndim(pv) == 2)
         self.n_hubs, self.action_dim = n_hubs, self.engine.action_stride
         lo, hi = observation_bounds([1, 1], self.tables["price"])
         self.observation_space = _box(lo, hi, dtype=np.float32)

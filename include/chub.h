@@ -135,6 +135,18 @@ int chub_set_traces(chub_engine *e, const double *pv, const double *wd, const do
  * step, like the single-hub gym wrapper, keeps a short ring and pokes the next slot before each step). */
 int chub_poke_trace(chub_engine *e, int32_t slot, double pv, double wd, double price, void *stream);
 
+/* On-device exogenous generator, instead of traces: every hub draws its own PV day and wind day at each reset
+ * (ReNew.renew_reset, renewable.py:51-53), adds Ornstein-Uhlenbeck noise to them (ReNew.get_pv_power /
+ * get_wd_power + OU_Noise, renewable.py:37-76) and to the price, whose noise is resampled every fourth state and
+ * held in between (make_state, evcssp_manager.py:344-361), inside the step / reset kernels.  The variates come
+ * from the per-hub X stream of include/chub_exo.h (keyed like the other streams, so chub_seed fixes them); the OU
+ * states survive resets like the reference's.  pv_days [n_pv_days][96] (unscaled: the x5 is applied inside),
+ * wd_days [n_wd_days][96]: host pointers, copied.  The price table is the one of chub_set_tables.
+ * With auto-reset the finished episode's last make_state is generated (and discarded) before the new episode's
+ * first one, which is what a reference loop "step ... done -> reset" consumes. */
+int chub_set_exogenous_generator(chub_engine *e, const double *pv_days, int32_t n_pv_days, const double *wd_days,
+                                 int32_t n_wd_days, double renew_fluctuate, double price_fluctuate);
+
 /* Streams: either derive (key0,key1,minstd state) from base_seed and the global hub id
  * (include/chub_rng.h), or set them explicitly (host arrays [n_hubs]; uctr may be NULL = 0). */
 int chub_seed(chub_engine *e, uint64_t base_seed);

@@ -44,12 +44,13 @@ FIELD = {
 
 def build(force=False):
     src = os.path.join(_HERE, "hub_oracle.c")
+    src2 = os.path.join(_HERE, "exo_oracle.c")
     if (not force and os.path.exists(_LIB_PATH)
-            and os.path.getmtime(_LIB_PATH) >= os.path.getmtime(src)):
+            and os.path.getmtime(_LIB_PATH) >= max(os.path.getmtime(src), os.path.getmtime(src2))):
         return _LIB_PATH
     os.makedirs(os.path.dirname(_LIB_PATH), exist_ok=True)
     subprocess.check_call(["gcc", "-O2", "-std=c11", "-fPIC", "-shared", "-ffp-contract=off", "-fno-builtin-pow",
-                           src, "-o", _LIB_PATH, "-lm"])
+                           src, src2, "-o", _LIB_PATH, "-lm"])
     return _LIB_PATH
 
 
@@ -181,3 +182,69 @@ class Oracle(object):
         rc = self.L.orc_get(self.E, fid, _p(out))
         assert rc == 0, name
         return out
+
+
+# ---- exogenous generator oracle (oracle/exo_oracle.c) ----
+class ExoOracle(object):
+    """CPU restatement of the reference's PV / wind / price generation on the per-hub X stream (include/chub_exo.h)."""
+
+    def __init__(self, H, tables, renew_fluctuate=0.0, price_fluctuate=0.0):
+        self.L, self.H = lib(), H
+        L = self.L
+        L.exo_create.restype = ctypes.c_void_p
+        L.exo_create.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                                 ctypes.c_void_p, ctypes.c_double, ctypes.c_double]
+        L.exo_destroy.argtypes = [ctypes.c_void_p]
+        L.exo_seed_base.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64]
+        L.exo_reset.argtypes = [ctypes.c_void_p] + [ctypes.c_void_p] * 4
+        L.exo_step.argtypes = [ctypes.c_void_p] + [ctypes.c_void_p] * 4
+        L.exo_get_days.argtypes = [ctypes.c_void_p] + [ctypes.c_void_p] * 3
+        pv = np.ascontiguousarray(tables["pv_days"], np.float64)
+        wd = np.ascontiguousarray(tables["wd_days"], np.float64)
+        pr = np.ascontiguousarray(tables["price"], np.float64)
+        self.X = L.exo_create(H, _p(pv), pv.shape[0], _p(wd), wd.shape[0], _p(pr), float(renew_fluctuate),
+                              float(price_fluctuate))
+
+    def __del__(self):
+        try:
+            self.L.exo_destroy(self.X)
+        except Exception:
+            pass
+
+    def seed_base(self, base_seed, hub_id_base=0):
+        self.L.exo_seed_base(self.X, int(base_seed), int(hub_id_base))
+
+    def reset(self, mask=None):
+        """Values of the state at time 0 after a reset: (pv, wd, price), each [H]; masked-out hubs keep zeros."""
+        out = [np.zeros(self.H, np.float64) for _ in range(3)]
+        m = None if mask is None else np.ascontiguousarray(mask, np.uint8)
+        self.L.exo_reset(self.X, _p(m), _p(out[0]), _p(out[1]), _p(out[2]))
+        return out
+
+    def step(self, time_prev):
+        """Values of the state entered by a step taken at per-hub time slot `time_prev`."""
+        out = [np.zeros(self.H, np.float64) for _ in range(3)]
+        tp = np.ascontiguousarray(np.broadcast_to(np.asarray(time_prev, np.int32), (self.H,)), np.int32)
+        self.L.exo_step(self.X, _p(tp), _p(out[0]), _p(out[1]), _p(out[2]))
+        return out
+
+    def days(self):
+        a, b, c = np.zeros(self.H, np.int32), np.zeros(self.H, np.int32), np.zeros(self.H, np.uint32)
+        self.L.exo_get_days(self.X, _p(a), _p(b), _p(c))
+        return a, b, c
+
+
+def exo_normals(k0, k1, ctr0, n):
+    L = lib()
+    L.exo_normals.argtypes = [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_int, ctypes.c_void_p,
+                              ctypes.c_void_p]
+    out, after = np.zeros(n, np.float64), np.zeros(1, np.uint32)
+    L.exo_normals(int(k0), int(k1), int(ctr0), n, _p(out), _p(after))
+    return out, int(after[0])
+
+
+def exo_rand31(k0, k1, ctr):
+    L = lib()
+    L.exo_rand31.restype = ctypes.c_uint32
+    L.exo_rand31.argtypes = [ctypes.c_uint32] * 3
+    return int(L.exo_rand31(int(k0), int(k1), int(ctr)))
