@@ -7,6 +7,7 @@ are what pins the oracle (tests/test_oracle_golden.py) and the CUDA engine (test
 on machines where /root/reference does not exist.  Run:  python -m oracle.gen_golden
 """
 import os
+import sys
 
 import numpy as np
 
@@ -31,6 +32,14 @@ CASES = {
                                3, 96, 15),
 }
 
+# scalar-load path (stations stepped through evs_step(float), CHS.hpp:1169-1186 / 1478-1495): the fixture also
+# holds "loads" float32 [T, H, 2], the station power targets in kW
+LOAD_CASES = {
+    "load_default_hub": (BASE, 5, 96, 21),
+    "load_constant_charging": (dict(BASE, constant_charging=True), 3, 96, 22),
+    "load_slow_first_small": (dict(BASE, station_list=[9, 3], station_type_list=["slow", "fast"], init_soc=0.6), 3, 96, 23),
+}
+
 KEEP = ["pile_car", "pile_charge", "pile_urgent", "pile_stay", "pile_already", "pile_soc", "pile_target",
         "pile_power", "pile_arrive", "st_line", "st_flow_in", "st_car_number", "st_min_power", "st_charge_power",
         "st_max_power", "hub_t", "hub_uctr", "hub_lcg", "fcev_arrive", "fcev_qn", "hub_done", "store", "store_soc",
@@ -41,10 +50,19 @@ KEEP = ["pile_car", "pile_charge", "pile_urgent", "pile_stay", "pile_already", "
 def main():
     os.makedirs(OUT, exist_ok=True)
     tabs = ref_rollout.reference_tables()
-    for name, (kw, H, T, seed) in CASES.items():
+    only = set(sys.argv[1:])
+    for name, (kw, H, T, seed) in list(CASES.items()) + list(LOAD_CASES.items()):
+        if only and name not in only:
+            continue
         A = sum(kw["station_list"]) + 2
-        actions = np.random.RandomState(1234 + seed).uniform(-1, 1, (T, H, A)).astype(np.float32)
-        out, env = ref_rollout.reference_rollout(kw, seed, np.arange(H), actions)
+        rs = np.random.RandomState(1234 + seed)
+        actions = rs.uniform(-1, 1, (T, H, A)).astype(np.float32)
+        loads = None
+        if name in LOAD_CASES:
+            cap = np.array([40.0 * n for n in kw["station_list"]])
+            loads = (rs.uniform(-0.1, 1.0, (T, H, 2)) ** 2 * cap).astype(np.float32)
+            loads[rs.uniform(size=loads.shape) < 0.1] = 1e9
+        out, env = ref_rollout.reference_rollout(kw, seed, np.arange(H), actions, loads=loads)
         pack = {k: out[k] for k in KEEP}
         for k in ("pile_car", "pile_charge", "pile_urgent", "pile_stay", "pile_already"):
             pack[k] = pack[k].astype(np.int8)
@@ -53,6 +71,8 @@ def main():
         pack["hub_uctr"] = pack["hub_uctr"].astype(np.uint32)
         pack["hub_lcg"] = pack["hub_lcg"].astype(np.uint32)
         pack["actions"] = actions
+        if loads is not None:
+            pack["loads"] = loads
         pack["el_table"] = np.array(env.hy_sys.hy_power_speed_list, np.float64)
         pack["transformer"] = np.array([s.transformer_limit for s in env.env_aggregator.evcssp_evs_objects], np.float64)
         kws = dict(kw)

@@ -76,6 +76,7 @@ def lib():
         L.orc_seed_base.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64]
         L.orc_reset.argtypes = [ctypes.c_void_p] * 5
         L.orc_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 3
+        L.orc_set_load_mode.argtypes = [ctypes.c_void_p, ctypes.c_int]
         L.orc_get.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
         L.orc_get.restype = ctypes.c_int
         L.orc_curve_batch.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long, ctypes.c_int]
@@ -175,6 +176,10 @@ class Oracle(object):
         assert actions.ndim == 2 and actions.shape[0] == self.H
         pv, wd, price = self._tr(pv), self._tr(wd), self._tr(price)
         self.L.orc_step(self.E, _p(actions), actions.shape[1], _p(pv), _p(wd), _p(price))
+
+    def set_load_mode(self, on=True):
+        """Rows passed to step() become [load0 kW, load1 kW, action[-2], action[-1]] (CHS.hpp:1169-1186, 1478-1495)."""
+        self.L.orc_set_load_mode(self.E, int(bool(on)))
 
     def get(self, name):
         fid, dt, shp = FIELD[name]

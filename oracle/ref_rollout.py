@@ -58,8 +58,32 @@ def _snap_station(st, out, t, h, s):
     out["st_max_power"][t, h, s] = d["max_power"]
 
 
-def reference_rollout(kwargs, base_seed, hub_ids, actions, py_seed=0, env=None):
-    """actions: float32 [T, H, A].  Returns (dict of arrays with leading [T+1, H], env)."""
+class _LoadStation(object):
+    """Wiring only: forwards everything to the reference station object, but answers the aggregator's
+    evs_step(Vector_float) (Aggregator_Simple.py:141-142) with the station's own evs_step(float) (CHS.hpp:1169 /
+    1478) on the power target set for this step.  Both sides of the call stay the unmodified reference."""
+
+    def __init__(self, st):
+        object.__setattr__(self, "_st", st)
+        object.__setattr__(self, "load", 0.0)
+
+    def evs_step(self, _pile_actions):
+        self._st.evs_step(float(np.float32(self.load)))
+
+    def __getattr__(self, name):
+        return getattr(self._st, name)
+
+    def __setattr__(self, name, value):
+        if name == "load":
+            object.__setattr__(self, name, value)
+        else:
+            setattr(self._st, name, value)
+
+
+def reference_rollout(kwargs, base_seed, hub_ids, actions, py_seed=0, env=None, loads=None):
+    """actions: float32 [T, H, A].  loads: None, or float32 [T, H, 2] station power targets (kW): the stations are then
+    stepped through evs_step(float) and the per-pile entries of `actions` are ignored.
+    Returns (dict of arrays with leading [T+1, H], env)."""
     ps = ref_env.load_shim()
     Env = ref_env.load_reference_env_class()
     T, H, A = actions.shape
@@ -70,6 +94,11 @@ def reference_rollout(kwargs, base_seed, hub_ids, actions, py_seed=0, env=None):
     if env is None:
         with ref_env.quiet():
             env = Env(**kwargs)
+    if loads is not None:
+        objs = env.env_aggregator.evcssp_evs_objects
+        for k in range(len(objs)):
+            if not isinstance(objs[k], _LoadStation):
+                objs[k] = _LoadStation(objs[k])
     S = T + 1
     out = {}
     for name in ("pile_car", "pile_charge", "pile_urgent", "pile_stay", "pile_already"):
@@ -109,6 +138,9 @@ def reference_rollout(kwargs, base_seed, hub_ids, actions, py_seed=0, env=None):
             env.reset()
             snap(0, h)
             for t in range(T):
+                if loads is not None:
+                    for k, st in enumerate(env.env_aggregator.evcssp_evs_objects):
+                        st.load = loads[t, h, k]
                 _, r, d, _ = env.step(actions[t, h])
                 snap(t + 1, h)
                 out["reward"][t + 1, h] = r

@@ -29,7 +29,7 @@ def load_case(path):
 
 
 def test_fixtures_present():
-    assert len(GOLD) >= 6
+    assert len(GOLD) >= 9
 
 
 def test_tables_match_reference(tables):
@@ -50,6 +50,9 @@ def test_oracle_reproduces_reference(path, tables):
     assert d["transformer0"] == z["transformer"][0] and d["transformer1"] == z["transformer"][1]
     orc.seed_base(int(z["base_seed"]), 0)
     orc.reset(z["pv"][0], z["wd"][0], z["price"][0])
+    loads = z["loads"] if "loads" in z.files else None
+    if loads is not None:
+        orc.set_load_mode(True)
 
     def check(t):
         for name in EXACT + (STEP_ONLY_EXACT if t else []):
@@ -65,6 +68,7 @@ def test_oracle_reproduces_reference(path, tables):
 
     check(0)
     for t in range(T):
-        orc.step(z["actions"][t], z["pv"][t + 1], z["wd"][t + 1], z["price"][t + 1])
+        rows = z["actions"][t] if loads is None else np.concatenate([loads[t], z["actions"][t][:, -2:]], axis=1)
+        orc.step(rows, z["pv"][t + 1], z["wd"][t + 1], z["price"][t + 1])
         check(t + 1)
     assert (orc.get("hub_err") == 0).all()
