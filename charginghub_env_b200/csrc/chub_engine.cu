@@ -48,6 +48,7 @@ struct chub_engine {
     double exo_renew_gain = 1.0, exo_price_gain = 1.0;
     double *exo_d = nullptr, *pv_days = nullptr, *wd_days = nullptr;
     uint2 *exo_i = nullptr;
+    unsigned long long *act_bits = nullptr;  // pile on-bits of the scalar-load step (chub_step_loads)
     cudaStream_t host_streams[3] = {nullptr, nullptr, nullptr};  // chub_step_host pipeline: copy in, step, copy out
     cudaEvent_t host_events[2 * 16 + 2] = {};
     int trace_len = 0, trace_per_hub = 0;
@@ -71,7 +72,7 @@ static void engine_free(chub_engine *e) {
         if (ev) cudaEventDestroy(ev);
     void *ptrs[] = {e->pile, e->arrive, e->hubA, e->store, e->keys, e->occ, e->cls, e->stats, e->last_stats, e->err, e->qsoc,
                     e->d_classes, e->d_el, e->lut, e->s2t_lut, e->pv, e->wd, e->price_tr, e->obs, e->reward, e->done, e->diag,
-                    e->st_power, e->step_index, e->actions_stage, e->exo_d, e->exo_i, e->pv_days, e->wd_days};
+                    e->st_power, e->step_index, e->actions_stage, e->exo_d, e->exo_i, e->pv_days, e->wd_days, e->act_bits};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     delete e;
@@ -495,6 +496,29 @@ extern "C" int chub_step(chub_engine *e, const float *actions_dev, void *stream)
     if (rc) return rc;
     P.actions = actions_dev;
     cudaStream_t s = (cudaStream_t) stream;
+    CK(chub_launch_step(P, s));
+    chub_launch_tick(e->step_index, 1, s);
+    CK(cudaGetLastError());
+    e->launches += 1;
+    return CHUB_OK;
+}
+
+// Scalar-load step: rows [load0 kW, load1 kW, a[-2], a[-1]]; the dispatch kernel turns the two station power targets
+// into pile on-bits (evs_step(float), CHS.hpp:1169-1186 / 1478-1495), then the ordinary step kernel runs on them.
+extern "C" int chub_step_loads(chub_engine *e, const float *loads_dev, void *stream) {
+    if (!e || !loads_dev) return fail(CHUB_ERR_ARG, "chub_step_loads: null argument");
+    CK(cudaSetDevice(e->cfg.device));
+    ChubParams P;
+    int rc = fill_params(e, P);
+    if (rc) return rc;
+    if (!e->act_bits) {
+        CK(cudaMalloc((void **) &e->act_bits, sizeof(unsigned long long) * (size_t) e->Hpad));
+        CK(cudaMemset(e->act_bits, 0, sizeof(unsigned long long) * (size_t) e->Hpad));
+    }
+    P.actions = loads_dev;
+    cudaStream_t s = (cudaStream_t) stream;
+    chub_launch_dispatch(P, e->act_bits, s);
+    P.act_bits = e->act_bits;
     CK(chub_launch_step(P, s));
     chub_launch_tick(e->step_index, 1, s);
     CK(cudaGetLastError());

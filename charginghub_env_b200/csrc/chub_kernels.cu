@@ -652,6 +652,14 @@ __device__ __forceinline__ void load_actions(const ChubParams &P, float *stage, 
     const int h0 = h - lane;
     const int stride = P.action_stride;
     bits = 0ull; a_m2 = 0.0f; a_m1 = 0.0f;
+    if (P.act_bits) {   // scalar-load mode: chub_dispatch_kernel already turned the two power targets into pile bits
+        if (active) {
+            bits = P.act_bits[h];
+            a_m2 = __ldg(P.actions + (size_t) h * 4 + 2);
+            a_m1 = __ldg(P.actions + (size_t) h * 4 + 3);
+        }
+        return;
+    }
     const bool staged = (h0 + 32 <= P.h_end) && (32 * stride <= stage_floats) &&
                         ((reinterpret_cast<uintptr_t>(P.actions) & 15u) == 0);
     const float *src = P.actions + (size_t) h * stride;
@@ -987,6 +995,93 @@ static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s) {
 // Launch shape.  One block per SM; the step's duration is (rounds of blocks over the SMs) x (warps per block) to
 // within a few per cent for 16..28 warps (measured), so the block size is chosen to waste the least of the last
 // round: 524,288 hubs are 3.95 rounds of 28-warp blocks but 4.6 of 24-warp ones.  CHUB_BLOCK overrides.
+// ---- scalar-load dispatch: the stations' evs_step(float) (CHS.hpp:1169-1186 slow, 1478-1495 fast) ----
+// The reference clamps the station's power target to [min_power, max_power] (catch_load, CHS.hpp:358-366), orders the
+// piles by urgency (a multimap keyed by -emergency: ties keep pile order, CHS.hpp:1375-1390) and switches cars on along
+// that order while the running fp32 sum of their posted powers stays within target + 1e-4 (CHS.hpp:1355-1360); with
+// constant-power charging it switches on the first round(target / constant_power) cars instead (CHS.hpp:1338-1349).
+// Everything after that -- car_step, remove_car, receive_car -- is the per-pile path, so this kernel only turns the two
+// targets of a hub into the same on-bits that a per-pile action row would give and the step kernel runs unchanged.
+// One thread per hub; urgencies and powers of its occupied piles wait in shared memory for the selection loop.
+// emergency = (needed / left)^2 is pow(float, 2) in double narrowed to float (CHS.hpp:890-891): the exact product
+// rounded once, which is what the fp32 multiply gives.
+// @region load dispatch
+#define DISPATCH_WARPS 4
+__device__ __forceinline__ int dispatch_pick(const float (*es)[32], int lane, uint32_t rem) {
+    float best = -1.0f;
+    int bi = 0;
+    for (uint32_t m = rem; m; m &= m - 1u) {
+        const int j = __ffs(m) - 1;
+        const float e = es[j][lane];
+        if (e > best) { best = e; bi = j; }   // strict: equal urgencies keep pile order
+    }
+    return bi;
+}
+
+__device__ __forceinline__ uint32_t dispatch_station(const ChubParams &P, float (*es)[32], float (*ps)[32], int h, int lane,
+                                                     int slot0, int type, int cp, uint32_t occ, float load) {
+    const uint4 *rp = P.pile + chub_pile_index(h, slot0, P.S0 + P.S1);
+    const float *tlut = P.s2t_lut + (cp * 2 + type) * 1000;
+    float mn = 0.0f, mx = 0.0f;
+    for (uint32_t m = occ; m; m &= m - 1u) {   // calculate_needed + calculate_output, ascending pile order
+        const int i = __ffs(m) - 1;
+        const uint4 r = rp[i * 32];
+        const float needed = __ldg(&tlut[PW_TU(r.w)]) - __uint_as_float(r.y);
+        const int left = (int) PW_STAY(r.w) - (int) PW_ALREADY(r.w);
+        float e = 0.0f;
+        if (needed > 0.0f) {
+            if ((float) left <= ceilf(needed)) e = 10.0f;
+            else { const float q = needed / (float) left; e = q * q; }
+        }
+        const float p = __uint_as_float(r.z);
+        mx += p;
+        if (e > 8.0f) mn += p;
+        es[i][lane] = e;
+        ps[i][lane] = p;
+    }
+    if (load > mx) load = mx;                  // catch_load
+    else if (load < mn) load = mn;
+    uint32_t on = 0u, rem = occ;
+    if (cp) {
+        const float cpw = type == CHUB_SLOW ? (float) 5.254973139368931 : (float) 36.44764034125146;
+        int k = (int) roundf(load / cpw);
+        for (; rem && k > 0; --k) {
+            const int bi = dispatch_pick(es, lane, rem);
+            rem &= ~(1u << bi);
+            on |= 1u << bi;
+        }
+    } else {
+        const double lim = (double) load + 0.0001;
+        float cum = 0.0f;
+        while (rem) {
+            const int bi = dispatch_pick(es, lane, rem);
+            rem &= ~(1u << bi);
+            cum += ps[bi][lane];
+            if (!(lim >= (double) cum)) break;   // powers are >= 0: the running sum never comes back under the target
+            on |= 1u << bi;
+        }
+    }
+    return on;
+}
+
+__global__ void __launch_bounds__(DISPATCH_WARPS * 32) chub_dispatch_kernel(const __grid_constant__ ChubParams P,
+                                                                           unsigned long long *out) {
+    __shared__ float es[DISPATCH_WARPS][32][32], ps[DISPATCH_WARPS][32][32];
+    const int h = blockIdx.x * (DISPATCH_WARPS * 32) + threadIdx.x, lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+    if (h >= P.H) return;
+    const ChubClass &c = P.classes[P.cls ? __ldg(&P.cls[h]) : 0];
+    const uint2 occ = P.occ[h];
+    const float load0 = __ldg(P.actions + (size_t) h * 4), load1 = __ldg(P.actions + (size_t) h * 4 + 1);
+    const uint32_t on0 = dispatch_station(P, es[wp], ps[wp], h, lane, 0, c.type[0], c.constant, occ.x, load0);
+    const uint32_t on1 = dispatch_station(P, es[wp], ps[wp], h, lane, P.S0, c.type[1], c.constant, occ.y, load1);
+    out[h] = (unsigned long long) on0 | ((unsigned long long) on1 << c.n[0]);
+}
+
+void chub_launch_dispatch(const ChubParams &p, unsigned long long *act_bits, cudaStream_t s) {
+    const int threads = DISPATCH_WARPS * 32;
+    chub_dispatch_kernel<<<(p.H + threads - 1) / threads, threads, 0, s>>>(p, act_bits);
+}
+
 cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s) {
     int shape = p.block;
     if (shape == 0) {

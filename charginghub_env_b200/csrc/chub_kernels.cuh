@@ -63,6 +63,7 @@ struct ChubParams {
     uint2 *exo_i;                     // [Hpad]: {pv_day | wd_day << 10 | price_count mod 4 << 20, X-stream counter}
     const double *pv_days, *wd_days;  // [n][96]
     const float *actions;
+    const unsigned long long *act_bits;  // scalar-load mode: pile on-bits from chub_dispatch_kernel; actions = [H][4] rows
     float *obs;
     float *reward;
     uint8_t *done;
@@ -73,6 +74,7 @@ struct ChubParams {
 
 cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s);
 void chub_launch_reset(const ChubParams &p, cudaStream_t s);
+void chub_launch_dispatch(const ChubParams &p, unsigned long long *act_bits, cudaStream_t s);
 void chub_launch_s2t_lut(float *out, cudaStream_t s);
 void chub_launch_tick(long long *step_index, int n, cudaStream_t s);
 cudaError_t chub_upload_const(const ChubConst &c);

@@ -198,6 +198,14 @@ class HubEngine(object):
         check(self.lib.chub_step(self.h, _tensor_ptr(actions), self._stream(stream)))
         return self.tensor("obs"), self.tensor("reward"), self.tensor("done")
 
+    def step_loads(self, loads, stream=None):
+        """The stations' scalar-load step, evs_step(float) (CHS.hpp:1169-1186, 1478-1495).  loads: CUDA float32
+        [n_hubs, 4], row = [power target of station 0 in kW, of station 1, a[-2], a[-1]]."""
+        if tuple(loads.shape) != (self.n_hubs, 4):
+            raise ValueError("loads must be [%d, 4]" % self.n_hubs)
+        check(self.lib.chub_step_loads(self.h, _tensor_ptr(loads), self._stream(stream)))
+        return self.tensor("obs"), self.tensor("reward"), self.tensor("done")
+
     def capture_rollout(self, actions, n_steps, stream=None):
         check(self.lib.chub_rollout_capture(self.h, _tensor_ptr(actions), int(n_steps), self._stream(stream)))
 

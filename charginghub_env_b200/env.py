@@ -207,6 +207,11 @@ class BatchedHubEnv(object):
         obs, reward, done = self.engine.step(actions)
         return obs, reward, done, {}
 
+    def step_loads(self, loads):
+        """Upper-level control: one power target (kW) per station, rows [load0, load1, a[-2], a[-1]]."""
+        obs, reward, done = self.engine.step_loads(loads)
+        return obs, reward, done, {}
+
     def capture_rollout(self, actions, n_steps):
         self.engine.capture_rollout(actions, n_steps)
 

@@ -163,6 +163,14 @@ int chub_reset(chub_engine *e, const uint8_t *mask_dev, int64_t step_index, void
  * in [-1,1] exactly as the reference's action vector.  Fills obs / reward / done buffers. */
 int chub_step(chub_engine *e, const float *actions_dev, void *stream);
 
+/* The stations' scalar-load step, evs_step(float) (CHS.hpp:1169-1186 slow, 1478-1495 fast; bound in main.cpp:196-197):
+ * each station gets ONE power target in kW instead of per-pile switches; it is clamped to [min_power, max_power]
+ * (catch_load, CHS.hpp:358-366) and handed out to the cars in order of urgency (assign_on_off / rank_power_add,
+ * CHS.hpp:1318-1362, 1375-1402).  The rest of the hub step is chub_step's.
+ * loads_dev: float32 [n_hubs][4], row = [target of station 0, target of station 1, a[-2], a[-1]]; the last two are the
+ * electrolyser / fuel-cell actions in [-1,1] as in chub_step.  Targets must be finite. */
+int chub_step_loads(chub_engine *e, const float *loads_dev, void *stream);
+
 /* The same through HOST buffers (what a CPU caller of the reference has): copies the actions in,
  * steps, copies obs/reward/done out, and synchronises the stream.  Any out pointer may be NULL. */
 int chub_step_host(chub_engine *e, const float *actions_host, float *obs_host, float *reward_host,

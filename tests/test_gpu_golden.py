@@ -53,7 +53,11 @@ def test_engine_reproduces_reference_trace(path, tables):
 
     check(0, obs)
     for t in range(T):
-        obs, rew, done = eng.step(torch.from_numpy(z["actions"][t]).cuda())
+        if "loads" in z.files:   # scalar-load fixtures: stations stepped through evs_step(float)
+            rows = np.concatenate([z["loads"][t], z["actions"][t][:, -2:]], axis=1).astype(np.float32)
+            obs, rew, done = eng.step_loads(torch.from_numpy(rows).cuda())
+        else:
+            obs, rew, done = eng.step(torch.from_numpy(z["actions"][t]).cuda())
         check(t + 1, obs, rew, done)
     assert eng.counters()["error_or"] == 0
     assert np.allclose(eng.class_table(0), z["el_table"])
