@@ -187,6 +187,9 @@ def main():
     ap.add_argument("--hubs", type=int, default=0, help="override hubs per GPU")
     ap.add_argument("--e2e-steps", type=int, default=24)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--control", default="piles", choices=["piles", "loads"],
+                    help="piles: per-pile action rows (the gym env's step, default); loads: one power target per station "
+                         "(the stations' evs_step(float)), which adds the dispatch kernel to every step")
     ap.add_argument("--exogenous", default="traces", choices=["traces", "device"],
                     help="traces: shared synthetic year (default); device: the on-device PV/wind/price generator")
     args = ap.parse_args()
@@ -225,6 +228,16 @@ def main():
     gen = torch.Generator(device="cuda").manual_seed(1234 + rank)
     npool = 4  # rotating action matrices; state + actions per step exceed the 126 MB L2 for config5/config3
     pool = [torch.rand((H, S), device="cuda", generator=gen) * 2 - 1 for _ in range(npool)]
+    step = eng.step
+    if args.control == "loads":
+        caps = torch.tensor([[40.0 * n for n in c["station_list"]] for c in wl["classes"]], device="cuda")
+        caps = caps[torch.as_tensor(wl["hub_class"], device="cuda").long()] if wl["hub_class"] is not None else caps[:1]
+        pool = [torch.cat([torch.rand((H, 2), device="cuda", generator=gen) ** 2 * caps,
+                           torch.rand((H, 2), device="cuda", generator=gen) * 2 - 1], dim=1).contiguous()
+                for _ in range(npool)]
+        step = eng.step_loads
+        host_rows = torch.rand((H, S), device="cuda", generator=gen) * 2 - 1   # the e2e leg stays the per-pile call
+        wl["desc"] += ", scalar-load control (dispatch kernel + step kernel)"
     eng.reset()
     torch.cuda.synchronize()
 
@@ -240,7 +253,7 @@ def main():
             dist.gather(stats, gathered, dst=0)
 
     for i in range(W):
-        eng.step(pool[i % npool])
+        step(pool[i % npool])
     gather_stats()  # warm-up includes the collective: NCCL sets its channels up on first use
     barrier()
     sampler = ClockSampler(local)
@@ -251,7 +264,7 @@ def main():
     barrier()
     ev0.record()
     for i in range(K):
-        eng.step(pool[i % npool])
+        step(pool[i % npool])
     gather_stats()
     ev1.record()
     barrier()
@@ -266,7 +279,7 @@ def main():
 
     # ---- end to end through the host-buffer C ABI call (pinned host memory both ways) ----
     hb = eng.host_buffers()
-    hb["actions"][...] = pool[0].cpu().numpy()
+    hb["actions"][...] = (host_rows if args.control == "loads" else pool[0]).cpu().numpy()
     KE = max(2, min(args.e2e_steps, K))
     for _ in range(2):
         eng.step_host()
@@ -305,7 +318,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(H * S * 4),
                     "d2h_bytes_per_step": int(H * (13 * 4 + 4 + 1)), "steps": KE,
                     "api": "chub_step_host: pinned host actions -> device, step, obs/reward/done -> pinned host, pipelined over %d hub ranges" % host_chunks},
-            "gpu_launches": int(launches) * 2 + KE * (host_chunks + 1),
+            "gpu_launches": int(launches) * (3 if args.control == "loads" else 2) + KE * (host_chunks + 1),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_detail": traffic_detail, "peak_source": peak_src, "algorithmic_bytes_per_hub_step": bytes_per_hub,
                          "kernel": "chub_step_kernel", "kernel_ms": kernel_ms},
