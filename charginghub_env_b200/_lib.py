@@ -78,6 +78,8 @@ SYMBOLS = {
     "chub_reset": (ctypes.c_int, [_vp, _vp, _i64, _vp]),
     "chub_step": (ctypes.c_int, [_vp, _vp, _vp]),
     "chub_step_loads": (ctypes.c_int, [_vp, _vp, _vp]),
+    "chub_situation_width": (ctypes.c_int, [_vp, _vp, _vp]),
+    "chub_situation": (ctypes.c_int, [_vp, _vp, _vp]),
     "chub_step_host": (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "chub_reset_host": (ctypes.c_int, [_vp, _vp, _vp]),
     "chub_rollout_capture": (ctypes.c_int, [_vp, _vp, _i32, _vp]),

@@ -526,6 +526,24 @@ extern "C" int chub_step_loads(chub_engine *e, const float *loads_dev, void *str
     return CHUB_OK;
 }
 
+extern "C" int chub_situation_width(chub_engine *e, int32_t *s0, int32_t *s1) {
+    if (!e || !e->have_classes) return fail(CHUB_ERR_STATE, "chub_situation_width: call chub_set_hub_classes first");
+    if (s0) *s0 = e->S0;
+    if (s1) *s1 = e->S1;
+    return CHUB_OK;
+}
+
+extern "C" int chub_situation(chub_engine *e, float *out_dev, void *stream) {
+    if (!e || !out_dev) return fail(CHUB_ERR_ARG, "chub_situation: null argument");
+    CK(cudaSetDevice(e->cfg.device));
+    ChubParams P;
+    int rc = fill_params(e, P);
+    if (rc) return rc;
+    chub_launch_situation(P, out_dev, (cudaStream_t) stream);
+    CK(cudaGetLastError());
+    return CHUB_OK;
+}
+
 // Host-buffer step.  The batch is cut into hub ranges that flow through three streams -- actions host->device,
 // step kernel, obs/reward/done device->host -- so the two PCIe directions and the kernel overlap; hubs are
 // independent, so stepping them range by range is the same computation as one launch.

@@ -1018,6 +1018,16 @@ __device__ __forceinline__ int dispatch_pick(const float (*es)[32], int lane, ui
     return bi;
 }
 
+// calculate_needed (CHS.hpp:879-898 / 1044-1063) from a pile record: s2t(soc) is cached, s2t(target) is a table
+__device__ __forceinline__ float pile_emergency(const float *tlut, const uint4 r) {
+    const float needed = __ldg(&tlut[PW_TU(r.w)]) - __uint_as_float(r.y);
+    const int left = (int) PW_STAY(r.w) - (int) PW_ALREADY(r.w);
+    if (!(needed > 0.0f)) return 0.0f;
+    if ((float) left <= ceilf(needed)) return 10.0f;
+    const float q = needed / (float) left;
+    return q * q;
+}
+
 __device__ __forceinline__ uint32_t dispatch_station(const ChubParams &P, float (*es)[32], float (*ps)[32], int h, int lane,
                                                      int slot0, int type, int cp, uint32_t occ, float load) {
     const uint4 *rp = P.pile + chub_pile_index(h, slot0, P.S0 + P.S1);
@@ -1026,13 +1036,7 @@ __device__ __forceinline__ uint32_t dispatch_station(const ChubParams &P, float 
     for (uint32_t m = occ; m; m &= m - 1u) {   // calculate_needed + calculate_output, ascending pile order
         const int i = __ffs(m) - 1;
         const uint4 r = rp[i * 32];
-        const float needed = __ldg(&tlut[PW_TU(r.w)]) - __uint_as_float(r.y);
-        const int left = (int) PW_STAY(r.w) - (int) PW_ALREADY(r.w);
-        float e = 0.0f;
-        if (needed > 0.0f) {
-            if ((float) left <= ceilf(needed)) e = 10.0f;
-            else { const float q = needed / (float) left; e = q * q; }
-        }
+        const float e = pile_emergency(tlut, r);
         const float p = __uint_as_float(r.z);
         mx += p;
         if (e > 8.0f) mn += p;
@@ -1080,6 +1084,41 @@ __global__ void __launch_bounds__(DISPATCH_WARPS * 32) chub_dispatch_kernel(cons
 void chub_launch_dispatch(const ChubParams &p, unsigned long long *act_bits, cudaStream_t s) {
     const int threads = DISPATCH_WARPS * 32;
     chub_dispatch_kernel<<<(p.H + threads - 1) / threads, threads, 0, s>>>(p, act_bits);
+}
+
+// ---- per-pile introspection: the stations' `situation` columns (CHS.hpp:204-231, read through main.cpp:54-74,
+// 142-184) as dense device matrices.  out: float32 [CHUB_SIT_COLUMNS][H][S0+S1]; slots of station 0 come first, slots
+// beyond a station's pile count and piles without a car read 0 like a reset position.
+// @region situation
+__global__ void __launch_bounds__(256) chub_situation_kernel(const __grid_constant__ ChubParams P, float *out) {
+    const int S = P.S0 + P.S1;
+    const long long idx = (long long) blockIdx.x * 256 + threadIdx.x;
+    if (idx >= (long long) P.H * S) return;
+    const int h = (int) (idx / S), slot = (int) (idx - (long long) h * S);
+    const ChubClass &c = P.classes[P.cls ? __ldg(&P.cls[h]) : 0];
+    const int st = slot >= P.S0, i = slot - (st ? P.S0 : 0);
+    float v[CHUB_SIT_COLUMNS] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+    if (i < c.n[st]) {
+        const size_t at = chub_pile_index(h, slot, S);
+        const uint4 r = P.pile[at];
+        if (r.w & PW_CAR) {
+            v[CHUB_SIT_CAR] = 1.0f;
+            v[CHUB_SIT_CHARGE] = (r.w & PW_CHARGE) ? 1.0f : 0.0f;
+            v[CHUB_SIT_EMERGENCY] = pile_emergency(P.s2t_lut + (c.constant * 2 + c.type[st]) * 1000, r);
+            v[CHUB_SIT_POWER] = __uint_as_float(r.z);
+            v[CHUB_SIT_SOC] = __uint_as_float(r.x);
+            v[CHUB_SIT_INIT_SOC] = P.arrive[at];
+            v[CHUB_SIT_TARGET_SOC] = target_of(PW_TU(r.w));
+        }
+    }
+    const size_t plane = (size_t) P.H * S;
+#pragma unroll
+    for (int k = 0; k < CHUB_SIT_COLUMNS; ++k) out[k * plane + idx] = v[k];
+}
+
+void chub_launch_situation(const ChubParams &p, float *out, cudaStream_t s) {
+    const long long n = (long long) p.H * (p.S0 + p.S1);
+    chub_situation_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(p, out);
 }
 
 cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s) {

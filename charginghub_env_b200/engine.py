@@ -206,6 +206,22 @@ class HubEngine(object):
         check(self.lib.chub_step_loads(self.h, _tensor_ptr(loads), self._stream(stream)))
         return self.tensor("obs"), self.tensor("reward"), self.tensor("done")
 
+    SITUATION_COLUMNS = ("car", "charge", "emergency", "assign", "power", "soc", "init_soc", "target_soc")
+
+    def situation(self, out=None, stream=None):
+        """The stations' `situation` table (CHS.hpp:204-231) as CUDA float32 matrices [n_hubs, S0 + S1] per column
+        (station 0's piles first).  Returns (dict column -> view, (S0, S1)); `out` may be a reusable [8, H, S] tensor."""
+        import torch
+        s0, s1 = ctypes.c_int32(0), ctypes.c_int32(0)
+        check(self.lib.chub_situation_width(self.h, ctypes.byref(s0), ctypes.byref(s1)))
+        shape = (len(self.SITUATION_COLUMNS), self.n_hubs, s0.value + s1.value)
+        if out is None:
+            out = torch.empty(shape, dtype=torch.float32, device="cuda:%d" % self.device)
+        if tuple(out.shape) != shape or out.dtype != torch.float32:
+            raise ValueError("out must be float32 %r" % (shape,))
+        check(self.lib.chub_situation(self.h, _tensor_ptr(out), self._stream(stream)))
+        return {name: out[k] for k, name in enumerate(self.SITUATION_COLUMNS)}, (s0.value, s1.value)
+
     def capture_rollout(self, actions, n_steps, stream=None):
         check(self.lib.chub_rollout_capture(self.h, _tensor_ptr(actions), int(n_steps), self._stream(stream)))
 

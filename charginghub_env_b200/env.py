@@ -169,8 +169,9 @@ class EvcsspManagerEnv_v6(_EnvBase):
             self.engine.close()
 
     def show_situation(self):
-        for name in ("pile_car", "pile_charge", "pile_soc", "pile_power", "pile_target", "pile_arrive"):
-            print(name, self.engine.get(name)[0])
+        cols, _ = self.engine.situation()
+        for name in self.engine.SITUATION_COLUMNS:
+            print(name, cols[name][0].cpu().numpy())
 
 
 class BatchedHubEnv(object):

@@ -189,6 +189,17 @@ int chub_buffer(chub_engine *e, int32_t which, void **dev_ptr, int64_t *bytes);
  * keeps the engine alive until its deleter runs. */
 int chub_tensor(chub_engine *e, int32_t which, void **dl_managed_tensor);
 
+/* The stations' `situation` table (CHS.hpp:204-231; what main.cpp:54-74, 142-184 exposes as nested maps) as dense
+ * device matrices for richer observations and debugging: out_dev = float32 [CHUB_SIT_COLUMNS][n_hubs][S], S = the
+ * widest station 0 + the widest station 1 over the hub classes (chub_situation_width); station 0's piles come first.
+ * Piles without a car and slots beyond a station's pile count read 0, as after reset_position.  Asynchronous. */
+enum chub_situation_column {
+    CHUB_SIT_CAR = 0, CHUB_SIT_CHARGE, CHUB_SIT_EMERGENCY, CHUB_SIT_ASSIGN /* always 0 on this path */, CHUB_SIT_POWER,
+    CHUB_SIT_SOC, CHUB_SIT_INIT_SOC, CHUB_SIT_TARGET_SOC, CHUB_SIT_COLUMNS
+};
+int chub_situation_width(chub_engine *e, int32_t *s0, int32_t *s1);
+int chub_situation(chub_engine *e, float *out_dev, void *stream);
+
 /* Parity / checkpoint read-back (synchronises). */
 int chub_get_field(chub_engine *e, int32_t field, void *host_out);
 int64_t chub_state_bytes(chub_engine *e);

@@ -122,3 +122,46 @@ def test_fcev_backlog_overflow_sets_error_bit(tables):
         eng.step(a)
     assert eng.counters()["error_or"] & 1
     assert (eng.tensor("error").cpu().numpy() & 1).any()
+
+
+def test_situation_matrices_match_the_oracle(tables):
+    """chub_situation: the stations' `situation` columns (CHS.hpp:204-231) as device matrices, against the oracle's
+    pile fields, on mixed hub classes (different pile counts, constant charging) in the middle of a day."""
+    import torch
+    from charginghub_env_b200 import HubEngine
+    from oracle import oracle as O
+    classes = [C.DEFAULT_KW, dict(C.DEFAULT_KW, station_list=[7, 30], station_type_list=["slow", "fast"]),
+               dict(C.DEFAULT_KW, station_list=[12, 4], constant_charging=True)]
+    H, seed = 200, 5
+    rs = np.random.RandomState(seed)
+    hub_class = rs.randint(0, 3, H).astype(np.int32)
+    eng = HubEngine(H, classes, hub_class=hub_class, device=0, diagnostics=True, tables=tables, seed=seed)
+    pv, wd, price = C.synth_traces(tables, 50, rs, H)
+    eng.set_traces(pv, wd, price, per_hub=True)
+    orc = O.Oracle(H, classes, hub_class=hub_class, tables=C.oracle_tables(tables))
+    orc.seed_base(seed, 0)
+    eng.reset()
+    orc.reset(pv[0], wd[0], price[0])
+    buf = torch.empty((8, H, 50), dtype=torch.float32, device="cuda")
+    for t in range(45):
+        a = rs.uniform(-1, 1, (H, eng.action_stride)).astype(np.float32)
+        eng.step(torch.from_numpy(a).cuda())
+        orc.step(a, pv[t + 1], wd[t + 1], price[t + 1])
+        if t % 11 and t != 44:
+            continue
+        cols, (s0, s1) = eng.situation(out=buf)
+        torch.cuda.synchronize()
+        assert (s0, s1) == (20, 30)
+        car = orc.get("pile_car")
+        for name, field in (("car", "pile_car"), ("charge", "pile_charge"), ("emergency", "pile_emergency"),
+                            ("power", "pile_power"), ("soc", "pile_soc"), ("init_soc", "pile_arrive"),
+                            ("target_soc", "pile_target")):
+            want = orc.get(field).astype(np.float32)
+            if name != "car":
+                want = want * car     # the oracle keeps some members of empty piles; the table reads 0 there
+            got = cols[name].cpu().numpy()
+            assert got.shape == (H, s0 + s1)
+            assert np.array_equal(got[:, :s0], want[:, 0, :s0]), (name, t, 0)
+            assert np.array_equal(got[:, s0:], want[:, 1, :s1]), (name, t, 1)
+        assert not cols["assign"].any()
+        assert car.sum() > H
