@@ -16,7 +16,7 @@ FCEV_QCAP = 8
 DAY = 96
 FAST, SLOW = 0, 1
 
-BUF_OBS, BUF_REWARD, BUF_DONE, BUF_STATS, BUF_LAST_STATS, BUF_ERROR = range(6)
+BUF_OBS, BUF_REWARD, BUF_DONE, BUF_STATS, BUF_LAST_STATS, BUF_ERROR, BUF_FINAL_SOC = range(7)
 
 # chub_field_id -> (id, numpy dtype name, per-hub shape)
 FIELDS = {

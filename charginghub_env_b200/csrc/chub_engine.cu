@@ -48,6 +48,7 @@ struct chub_engine {
     double exo_renew_gain = 1.0, exo_price_gain = 1.0;
     double *exo_d = nullptr, *pv_days = nullptr, *wd_days = nullptr;
     uint2 *exo_i = nullptr;
+    float *final_soc = nullptr;
     unsigned long long *act_bits = nullptr;  // pile on-bits of the scalar-load step (chub_step_loads)
     cudaStream_t host_streams[3] = {nullptr, nullptr, nullptr};  // chub_step_host pipeline: copy in, step, copy out
     cudaEvent_t host_events[2 * 16 + 2] = {};
@@ -72,7 +73,7 @@ static void engine_free(chub_engine *e) {
         if (ev) cudaEventDestroy(ev);
     void *ptrs[] = {e->pile, e->arrive, e->hubA, e->store, e->keys, e->occ, e->cls, e->stats, e->last_stats, e->err, e->qsoc,
                     e->d_classes, e->d_el, e->lut, e->s2t_lut, e->pv, e->wd, e->price_tr, e->obs, e->reward, e->done, e->diag,
-                    e->st_power, e->step_index, e->actions_stage, e->exo_d, e->exo_i, e->pv_days, e->wd_days, e->act_bits};
+                    e->st_power, e->step_index, e->actions_stage, e->exo_d, e->exo_i, e->pv_days, e->wd_days, e->act_bits, e->final_soc};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     delete e;
@@ -108,7 +109,7 @@ extern "C" int chub_create(const chub_config *cfg, chub_engine **out) {
     cudaError_t r = cudaSuccess;
     auto A = [&](cudaError_t x) { if (r == cudaSuccess) r = x; };
     A(dalloc(&e->hubA, Hp)); A(dalloc(&e->store, Hp)); A(dalloc(&e->keys, Hp)); A(dalloc(&e->occ, Hp));
-    A(dalloc(&e->stats, Hp)); A(dalloc(&e->last_stats, Hp)); A(dalloc(&e->err, Hp));
+    A(dalloc(&e->stats, Hp)); A(dalloc(&e->last_stats, Hp)); A(dalloc(&e->err, Hp)); A(dalloc(&e->final_soc, Hp));
     A(dalloc(&e->qsoc, Hp * CHUB_FCEV_QCAP)); A(dalloc(&e->lut, (size_t) 96 * 1000)); A(dalloc(&e->s2t_lut, (size_t) 4000));
     A(dalloc(&e->obs, Hp * CHUB_OBS_DIM)); A(dalloc(&e->reward, Hp)); A(dalloc(&e->done, Hp));
     A(dalloc(&e->step_index, 1)); A(dalloc(&e->actions_stage, Hp * (size_t) cfg->action_stride));
@@ -466,7 +467,7 @@ static int fill_params(chub_engine *e, ChubParams &P) {
     P.exo_renew_gain = e->exo_renew_gain; P.exo_price_gain = e->exo_price_gain;
     P.exo_d = e->exo_d; P.exo_i = e->exo_i; P.pv_days = e->pv_days; P.wd_days = e->wd_days;
     P.actions = nullptr; P.obs = e->obs; P.reward = e->reward; P.done = e->done;
-    P.diag = e->diag; P.st_power = e->st_power; P.reset_mask = nullptr;
+    P.diag = e->diag; P.st_power = e->st_power; P.reset_mask = nullptr; P.final_soc = e->final_soc;
     return CHUB_OK;
 }
 
@@ -675,6 +676,7 @@ static bool buf_info(chub_engine *e, int which, BufInfo &b) {
         case CHUB_BUF_STATS: b = {e->stats, H * 16, 2, {H, 4}, 2, 32}; return true;
         case CHUB_BUF_LAST_STATS: b = {e->last_stats, H * 16, 2, {H, 4}, 2, 32}; return true;
         case CHUB_BUF_ERROR: b = {e->err, H * 4, 1, {H, 1}, 1, 32}; return true;
+        case CHUB_BUF_FINAL_SOC: b = {e->final_soc, H * 4, 1, {H, 1}, 2, 32}; return true;
     }
     return false;
 }

@@ -921,6 +921,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     st.z += (float) (l0 + l1 + h2_grid);
     st.w += (float) (s0.incomplete + s1.incomplete);
     if (done) {
+        P.final_soc[h] = (float) store_soc;
         P.last_stats[h] = st;
         st = make_float4(0.f, 0.f, 0.f, 0.f);
     }

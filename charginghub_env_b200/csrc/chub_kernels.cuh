@@ -63,6 +63,7 @@ struct ChubParams {
     uint2 *exo_i;                     // [Hpad]: {pv_day | wd_day << 10 | price_count mod 4 << 20, X-stream counter}
     const double *pv_days, *wd_days;  // [n][96]
     const float *actions;
+    float *final_soc;                    // store SOC at the end of the last finished episode (evcssp_manager.py:275-290)
     const unsigned long long *act_bits;  // scalar-load mode: pile on-bits from chub_dispatch_kernel; actions = [H][4] rows
     float *obs;
     float *reward;

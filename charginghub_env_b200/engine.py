@@ -234,7 +234,7 @@ class HubEngine(object):
             return self._tensors[name]
         import torch
         which = {"obs": _lib.BUF_OBS, "reward": _lib.BUF_REWARD, "done": _lib.BUF_DONE, "stats": _lib.BUF_STATS,
-                 "last_stats": _lib.BUF_LAST_STATS, "error": _lib.BUF_ERROR}[name]
+                 "last_stats": _lib.BUF_LAST_STATS, "error": _lib.BUF_ERROR, "final_soc": _lib.BUF_FINAL_SOC}[name]
         p = ctypes.c_void_p()
         check(self.lib.chub_tensor(self.h, which, ctypes.byref(p)))
         ctypes.pythonapi.PyCapsule_New.restype = ctypes.py_object

@@ -156,6 +156,10 @@ class EvcsspManagerEnv_v6(_EnvBase):
         self.acumulate_reward += reward
         store_soc = float(e.get("diag_store_soc")[0])
         self.deviation = abs(store_soc - self.hy_init_soc)
+        if bool(done[0]):  # evcssp_manager.py:275-290: computed and kept, the reward deduction itself is commented out
+            cap_g = 0.089 * 200 * (5000.0 if self._kw["hydro_store_vlt"] is None else self._kw["hydro_store_vlt"]) * 1000
+            dev = (store_soc - self.hy_init_soc) if self.use_lagrangian else abs(store_soc - self.hy_init_soc)
+            self.test_penalty = abs(dev * cap_g / 1000 / 0.2)
         self.re_pv_power, self.re_wd_power = pv, wd
         self.real_state = self._real_state(pv, wd, price)
         self.state = np.array(obs[0, : self._n_obs], dtype=np.float64)
@@ -226,6 +230,73 @@ class BatchedHubEnv(object):
 
     def close(self):
         self.engine.close()
+
+
+class VectorHubEnv(object):
+    """gymnasium.vector.VectorEnv-shaped adapter over BatchedHubEnv (same-step autoreset): reset() -> (obs, info),
+    step(a) -> (obs, reward, terminated, truncated, info), everything CUDA tensors.
+
+    max_episode_steps: the reference registers the env under a TimeLimit of 999 steps (evcssp_env_cpp/__init__.py:3-8),
+        which never fires because an episode ends after 96; a smaller value truncates (masked reset) like TimeLimit would
+        (use traces="device" then: shared traces are addressed by the global step index and would lose their phase).
+    soc_penalty: the end-of-episode hydrogen-store penalty the reference computes but leaves commented out
+        (evcssp_manager.py:275-297): None (as shipped), "abs" (reward -= test_penalty) or "lagrangian"
+        (reward -= signed deviation * lagrangian_factor).  deviation = (SOC_end - init_soc) * capacity_kg / 0.2.
+    """
+
+    def __init__(self, n_hubs, env_kwargs=None, max_episode_steps=999, soc_penalty=None, lagrangian_factor=1.0, **kw):
+        import torch
+        if soc_penalty not in (None, "abs", "lagrangian"):
+            raise ValueError("soc_penalty must be None, 'abs' or 'lagrangian'")
+        self.env = BatchedHubEnv(n_hubs, env_kwargs=env_kwargs, auto_reset=True, **kw)
+        self.engine = self.env.engine
+        self.num_envs = n_hubs
+        self.single_observation_space, self.single_action_space = self.env.observation_space, self.env.action_space
+        self.observation_space = _box(np.tile(self.single_observation_space.low, (n_hubs, 1)),
+                                      np.tile(self.single_observation_space.high, (n_hubs, 1)), dtype=np.float32)
+        self.action_space = _box(-1.0, 1.0, shape=(n_hubs, self.env.action_dim), dtype=np.float32)
+        self.max_episode_steps = int(max_episode_steps)
+        self.soc_penalty, self.lagrangian_factor = soc_penalty, float(lagrangian_factor)
+        classes = kw.get("classes") or [dict(env_kwargs or {})]
+        dev = "cuda:%d" % self.engine.device
+        hc = kw.get("hub_class")
+        pick = torch.zeros(n_hubs, dtype=torch.long, device=dev) if hc is None else torch.as_tensor(
+            np.asarray(hc), device=dev).long()
+        vlt = [c.get("hydro_store_vlt") for c in classes]
+        # capacity_mass = 0.089 * 200 * store_v * 1000 g (hydro_sys.py:94-98), / 1000 -> kg
+        cap = torch.tensor([0.089 * 200 * (5000.0 if v is None else float(v)) for v in vlt], dtype=torch.float64, device=dev)
+        init = torch.tensor([float(c.get("init_soc", 0.5)) for c in classes], dtype=torch.float64, device=dev)
+        self._cap_kg, self._init_soc = cap[pick], init[pick]
+        self._elapsed = torch.zeros(n_hubs, dtype=torch.int32, device=dev)
+
+    def reset(self, seed=None, options=None):
+        if seed is not None:
+            self.engine.seed(int(seed))
+        self._elapsed.zero_()
+        return self.env.reset(), {}
+
+    def step(self, actions):
+        import torch
+        obs, reward, done, _ = self.env.step(actions)
+        terminated = done.bool()
+        self._elapsed += 1
+        info = {"final_soc": self.engine.tensor("final_soc"), "episode_stats": self.env.episode_stats()}
+        if self.soc_penalty is not None:
+            dev = (info["final_soc"].double() - self._init_soc) * self._cap_kg / 0.2
+            pen = dev * self.lagrangian_factor if self.soc_penalty == "lagrangian" else dev.abs()
+            pen = torch.where(terminated, pen, torch.zeros_like(pen)).float()
+            reward = reward - pen
+            info["soc_penalty"] = pen
+        if self.max_episode_steps < 96:
+            truncated = (self._elapsed >= self.max_episode_steps) & ~terminated
+            obs = self.env.reset(mask=truncated.to(torch.uint8))
+        else:
+            truncated = torch.zeros_like(terminated)
+        self._elapsed = torch.where(terminated | truncated, torch.zeros_like(self._elapsed), self._elapsed)
+        return obs, reward, terminated, truncated, info
+
+    def close(self):
+        self.env.close()
 
 
 def register():

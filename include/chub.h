@@ -91,7 +91,10 @@ enum chub_buffer_id {
     CHUB_BUF_DONE = 2,       /* uint8   [n_hubs] */
     CHUB_BUF_STATS = 3,      /* float32 [n_hubs][4]: episode return, income, grid energy drawn (kW-steps), incomplete departures */
     CHUB_BUF_LAST_STATS = 4, /* float32 [n_hubs][4]: the same, frozen at the last completed episode */
-    CHUB_BUF_ERROR = 5       /* uint32  [n_hubs] sticky error bits */
+    CHUB_BUF_ERROR = 5,      /* uint32  [n_hubs] sticky error bits */
+    CHUB_BUF_FINAL_SOC = 6   /* float32 [n_hubs] hydrogen store SOC when the last finished episode ended: what the
+                              * reference's end-of-episode SOC deviation / test_penalty is formed from
+                              * (evcssp_manager.py:275-290); an output like `done`, not part of the checkpoint */
 };
 
 /* Field ids for chub_get_field (read-back for parity tests, introspection, checkpoints).

@@ -117,3 +117,53 @@ def test_batched_env_auto_reset_and_stats(tables):
     assert int(env.engine.get("hub_t").max()) == 0  # everyone is at the start of the next day
     assert torch.isfinite(obs).all() and float(obs[:, 0].abs().max()) == 0.0  # sin(0)
     env.close()
+
+
+def test_vector_env_adapter(tables):
+    """gymnasium-VectorEnv-shaped adapter: five-tuple step, same-step autoreset, end-of-episode SOC penalty
+    (evcssp_manager.py:275-297) formed from the terminal store SOC, TimeLimit-style truncation."""
+    import torch
+    from charginghub_env_b200.env import VectorHubEnv
+    H = 64
+    kw = dict(C.DEFAULT_KW, hydro_store_vlt=10.0, init_soc=0.5)
+    plain = VectorHubEnv(H, env_kwargs=kw, seed=11)
+    pen = VectorHubEnv(H, env_kwargs=kw, seed=11, soc_penalty="abs")
+    lag = VectorHubEnv(H, env_kwargs=kw, seed=11, soc_penalty="lagrangian", lagrangian_factor=0.5)
+    o0, info = plain.reset()
+    pen.reset(); lag.reset()
+    assert info == {} and o0.shape == (H, 13) and plain.num_envs == H
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    last_soc = None
+    for t in range(96):
+        a = torch.rand((H, plain.env.action_dim), device="cuda", generator=gen) * 2 - 1
+        o1, r1, term1, trunc1, i1 = plain.step(a)
+        if t == 94:
+            last_soc = None
+        o2, r2, term2, trunc2, i2 = pen.step(a)
+        o3, r3, term3, trunc3, i3 = lag.step(a)
+        assert not trunc1.any()
+        if t < 95:
+            assert not term1.any() and torch.equal(r1, r2) and torch.equal(r1, r3)
+            last_soc = o1[:, 10].clone()
+    torch.cuda.synchronize()
+    assert term1.all() and term2.all()
+    final = i1["final_soc"]
+    # the terminal SOC is one hub step past the last observation seen before the autoreset
+    assert (final > 0).all() and (final <= 1).all() and (final - last_soc).abs().max() < 0.2
+    dev = (final.double() - 0.5) * (0.089 * 200 * 10.0) / 0.2
+    assert torch.allclose((r1 - r2).double(), dev.abs(), atol=1e-5)
+    assert torch.allclose((r1 - r3).double(), 0.5 * dev, atol=1e-5)
+    assert torch.equal(o1, o2)            # the penalty does not touch the dynamics
+    assert torch.allclose(i1["episode_stats"][:, 0], plain.env.episode_stats()[:, 0])
+    for e in (plain, pen, lag):
+        e.close()
+    # TimeLimit-style truncation
+    short = VectorHubEnv(H, env_kwargs=kw, seed=11, max_episode_steps=10, traces="device")
+    short.reset()
+    for t in range(10):
+        a = torch.rand((H, short.env.action_dim), device="cuda", generator=gen) * 2 - 1
+        o, r, term, trunc, _ = short.step(a)
+        assert bool(trunc.all()) == (t == 9) and not term.any()
+    assert abs(float(o[0, 0])) < 1e-6     # sin(2 pi 0 / 96): back at the first step of a day
+    assert int(short._elapsed.max()) == 0
+    short.close()
