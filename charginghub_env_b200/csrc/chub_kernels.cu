@@ -133,21 +133,31 @@ struct WarpScratch {
     uint32_t pw[1][32];               // [pile][lane], max(S0, S1) rows in fact: power (f32 bits, >= 0) of the car now on that
                                       // pile; sign bit = urgent
 };
+// The warp's scratch is addressed through ONE 32-bit offset into chub_smem that stays in a register: a C++ reference
+// to the struct made the compiler re-derive the shared-window address (S2R tid, S2UR cta id, LDC ws_bytes, IMAD) at
+// almost every use inside the scan loop.
+template <int Q>
+struct Scr {
+    uint32_t base;
+    __device__ __forceinline__ WarpScratch<Q> *operator->() const {
+        return reinterpret_cast<WarpScratch<Q> *>(__cvta_shared_to_generic((size_t) base));
+    }
+};
 template <int Q>
 static size_t warp_scratch_bytes(int rows) { return offsetof(WarpScratch<Q>, pw) + (size_t) rows * 128; }
 #define PWB_URGENT 0x80000000u
 
 // @region flat A shell (car_step batch)
 template <int TYPE, int CP, int SEG, int Q>
-__device__ __forceinline__ void flat_car_step(const ChubParams &P, WarpScratch<Q> &S, const float *tlut, uint4 *pile0,
+__device__ __forceinline__ void flat_car_step(const ChubParams &P, Scr<Q> S, const float *tlut, uint4 *pile0,
                                               int head, int count) {
     const int lane = threadIdx.x & 31;
     __syncwarp();
     if (lane < count) {
         const int sl = (head + lane) & (LA_RING - 1);
-        const float tt = __uint_as_float(S.la_t[SEG][sl]);
-        const uint32_t w = S.la_w[SEG][sl];
-        const uint32_t id = S.la_id[SEG][sl], owner = id & 31u, i = id >> 5;
+        const float tt = __uint_as_float(S->la_t[SEG][sl]);
+        const uint32_t w = S->la_w[SEG][sl];
+        const uint32_t id = S->la_id[SEG][sl], owner = id & 31u, i = id >> 5;
         float soc, power;
         curve_step<TYPE, CP, SEG>(tt, soc, power);            // car_step, CHS.hpp:900-905 / 1065-1070
         const float tsoc = curve_s2t<TYPE, CP>(soc);
@@ -157,13 +167,13 @@ __device__ __forceinline__ void flat_car_step(const ChubParams &P, WarpScratch<Q
         const int left = (int) PW_STAY(w) - (int) PW_ALREADY(w) - 1;
         uint4 r = make_uint4(0u, 0u, 0u, 0u);
         if (left <= 0) {                                      // remove_car, CHS.hpp:912-930
-            if (ceilf(soc) < floorf(target_of(tu))) atomicAdd(&S.inc_s[owner], 1u);
+            if (ceilf(soc) < floorf(target_of(tu))) atomicAdd(&S->inc_s[owner], 1u);
         } else {
             const uint32_t urgent = (cn > 0 && left <= cn) ? 1u : 0u;
             r = make_uint4(__float_as_uint(soc), __float_as_uint(tsoc), __float_as_uint(power),
                            ((w + (1u << 6)) & 0xfffu) | PW_CAR | PW_CHARGE | (urgent << 14) | ((uint32_t) cn << 15) |
                                (w & (0x3ffu << 20)));
-            (&S.pw[0][0])[i * 32u + owner] = __float_as_uint(power) | (urgent << 31);
+            (&S->pw[0][0])[i * 32u + owner] = __float_as_uint(power) | (urgent << 31);
         }
         pile0[i * 32u + owner] = r;
     }
@@ -176,9 +186,9 @@ __device__ __forceinline__ void flat_car_step(const ChubParams &P, WarpScratch<Q
 // variates, the curves and the pile record are computed here.  Items sit in the (idle) car_step rings:
 // la_t = start state of the mk_soc attempt, la_w = of the mk_late_time attempt, la_id = lane | pile << 5 | u << 10.
 template <int TYPE, int CP, int Q>
-__device__ __forceinline__ void flat_add_car(WarpScratch<Q> &S, const float *tlut, uint4 *pile0, float *arrive0, int total) {
+__device__ __forceinline__ void flat_add_car(Scr<Q> S, const float *tlut, uint4 *pile0, float *arrive0, int total) {
     const int lane = threadIdx.x & 31;
-    const uint32_t *const sd = &S.la_t[0][0], *const sf = &S.la_w[0][0], *const sx = &S.la_id[0][0];
+    const uint32_t *const sd = &S->la_t[0][0], *const sf = &S->la_w[0][0], *const sx = &S->la_id[0][0];
     for (int j = lane; j < total; j += 32) {
         const uint32_t x = sx[j], owner = x & 31u, i = (x >> 5) & 31u, tu = x >> 10;
         const float arrive = mk_soc_from<1>(sd[j]);
@@ -190,7 +200,7 @@ __device__ __forceinline__ void flat_add_car(WarpScratch<Q> &S, const float *tlu
         const float power = curve_t2p<TYPE, CP>(tsoc);
         int cn = needed > 0.0f ? must_needed : 0;
         if (stay > 63 || stay < 1 || cn > 31) {
-            atomicOr(&S.err_s[owner], (uint32_t) CHUB_HUBERR_COUNTER);
+            atomicOr(&S->err_s[owner], (uint32_t) CHUB_HUBERR_COUNTER);
             stay = min(max(stay, 1), 63);
             cn = min(cn, 31);
         }
@@ -199,7 +209,7 @@ __device__ __forceinline__ void flat_add_car(WarpScratch<Q> &S, const float *tlu
         pile0[at] = make_uint4(__float_as_uint(arrive), __float_as_uint(tsoc), __float_as_uint(power),
                                (uint32_t) stay | PW_CAR | (urgent << 14) | ((uint32_t) cn << 15) | (tu << 20));
         arrive0[at] = arrive;
-        (&S.pw[0][0])[at] = __float_as_uint(power) | (urgent << 31);
+        (&S->pw[0][0])[at] = __float_as_uint(power) | (urgent << 31);
     }
     __syncwarp();
 }
@@ -208,7 +218,7 @@ __device__ __forceinline__ void flat_add_car(WarpScratch<Q> &S, const float *tlu
 // position; the other lanes own no piles here but still work on the pooled items.
 // @region station prologue + receive_car draws
 template <int TYPE, int CP, int Q>
-__device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q> &S, const float *tl_s, bool mine, int h,
+__device__ __forceinline__ void station_step(const ChubParams &P, Scr<Q> S, const float *tl_s, bool mine, int h,
                                           int slot0, int n_in, int t, int line_in, uint32_t act_bits, uint32_t occ_in,
                                           HubRng &rng, uint32_t &err, StationOut &o) {
     const unsigned full = 0xffffffffu;
@@ -217,7 +227,7 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
     const int n = mine ? n_in : 0;
     // s2t(target) of the 1000 possible targets: shared-memory copy for curve charging, global (L1) for constant power
     const float *tlut = CP ? P.s2t_lut + (2 + TYPE) * 1000 : tl_s + TYPE * 1000;
-    S.inc_s[lane] = 0u; S.err_s[lane] = 0u;
+    S->inc_s[lane] = 0u; S->err_s[lane] = 0u;
 
     // ---- station-level draws of receive_car (CHS.hpp:1272-1306), before any per-car draw ----
     int want = 0, flow = 0;
@@ -253,7 +263,7 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
     uint32_t rows = __reduce_or_sync(full, occ);
     uint4 *rp = pile0 + lane;
     asm volatile("" : "+l"(rp));                     // keep the tile pointer in a register pair instead of re-deriving it
-    uint32_t *const pwp = &S.pw[0][lane];
+    uint32_t *const pwp = &S->pw[0][lane];
     int inext = __ffs(rows) - 1;
     uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
     if (rows && ((occ >> inext) & 1u)) nxt = rp[inext * 32];
@@ -290,9 +300,9 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
         if ((m0 | m1) != 0u || need == 1) {          // otherwise nobody charges on this row: nothing to queue
             if (seg >= 0) {
                 const int sl = seg * LA_RING + ((seg == 0 ? head0 + cnt0 + __popc(m0 & lt) : head1 + cnt1 + __popc(m1 & lt)) & (LA_RING - 1));
-                (&S.la_t[0][0])[sl] = __float_as_uint(tt);
-                (&S.la_w[0][0])[sl] = w;
-                (&S.la_id[0][0])[sl] = (uint32_t) lane | ((uint32_t) i << 5);
+                (&S->la_t[0][0])[sl] = __float_as_uint(tt);
+                (&S->la_w[0][0])[sl] = w;
+                (&S->la_id[0][0])[sl] = (uint32_t) lane | ((uint32_t) i << 5);
             }
             cnt0 += __popc(m0);
             cnt1 += __popc(m1);
@@ -350,9 +360,9 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
                 rng.lcg = wf.y;
                 const uint32_t i = (uint32_t) __ffs(rem) - 1u;
                 rem &= rem - 1u;
-                (&S.la_t[0][0])[slot] = wd.x;
-                (&S.la_w[0][0])[slot] = wf.x;
-                (&S.la_id[0][0])[slot] = (uint32_t) lane | (i << 5) | (tu << 10);
+                (&S->la_t[0][0])[slot] = wd.x;
+                (&S->la_w[0][0])[slot] = wf.x;
+                (&S->la_id[0][0])[slot] = (uint32_t) lane | (i << 5) | (tu << 10);
             }
             __syncwarp();
             flat_add_car<TYPE, CP, Q>(S, tlut, pile0, P.arrive + tile0, total);
@@ -378,8 +388,8 @@ __device__ __forceinline__ void station_step(const ChubParams &P, WarpScratch<Q>
         o.number = __popc(present);
         o.line = min(want - assigned, 10);
         o.flow = flow;
-        o.incomplete = incomplete + (int) S.inc_s[lane];
-        err |= S.err_s[lane];
+        o.incomplete = incomplete + (int) S->inc_s[lane];
+        err |= S->err_s[lane];
         o.occ = present;
     }
     __syncwarp();
@@ -689,7 +699,7 @@ struct StationIO {
     StationOut o;
 };
 template <int TYPE, int Q>
-__device__ __noinline__ StationIO station_step_cp(const ChubParams &P, WarpScratch<Q> &S, const float *tl_s, bool mine, int h,
+__device__ __noinline__ StationIO station_step_cp(const ChubParams &P, Scr<Q> S, const float *tl_s, bool mine, int h,
                                                   int slot0, int n, int t, int line, uint32_t act_bits, uint32_t occ_in, StationIO io) {
     station_step<TYPE, 1, Q>(P, S, tl_s, mine, h, slot0, n, t, line, act_bits, occ_in, io.rng, io.err, io.o);
     return io;
@@ -705,7 +715,9 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     float *const tl_w = reinterpret_cast<float *>(smem + CHUB_LOG_N * 16);   // then the two curve-charging s2t(target) tables
     for (int i = threadIdx.x; i < 2000; i += WARPS * 32) tl_w[i] = __ldg(&P.s2t_lut[i]);
     __syncthreads();
-    WarpScratch<Q> &S = *reinterpret_cast<WarpScratch<Q> *>(smem + CHUB_SMEM_TABLES + (threadIdx.x >> 5) * P.ws_bytes);
+    Scr<Q> S;
+    S.base = (uint32_t) __cvta_generic_to_shared(chub_smem + CHUB_SMEM_TABLES + (threadIdx.x >> 5) * P.ws_bytes);
+    asm volatile("" : "+r"(S.base));
 
     const unsigned full = 0xffffffffu;
     const int h = P.h_begin + blockIdx.x * (WARPS * 32) + threadIdx.x;
@@ -716,10 +728,10 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     unsigned long long bits;
     {
         float a_m2, a_m1;
-        load_actions(P, reinterpret_cast<float *>(&S.park[0][0][0]), (P.ws_bytes - (int) offsetof(WarpScratch<Q>, park)) / 4, h,
+        load_actions(P, reinterpret_cast<float *>(&S->park[0][0][0]), (P.ws_bytes - (int) offsetof(WarpScratch<Q>, park)) / 4, h,
                      active, n0 + n1, bits, a_m2, a_m1);
-        S.am[0][threadIdx.x & 31] = a_m2;
-        S.am[1][threadIdx.x & 31] = a_m1;
+        S->am[0][threadIdx.x & 31] = a_m2;
+        S->am[1][threadIdx.x & 31] = a_m1;
     }
 
     // During the stations only the random streams, the time slot and the two queue lengths are needed; the rest of
@@ -763,9 +775,9 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
             rng = io.rng; err = io.err; o = io.o;
         }
         // the station's outputs wait in shared memory for the hub section
-        S.park[s][0][lane_] = __float_as_uint(o.mn); S.park[s][1][lane_] = __float_as_uint(o.mx);
-        S.park[s][2][lane_] = __float_as_uint(o.now); S.park[s][3][lane_] = o.occ;
-        S.park[s][4][lane_] = (uint32_t) (o.line & 0xff) | ((uint32_t) (o.flow & 0xff) << 8) | ((uint32_t) o.incomplete << 16);
+        S->park[s][0][lane_] = __float_as_uint(o.mn); S->park[s][1][lane_] = __float_as_uint(o.mx);
+        S->park[s][2][lane_] = __float_as_uint(o.now); S->park[s][3][lane_] = o.occ;
+        S->park[s][4][lane_] = (uint32_t) (o.line & 0xff) | ((uint32_t) (o.flow & 0xff) << 8) | ((uint32_t) o.incomplete << 16);
     }
     if (P.phase_sync & 2) __syncthreads();
     if (!active) return;
@@ -775,12 +787,12 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     v.t = az & 0xff; v.qn = az >> 24; v.fline = (aw >> 16) & 0xff; v.farr = aw >> 24;
     StationOut s0, s1;
     {
-        const uint32_t p0 = S.park[0][4][lane_], p1 = S.park[1][4][lane_];
-        s0.mn = __uint_as_float(S.park[0][0][lane_]); s0.mx = __uint_as_float(S.park[0][1][lane_]);
-        s0.now = __uint_as_float(S.park[0][2][lane_]); s0.occ = S.park[0][3][lane_];
+        const uint32_t p0 = S->park[0][4][lane_], p1 = S->park[1][4][lane_];
+        s0.mn = __uint_as_float(S->park[0][0][lane_]); s0.mx = __uint_as_float(S->park[0][1][lane_]);
+        s0.now = __uint_as_float(S->park[0][2][lane_]); s0.occ = S->park[0][3][lane_];
         s0.line = p0 & 0xff; s0.flow = (int) (signed char) ((p0 >> 8) & 0xff); s0.incomplete = p0 >> 16; s0.number = __popc(s0.occ);
-        s1.mn = __uint_as_float(S.park[1][0][lane_]); s1.mx = __uint_as_float(S.park[1][1][lane_]);
-        s1.now = __uint_as_float(S.park[1][2][lane_]); s1.occ = S.park[1][3][lane_];
+        s1.mn = __uint_as_float(S->park[1][0][lane_]); s1.mx = __uint_as_float(S->park[1][1][lane_]);
+        s1.now = __uint_as_float(S->park[1][2][lane_]); s1.occ = S->park[1][3][lane_];
         s1.line = p1 & 0xff; s1.flow = (int) (signed char) ((p1 >> 8) & 0xff); s1.incomplete = p1 >> 16; s1.number = __popc(s1.occ);
     }
     v.store = P.store[h];
@@ -788,7 +800,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     double pv_t, wd_t, pr_t;
     if (P.exo_mode) exo_current(P, h, pv_t, wd_t, pr_t);
     else trace_at(P, h, k, pv_t, wd_t, pr_t);
-    const float a_m2 = S.am[0][lane_], a_m1 = S.am[1][lane_];
+    const float a_m2 = S->am[0][lane_], a_m1 = S->am[1][lane_];
     v.line0 = s0.line; v.line1 = s1.line;
     v.flow0 = s0.flow; v.flow1 = s1.flow;
     v.occ0 = s0.occ; v.occ1 = s1.occ;
