@@ -139,6 +139,7 @@ struct WarpScratch {
 template <int Q>
 struct Scr {
     uint32_t base;
+    int lane;   // threadIdx.x & 31, read from the special register once
     __device__ __forceinline__ WarpScratch<Q> *operator->() const {
         return reinterpret_cast<WarpScratch<Q> *>(__cvta_shared_to_generic((size_t) base));
     }
@@ -151,7 +152,7 @@ static size_t warp_scratch_bytes(int rows) { return offsetof(WarpScratch<Q>, pw)
 template <int TYPE, int CP, int SEG, int Q>
 __device__ __forceinline__ void flat_car_step(const ChubParams &P, Scr<Q> S, const float *tlut, uint4 *pile0,
                                               int head, int count) {
-    const int lane = threadIdx.x & 31;
+    const int lane = S.lane;
     __syncwarp();
     if (lane < count) {
         const int sl = (head + lane) & (LA_RING - 1);
@@ -187,7 +188,7 @@ __device__ __forceinline__ void flat_car_step(const ChubParams &P, Scr<Q> S, con
 // la_t = start state of the mk_soc attempt, la_w = of the mk_late_time attempt, la_id = lane | pile << 5 | u << 10.
 template <int TYPE, int CP, int Q>
 __device__ __forceinline__ void flat_add_car(Scr<Q> S, const float *tlut, uint4 *pile0, float *arrive0, int total) {
-    const int lane = threadIdx.x & 31;
+    const int lane = S.lane;
     const uint32_t *const sd = &S->la_t[0][0], *const sf = &S->la_w[0][0], *const sx = &S->la_id[0][0];
     for (int j = lane; j < total; j += 32) {
         const uint32_t x = sx[j], owner = x & 31u, i = (x >> 5) & 31u, tu = x >> 10;
@@ -222,7 +223,7 @@ __device__ __forceinline__ void station_step(const ChubParams &P, Scr<Q> S, cons
                                           int slot0, int n_in, int t, int line_in, uint32_t act_bits, uint32_t occ_in,
                                           HubRng &rng, uint32_t &err, StationOut &o) {
     const unsigned full = 0xffffffffu;
-    const int lane = threadIdx.x & 31;
+    const int lane = S.lane;
     const int h0 = h - lane;
     const int n = mine ? n_in : 0;
     // s2t(target) of the 1000 possible targets: shared-memory copy for curve charging, global (L1) for constant power
@@ -717,7 +718,8 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     __syncthreads();
     Scr<Q> S;
     S.base = (uint32_t) __cvta_generic_to_shared(chub_smem + CHUB_SMEM_TABLES + (threadIdx.x >> 5) * P.ws_bytes);
-    asm volatile("" : "+r"(S.base));
+    S.lane = threadIdx.x & 31;
+    asm volatile("" : "+r"(S.base), "+r"(S.lane));
 
     const unsigned full = 0xffffffffu;
     const int h = P.h_begin + blockIdx.x * (WARPS * 32) + threadIdx.x;
@@ -730,8 +732,8 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
         float a_m2, a_m1;
         load_actions(P, reinterpret_cast<float *>(&S->park[0][0][0]), (P.ws_bytes - (int) offsetof(WarpScratch<Q>, park)) / 4, h,
                      active, n0 + n1, bits, a_m2, a_m1);
-        S->am[0][threadIdx.x & 31] = a_m2;
-        S->am[1][threadIdx.x & 31] = a_m1;
+        S->am[0][S.lane] = a_m2;
+        S->am[1][S.lane] = a_m1;
     }
 
     // During the stations only the random streams, the time slot and the two queue lengths are needed; the rest of
@@ -755,7 +757,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     }
 
     // ---- the two EV stations, station 0 first (Aggregator_Simple.py:141-142); the whole warp takes part ----
-    const int lane_ = threadIdx.x & 31;
+    const int lane_ = S.lane;
 #pragma unroll 1
     for (int s = 0; s < 2; ++s) {
         const int type = c.type[s], n = s ? n1 : n0, slot0 = s ? P.S0 : 0, line = (az >> (8 + 8 * s)) & 0xff, t = az & 0xff;
