@@ -1,0 +1,126 @@
+"""-m gpu: parity at BASELINE's full per-GPU size (the config-5 shard, 524,288 hubs; here minus 13 so that the last
+warp is ragged).  The oracle cannot step half a million hubs in test time, so it steps windows of hubs spread over the
+whole range -- each seeded from its GLOBAL hub ids, which is all a hub's trajectory depends on -- and the engine must
+agree with it there; plus two size-independent properties: the launch shape does not change a single bit, and a
+second engine holding only the upper half of the hubs (hub_id_base) reproduces that half."""
+import os
+
+import numpy as np
+import pytest
+
+from tests import common as C
+
+pytestmark = pytest.mark.gpu
+
+H_FULL = 524288 - 13
+WINDOW = 128
+
+
+def _year(tabs, L):
+    t = np.arange(L, dtype=np.float64)
+    pv = 210.0 * np.maximum(0.0, np.sin(np.pi * ((t % 96) - 24) / 48.0))
+    wd = np.clip(46 + 40 * np.sin(2 * np.pi * t / 355.0), 0, 98)
+    price = tabs["price"][(t.astype(np.int64) - 1) % 96]
+    return pv, wd, price
+
+
+def _engine(H, tabs, seed, base=0):
+    from charginghub_env_b200 import HubEngine
+    eng = HubEngine(H, [C.DEFAULT_KW], device=0, hub_id_base=base, diagnostics=True, tables=tabs, seed=seed)
+    eng.set_traces(*_year(tabs, 98))
+    return eng
+
+
+def test_windows_of_the_full_shard_match_the_oracle(tables):
+    import torch
+    from oracle import oracle as O
+    seed = 0x5EED
+    eng = _engine(H_FULL, tables, seed)
+    pv, wd, price = _year(tables, 98)
+    bases = [0, 1000, 77777, H_FULL // 2 - 50, 300001, 444444, H_FULL - 3 * WINDOW, H_FULL - WINDOW]
+    orcs = []
+    for b in bases:
+        o = O.Oracle(WINDOW, [C.DEFAULT_KW], tables=C.oracle_tables(tables))
+        o.seed_base(seed, b)
+        o.reset(pv[0], wd[0], price[0])
+        orcs.append(o)
+    obs = eng.reset()
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    S = eng.action_stride
+
+    def compare(t, obs, rew, done, deep):
+        torch.cuda.synchronize()
+        for b, o in zip(bases, orcs):
+            sl = slice(b, b + WINDOW)
+            assert C.close(obs[sl].cpu().numpy(), o.get("obs"), atol=C.RTOL).all(), ("obs", t, b)
+            if t:
+                assert C.close(rew[sl].cpu().numpy(), o.get("reward"), atol=C.RTOL).all(), ("reward", t, b)
+                assert np.array_equal(done[sl].cpu().numpy().astype(np.int32), o.get("hub_done")), ("done", t, b)
+        if not deep:
+            return
+        for name in C.INT_FIELDS:
+            a = eng.get(name)
+            for b, o in zip(bases, orcs):
+                x, y = a[b:b + WINDOW], o.get(name)
+                if name in ("hub_uctr", "hub_lcg"):
+                    x, y = x.astype(np.uint32), y.astype(np.uint32)
+                assert np.array_equal(x, y), (name, t, b)
+        for name in C.PILE_FLOATS + ["store"]:
+            a = eng.get(name)
+            for b, o in zip(bases, orcs):
+                y = o.get(name)
+                if name == "pile_power":
+                    y = y * o.get("pile_car")
+                assert C.close(a[b:b + WINDOW], y, atol=C.RTOL).all(), (name, t, b)
+
+    compare(0, obs, None, None, True)
+    for t in range(96):
+        a = torch.rand((H_FULL, S), device="cuda", generator=gen) * 2 - 1
+        obs, rew, done = eng.step(a)
+        for b, o in zip(bases, orcs):
+            o.step(a[b:b + WINDOW].cpu().numpy(), pv[t + 1], wd[t + 1], price[t + 1])
+        if t % 8 == 7 or t == 0:
+            compare(t + 1, obs, rew, done, t in (0, 47, 95))
+    assert eng.counters()["error_or"] == 0
+
+
+def _digest(eng):
+    """Order-sensitive checksum of everything a hub's trajectory is made of (integers and float bit patterns)."""
+    import torch
+    parts = [eng.tensor("obs").view(torch.int32).long().sum(dim=1), eng.tensor("reward").view(torch.int32).long(),
+             eng.tensor("stats").view(torch.int32).long().sum(dim=1)]
+    cols, _ = eng.situation()
+    for name in ("car", "charge", "power", "soc", "target_soc", "init_soc", "emergency"):
+        parts.append(cols[name].view(torch.int32).long().sum(dim=1))
+    return torch.stack(parts, dim=1)
+
+
+def _rollout(eng, steps, seed, H, offset=0):
+    import torch
+    gen = torch.Generator(device="cuda").manual_seed(seed)
+    eng.reset()
+    for t in range(steps):
+        a = torch.rand((H, eng.action_stride), device="cuda", generator=gen) * 2 - 1
+        eng.step(a[offset:offset + eng.n_hubs].contiguous())
+    torch.cuda.synchronize()
+    return _digest(eng)
+
+
+def test_launch_shape_and_sharding_do_not_change_a_bit(tables):
+    import torch
+    seed, steps = 99, 40      # through the morning ramp into the busy hours
+    ref = _rollout(_engine(H_FULL, tables, seed), steps, 7, H_FULL)
+    old = os.environ.get("CHUB_BLOCK")
+    try:
+        for shape in ("1610", "810"):      # 16 and 8 warps per block instead of the fitted 28
+            os.environ["CHUB_BLOCK"] = shape
+            got = _rollout(_engine(H_FULL, tables, seed), steps, 7, H_FULL)
+            assert torch.equal(ref, got), shape
+    finally:
+        if old is None:
+            os.environ.pop("CHUB_BLOCK", None)
+        else:
+            os.environ["CHUB_BLOCK"] = old
+    half = H_FULL // 2 + 5                 # an unaligned split: the upper part as its own engine (another "rank")
+    upper = _rollout(_engine(H_FULL - half, tables, seed, base=half), steps, 7, H_FULL, offset=half)
+    assert torch.equal(ref[half:], upper)
