@@ -1048,15 +1048,28 @@ __device__ __forceinline__ uint32_t dispatch_station(const ChubParams &P, float 
     const uint4 *rp = P.pile + chub_pile_index(h, slot0, P.S0 + P.S1);
     const float *tlut = P.s2t_lut + (cp * 2 + type) * 1000;
     float mn = 0.0f, mx = 0.0f;
-    for (uint32_t m = occ; m; m &= m - 1u) {   // calculate_needed + calculate_output, ascending pile order
-        const int i = __ffs(m) - 1;
-        const uint4 r = rp[i * 32];
-        const float e = pile_emergency(tlut, r);
-        const float p = __uint_as_float(r.z);
-        mx += p;
-        if (e > 8.0f) mn += p;
-        es[i][lane] = e;
-        ps[i][lane] = p;
+    for (uint32_t m = occ; m;) {   // calculate_needed + calculate_output, ascending pile order, 8 records in flight
+        int idx[8];
+        uint4 r[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            idx[u] = -1;
+            if (m) {
+                idx[u] = __ffs(m) - 1;
+                m &= m - 1u;
+                r[u] = rp[idx[u] * 32];
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            if (idx[u] < 0) break;
+            const float e = pile_emergency(tlut, r[u]);
+            const float p = __uint_as_float(r[u].z);
+            mx += p;
+            if (e > 8.0f) mn += p;
+            es[idx[u]][lane] = e;
+            ps[idx[u]][lane] = p;
+        }
     }
     if (load > mx) load = mx;                  // catch_load
     else if (load < mn) load = mn;
