@@ -33,7 +33,11 @@ struct StationOut {
 };
 
 __device__ __forceinline__ float target_of(uint32_t tu) {  // uniform_rand(80, 100), CHS.hpp:41-42, 867
-    return (float) tu / 999.0f * 20.0f + 80.0f;
+    // tu / 999 correctly rounded without the generic division: reciprocal multiply + one residual correction, equal to
+    // the IEEE quotient for every tu in 0..1023 (tools/verify_divf.c checks all of them)
+    const float t = (float) tu, q0 = t * (1.0f / 999.0f);
+    const float q = fmaf(fmaf(-q0, 999.0f, t), 1.0f / 999.0f, q0);
+    return q * 20.0f + 80.0f;
 }
 
 // evs_reset of one EV station of one hub (CHS.hpp:1209-1231 / 1520-1542), one thread per hub: draw the

@@ -26,6 +26,15 @@ int main(void) {
             }
             n++;
         }
+    {   /* target_of (chub_kernels.cu): tu / 999 for the 10-bit target draw */
+        const float r9 = 1.0f / 999.0f;
+        for (int tu = 0; tu < 1024; ++tu) {
+            float t = (float) tu;
+            volatile float ref = t / 999.0f;
+            float q0 = t * r9, q = fmaf(fmaf(-q0, 999.0f, t), r9, q0), rr = ref;
+            if (memcmp(&q, &rr, 4) != 0) { printf("tu=%d ref=%a got=%a\n", tu, rr, q); bad++; }
+        }
+    }
     printf("tested %llu floats, %llu mismatches at |a| >= 2^-60, %llu below\n", (unsigned long long) n,
            (unsigned long long) bad, (unsigned long long) tiny);
     return bad != 0;
