@@ -1026,14 +1026,15 @@ static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s) {
 // rounded once, which is what the fp32 multiply gives.
 // @region load dispatch
 #define DISPATCH_WARPS 4
-__device__ __forceinline__ int dispatch_pick(const float (*es)[32], int lane, uint32_t rem) {
-    float best = -1.0f;
+__device__ __forceinline__ int dispatch_pick(float (*es)[32], int lane, int n) {
+    float best = -1.0f;   // piles without a car and cars already taken hold -1
     int bi = 0;
-    for (uint32_t m = rem; m; m &= m - 1u) {
-        const int j = __ffs(m) - 1;
+#pragma unroll 4
+    for (int j = 0; j < n; ++j) {
         const float e = es[j][lane];
         if (e > best) { best = e; bi = j; }   // strict: equal urgencies keep pile order
     }
+    es[bi][lane] = -1.0f;
     return bi;
 }
 
@@ -1048,8 +1049,9 @@ __device__ __forceinline__ float pile_emergency(const float *tlut, const uint4 r
 }
 
 __device__ __forceinline__ uint32_t dispatch_station(const ChubParams &P, float (*es)[32], float (*ps)[32], int h, int lane,
-                                                     int slot0, int type, int cp, uint32_t occ, float load) {
+                                                     int slot0, int n, int type, int cp, uint32_t occ, float load) {
     const uint4 *rp = P.pile + chub_pile_index(h, slot0, P.S0 + P.S1);
+    for (int i = 0; i < n; ++i) es[i][lane] = -1.0f;
     const float *tlut = P.s2t_lut + (cp * 2 + type) * 1000;
     float mn = 0.0f, mx = 0.0f;
     for (uint32_t m = occ; m;) {   // calculate_needed + calculate_output, ascending pile order, 8 records in flight
@@ -1077,21 +1079,17 @@ __device__ __forceinline__ uint32_t dispatch_station(const ChubParams &P, float 
     }
     if (load > mx) load = mx;                  // catch_load
     else if (load < mn) load = mn;
-    uint32_t on = 0u, rem = occ;
+    uint32_t on = 0u;
+    int cars = __popc(occ);
     if (cp) {
         const float cpw = type == CHUB_SLOW ? (float) 5.254973139368931 : (float) 36.44764034125146;
         int k = (int) roundf(load / cpw);
-        for (; rem && k > 0; --k) {
-            const int bi = dispatch_pick(es, lane, rem);
-            rem &= ~(1u << bi);
-            on |= 1u << bi;
-        }
+        for (; cars > 0 && k > 0; --k, --cars) on |= 1u << dispatch_pick(es, lane, n);
     } else {
         const double lim = (double) load + 0.0001;
         float cum = 0.0f;
-        while (rem) {
-            const int bi = dispatch_pick(es, lane, rem);
-            rem &= ~(1u << bi);
+        for (; cars > 0; --cars) {
+            const int bi = dispatch_pick(es, lane, n);
             cum += ps[bi][lane];
             if (!(lim >= (double) cum)) break;   // powers are >= 0: the running sum never comes back under the target
             on |= 1u << bi;
@@ -1108,8 +1106,8 @@ __global__ void __launch_bounds__(DISPATCH_WARPS * 32) chub_dispatch_kernel(cons
     const ChubClass &c = P.classes[P.cls ? __ldg(&P.cls[h]) : 0];
     const uint2 occ = P.occ[h];
     const float load0 = __ldg(P.actions + (size_t) h * 4), load1 = __ldg(P.actions + (size_t) h * 4 + 1);
-    const uint32_t on0 = dispatch_station(P, es[wp], ps[wp], h, lane, 0, c.type[0], c.constant, occ.x, load0);
-    const uint32_t on1 = dispatch_station(P, es[wp], ps[wp], h, lane, P.S0, c.type[1], c.constant, occ.y, load1);
+    const uint32_t on0 = dispatch_station(P, es[wp], ps[wp], h, lane, 0, c.n[0], c.type[0], c.constant, occ.x, load0);
+    const uint32_t on1 = dispatch_station(P, es[wp], ps[wp], h, lane, P.S0, c.n[1], c.type[1], c.constant, occ.y, load1);
     out[h] = (unsigned long long) on0 | ((unsigned long long) on1 << c.n[0]);
 }
 
