@@ -27,6 +27,9 @@ CASES = {
     "constant_charging": (dict(BASE, constant_charging=True), 3, 96, 13),
     "two_fast_low_store": (dict(BASE, station_list=[7, 9], station_type_list=["fast", "fast"], fcev_permeate=0.05,
                                 hydro_store_vlt=10.0, init_soc=0.1), 3, 96, 14),
+    "no_fast_station": (dict(BASE, station_list=[0, 25]), 3, 96, 16),      # 9-entry observation
+    "no_slow_station": (dict(BASE, station_list=[20, 0]), 3, 96, 17),
+    "max_piles_both": (dict(BASE, station_list=[32, 32], init_soc=0.7), 3, 96, 18),   # the widest stations the engine takes
     "two_slow_defaults_none": (dict(BASE, station_list=[12, 12], station_type_list=["slow", "slow"],
                                     hydro_prod_rate=None, hydro_store_vlt=None, fc_max_power=None, init_soc=0.5),
                                3, 96, 15),

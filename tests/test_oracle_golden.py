@@ -29,7 +29,7 @@ def load_case(path):
 
 
 def test_fixtures_present():
-    assert len(GOLD) >= 9
+    assert len(GOLD) >= 12
 
 
 def test_tables_match_reference(tables):
