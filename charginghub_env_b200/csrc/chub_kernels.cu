@@ -1105,7 +1105,12 @@ __global__ void __launch_bounds__(DISPATCH_WARPS * 32) chub_dispatch_kernel(cons
     if (h >= P.H) return;
     const ChubClass &c = P.classes[P.cls ? __ldg(&P.cls[h]) : 0];
     const uint2 occ = P.occ[h];
-    const float load0 = __ldg(P.actions + (size_t) h * 4), load1 = __ldg(P.actions + (size_t) h * 4 + 1);
+    float load0 = __ldg(P.actions + (size_t) h * 4), load1 = __ldg(P.actions + (size_t) h * 4 + 1);
+    if (load0 != load0 || load1 != load1) {   // a NaN target would slip through catch_load's comparisons
+        P.err[h] |= CHUB_HUBERR_BAD_LOAD;
+        if (load0 != load0) load0 = 0.0f;
+        if (load1 != load1) load1 = 0.0f;
+    }
     const uint32_t on0 = dispatch_station(P, es[wp], ps[wp], h, lane, 0, c.n[0], c.type[0], c.constant, occ.x, load0);
     const uint32_t on1 = dispatch_station(P, es[wp], ps[wp], h, lane, P.S0, c.n[1], c.type[1], c.constant, occ.y, load1);
     out[h] = (unsigned long long) on0 | ((unsigned long long) on1 << c.n[0]);

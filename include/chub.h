@@ -43,6 +43,7 @@ extern "C" {
 #define CHUB_HUBERR_FCEV_OVERFLOW 1u   /* FCEV list longer than CHUB_FCEV_QCAP (hydro_sys.py:266-285) */
 #define CHUB_HUBERR_STORE_ASSERT 2u    /* hydro_sys.py:111-112 assert would have fired */
 #define CHUB_HUBERR_COUNTER 4u         /* a stay/queue counter left its packed range */
+#define CHUB_HUBERR_BAD_LOAD 8u        /* chub_step_loads got a NaN power target (treated as "nothing beyond min_power") */
 
 typedef struct chub_engine chub_engine;
 

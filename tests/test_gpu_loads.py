@@ -95,3 +95,18 @@ def test_per_pile_step_after_load_step(tables):
         C.compare_state(eng, orc, t + 1, mm, C.SCALE, obs=obs.cpu().numpy(), reward=rew.cpu().numpy(),
                         done=done.cpu().numpy())
     assert not mm, str(mm)
+
+
+def test_nan_target_sets_error_bit(tables):
+    import torch
+    from charginghub_env_b200 import HubEngine
+    eng = HubEngine(64, [C.DEFAULT_KW], device=0, tables=tables, seed=1)
+    pv, wd, price = C.synth_traces(tables, 4, np.random.RandomState(0), None)
+    eng.set_traces(pv, wd, price)
+    eng.reset()
+    rows = torch.zeros((64, 4), device="cuda")
+    rows[5, 1] = float("nan")
+    eng.step_loads(rows)
+    torch.cuda.synchronize()
+    err = eng.tensor("error").cpu().numpy().reshape(-1)
+    assert err[5] == 8 and (np.delete(err, 5) == 0).all()   # CHUB_HUBERR_BAD_LOAD, sticky, only that hub
