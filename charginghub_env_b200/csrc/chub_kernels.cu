@@ -265,6 +265,7 @@ __device__ __forceinline__ void station_step(const ChubParams &P, Scr<Q> S, cons
     // Only rows on which some hub of the warp has a car are visited, and a lane only loads the piles its own
     // occupancy mask names: the traffic of a quiet hour is proportional to the cars, not to the pile count.
     const uint32_t occ = mine ? occ_in : 0u;
+    asm volatile("" : "+r"(act_bits));               // this station's action bits stay in one register through the scan
     uint32_t rows = __reduce_or_sync(full, occ);
     uint4 *rp = pile0 + lane;
     asm volatile("" : "+l"(rp));                     // keep the tile pointer in a register pair instead of re-deriving it
