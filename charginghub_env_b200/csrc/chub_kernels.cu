@@ -1022,20 +1022,25 @@ static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s) {
 // constant-power charging it switches on the first round(target / constant_power) cars instead (CHS.hpp:1338-1349).
 // Everything after that -- car_step, remove_car, receive_car -- is the per-pile path, so this kernel only turns the two
 // targets of a hub into the same on-bits that a per-pile action row would give and the step kernel runs unchanged.
-// One thread per hub; urgencies and powers of its occupied piles wait in shared memory for the selection loop.
+// One thread per hub; urgencies and powers of its occupied piles wait in shared memory (one row per thread, read four
+// at a time) for the selection loop.
 // emergency = (needed / left)^2 is pow(float, 2) in double narrowed to float (CHS.hpp:890-891): the exact product
 // rounded once, which is what the fp32 multiply gives.
 // @region load dispatch
 #define DISPATCH_WARPS 4
-__device__ __forceinline__ int dispatch_pick(float (*es)[32], int lane, int n) {
+#define DISPATCH_LD 36   // floats per lane row: a multiple of 4 (128-bit reads) that keeps the quarter-warps on distinct banks
+__device__ __forceinline__ int dispatch_pick(float *es, int n4) {
     float best = -1.0f;   // piles without a car and cars already taken hold -1
     int bi = 0;
-#pragma unroll 4
-    for (int j = 0; j < n; ++j) {
-        const float e = es[j][lane];
-        if (e > best) { best = e; bi = j; }   // strict: equal urgencies keep pile order
+    const float4 *row = reinterpret_cast<const float4 *>(es);
+    for (int j = 0; j < n4; ++j) {
+        const float4 v = row[j];
+        if (v.x > best) { best = v.x; bi = 4 * j; }   // strict: equal urgencies keep pile order
+        if (v.y > best) { best = v.y; bi = 4 * j + 1; }
+        if (v.z > best) { best = v.z; bi = 4 * j + 2; }
+        if (v.w > best) { best = v.w; bi = 4 * j + 3; }
     }
-    es[bi][lane] = -1.0f;
+    es[bi] = -1.0f;
     return bi;
 }
 
@@ -1049,10 +1054,11 @@ __device__ __forceinline__ float pile_emergency(const float *tlut, const uint4 r
     return q * q;
 }
 
-__device__ __forceinline__ uint32_t dispatch_station(const ChubParams &P, float (*es)[32], float (*ps)[32], int h, int lane,
+__device__ __forceinline__ uint32_t dispatch_station(const ChubParams &P, float *es, float *ps, int h,
                                                      int slot0, int n, int type, int cp, uint32_t occ, float load) {
     const uint4 *rp = P.pile + chub_pile_index(h, slot0, P.S0 + P.S1);
-    for (int i = 0; i < n; ++i) es[i][lane] = -1.0f;
+    const int n4 = (n + 3) >> 2;
+    for (int j = 0; j < n4; ++j) reinterpret_cast<float4 *>(es)[j] = make_float4(-1.0f, -1.0f, -1.0f, -1.0f);
     const float *tlut = P.s2t_lut + (cp * 2 + type) * 1000;
     float mn = 0.0f, mx = 0.0f;
     for (uint32_t m = occ; m;) {   // calculate_needed + calculate_output, ascending pile order, 8 records in flight
@@ -1074,8 +1080,8 @@ __device__ __forceinline__ uint32_t dispatch_station(const ChubParams &P, float 
             const float p = __uint_as_float(r[u].z);
             mx += p;
             if (e > 8.0f) mn += p;
-            es[idx[u]][lane] = e;
-            ps[idx[u]][lane] = p;
+            es[idx[u]] = e;
+            ps[idx[u]] = p;
         }
     }
     if (load > mx) load = mx;                  // catch_load
@@ -1085,13 +1091,13 @@ __device__ __forceinline__ uint32_t dispatch_station(const ChubParams &P, float 
     if (cp) {
         const float cpw = type == CHUB_SLOW ? (float) 5.254973139368931 : (float) 36.44764034125146;
         int k = (int) roundf(load / cpw);
-        for (; cars > 0 && k > 0; --k, --cars) on |= 1u << dispatch_pick(es, lane, n);
+        for (; cars > 0 && k > 0; --k, --cars) on |= 1u << dispatch_pick(es, n4);
     } else {
         const double lim = (double) load + 0.0001;
         float cum = 0.0f;
         for (; cars > 0; --cars) {
-            const int bi = dispatch_pick(es, lane, n);
-            cum += ps[bi][lane];
+            const int bi = dispatch_pick(es, n4);
+            cum += ps[bi];
             if (!(lim >= (double) cum)) break;   // powers are >= 0: the running sum never comes back under the target
             on |= 1u << bi;
         }
@@ -1101,8 +1107,8 @@ __device__ __forceinline__ uint32_t dispatch_station(const ChubParams &P, float 
 
 __global__ void __launch_bounds__(DISPATCH_WARPS * 32) chub_dispatch_kernel(const __grid_constant__ ChubParams P,
                                                                            unsigned long long *out) {
-    __shared__ float es[DISPATCH_WARPS][32][32], ps[DISPATCH_WARPS][32][32];
-    const int h = blockIdx.x * (DISPATCH_WARPS * 32) + threadIdx.x, lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+    __shared__ __align__(16) float es[DISPATCH_WARPS * 32][DISPATCH_LD], ps[DISPATCH_WARPS * 32][DISPATCH_LD];   // [thread][pile]
+    const int h = blockIdx.x * (DISPATCH_WARPS * 32) + threadIdx.x;
     if (h >= P.H) return;
     const ChubClass &c = P.classes[P.cls ? __ldg(&P.cls[h]) : 0];
     const uint2 occ = P.occ[h];
@@ -1112,8 +1118,8 @@ __global__ void __launch_bounds__(DISPATCH_WARPS * 32) chub_dispatch_kernel(cons
         if (load0 != load0) load0 = 0.0f;
         if (load1 != load1) load1 = 0.0f;
     }
-    const uint32_t on0 = dispatch_station(P, es[wp], ps[wp], h, lane, 0, c.n[0], c.type[0], c.constant, occ.x, load0);
-    const uint32_t on1 = dispatch_station(P, es[wp], ps[wp], h, lane, P.S0, c.n[1], c.type[1], c.constant, occ.y, load1);
+    const uint32_t on0 = dispatch_station(P, es[threadIdx.x], ps[threadIdx.x], h, 0, c.n[0], c.type[0], c.constant, occ.x, load0);
+    const uint32_t on1 = dispatch_station(P, es[threadIdx.x], ps[threadIdx.x], h, P.S0, c.n[1], c.type[1], c.constant, occ.y, load1);
     out[h] = (unsigned long long) on0 | ((unsigned long long) on1 << c.n[0]);
 }
 

@@ -12,6 +12,7 @@ ap.add_argument("--hubs", type=int, default=524288)
 ap.add_argument("--warm", type=int, default=40)
 ap.add_argument("--steps", type=int, default=3)
 ap.add_argument("--workload", default="config5")
+ap.add_argument("--control", default="piles", choices=["piles", "loads"])
 a = ap.parse_args()
 tabs = load_tables()
 wl = bench.workload(a.workload, tabs)
@@ -21,7 +22,10 @@ eng = HubEngine(H, wl["classes"], hub_class=hc, action_stride=wl["stride"], auto
 eng.set_traces(*bench.year_traces(tabs, 35041))
 acts = torch.rand((H, wl["stride"]), device="cuda") * 2 - 1
 eng.reset()
+if a.control == "loads":   # one power target per station: [load0 kW, load1 kW, a[-2], a[-1]]
+    caps = torch.tensor([[40.0 * n for n in wl["classes"][0]["station_list"]]], device="cuda")
+    acts = torch.cat([torch.rand((H, 2), device="cuda") ** 2 * caps, torch.rand((H, 2), device="cuda") * 2 - 1], dim=1).contiguous()
 for _ in range(a.warm + a.steps):
-    eng.step(acts)
+    (eng.step_loads if a.control == "loads" else eng.step)(acts)
 torch.cuda.synchronize()
 print("ok", eng.counters())
