@@ -82,6 +82,10 @@ SYMBOLS = {
     "chub_situation": (ctypes.c_int, [_vp, _vp, _vp]),
     "chub_step_host": (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "chub_reset_host": (ctypes.c_int, [_vp, _vp, _vp]),
+    "chub_step_packed": (ctypes.c_int, [_vp, _vp, _vp]),
+    "chub_set_host_threads": (ctypes.c_int, [_vp, _i32, _i32]),
+    "chub_pack_actions": (ctypes.c_int, [_vp, _vp, _vp]),
+    "chub_pack_rows": (None, [_vp, _i32, _vp, _i32, _i64, _vp]),
     "chub_rollout_capture": (ctypes.c_int, [_vp, _vp, _i32, _vp]),
     "chub_rollout": (ctypes.c_int, [_vp, _vp]),
     "chub_buffer": (ctypes.c_int, [_vp, _i32, ctypes.POINTER(_vp), ctypes.POINTER(_i64)]),

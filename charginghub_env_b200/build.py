@@ -4,8 +4,8 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["chub_kernels.cu", "chub_engine.cu"]
-HEADERS = ["chub_kernels.cuh", "chub_device.cuh", os.path.join("..", "..", "include", "chub.h"),
+SOURCES = ["chub_kernels.cu", "chub_engine.cu", "chub_hostpack.cpp"]
+HEADERS = ["chub_kernels.cuh", "chub_device.cuh", "chub_hostpack.h", "chub_fastmath.h", os.path.join("..", "..", "include", "chub.h"),
            os.path.join("..", "..", "include", "chub_rng.h")]
 OUT = os.path.join(CSRC, "libchub.so")
 # -fmad=false: the kernels reproduce the reference's separately rounded multiply/add; fused ops are

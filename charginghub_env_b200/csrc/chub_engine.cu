@@ -10,8 +10,10 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
+#include "chub_hostpack.h"
 #include "chub_kernels.cuh"
 
 static thread_local std::string g_err;
@@ -43,7 +45,13 @@ struct chub_engine {
     float *obs = nullptr, *reward = nullptr; uint8_t *done = nullptr; double *diag = nullptr; float *st_power = nullptr;
     long long *step_index = nullptr;
     int num_sms = 0;
-    float *actions_stage = nullptr;  // device copy target of chub_step_host
+    float *actions_stage = nullptr;  // device copy target of chub_step_host when the rows travel unpacked (host_threads == 0)
+    uint4 *packed_stage = nullptr;   // device copy target of chub_step_host: one packed record per hub
+    uint4 *packed_host = nullptr;    // pinned: where the pool packs the caller's rows
+    ChubPackPool *pool = nullptr;
+    int host_threads = -1;           // -1: not chosen yet (CHUB_HOST_THREADS or the machine's core count); 0: unpacked rows
+    int host_ranges = 8;             // hub ranges of the chub_step_host pipeline
+    std::vector<int32_t> na_row;     // per-hub number of pile actions (only with more than one class)
     int exo_mode = 0, n_pv_days = 0, n_wd_days = 0;
     double exo_renew_gain = 1.0, exo_price_gain = 1.0;
     double *exo_d = nullptr, *pv_days = nullptr, *wd_days = nullptr;
@@ -51,7 +59,7 @@ struct chub_engine {
     float *final_soc = nullptr;
     unsigned long long *act_bits = nullptr;  // pile on-bits of the scalar-load step (chub_step_loads)
     cudaStream_t host_streams[3] = {nullptr, nullptr, nullptr};  // chub_step_host pipeline: copy in, step, copy out
-    cudaEvent_t host_events[2 * 16 + 2] = {};
+    cudaEvent_t host_events[2 * CHUB_PACK_MAX_RANGES + 2] = {};
     int trace_len = 0, trace_per_hub = 0;
     bool have_tables = false, have_classes = false, have_traces = false, have_seed = false;
     long long launches = 0;
@@ -65,6 +73,8 @@ extern "C" int chub_version(void) { return 100; }
 
 static void engine_free(chub_engine *e) {
     cudaSetDevice(e->cfg.device);
+    if (e->pool) chub_pack_pool_destroy(e->pool);
+    if (e->packed_host) cudaFreeHost(e->packed_host);
     if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
     if (e->graph) cudaGraphDestroy(e->graph);
     for (cudaStream_t st : e->host_streams)
@@ -73,7 +83,7 @@ static void engine_free(chub_engine *e) {
         if (ev) cudaEventDestroy(ev);
     void *ptrs[] = {e->pile, e->arrive, e->hubA, e->store, e->keys, e->occ, e->cls, e->stats, e->last_stats, e->err, e->qsoc,
                     e->d_classes, e->d_el, e->lut, e->s2t_lut, e->pv, e->wd, e->price_tr, e->obs, e->reward, e->done, e->diag,
-                    e->st_power, e->step_index, e->actions_stage, e->exo_d, e->exo_i, e->pv_days, e->wd_days, e->act_bits, e->final_soc};
+                    e->st_power, e->step_index, e->actions_stage, e->exo_d, e->exo_i, e->pv_days, e->wd_days, e->act_bits, e->final_soc, e->packed_stage};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     delete e;
@@ -112,7 +122,7 @@ extern "C" int chub_create(const chub_config *cfg, chub_engine **out) {
     A(dalloc(&e->stats, Hp)); A(dalloc(&e->last_stats, Hp)); A(dalloc(&e->err, Hp)); A(dalloc(&e->final_soc, Hp));
     A(dalloc(&e->qsoc, Hp * CHUB_FCEV_QCAP)); A(dalloc(&e->lut, (size_t) 96 * 1000)); A(dalloc(&e->s2t_lut, (size_t) 4000));
     A(dalloc(&e->obs, Hp * CHUB_OBS_DIM)); A(dalloc(&e->reward, Hp)); A(dalloc(&e->done, Hp));
-    A(dalloc(&e->step_index, 1)); A(dalloc(&e->actions_stage, Hp * (size_t) cfg->action_stride));
+    A(dalloc(&e->step_index, 1));
     if (cfg->diagnostics) { A(dalloc(&e->diag, Hp * CHUB_D_COUNT)); A(dalloc(&e->st_power, Hp * 6)); }
     if (r != cudaSuccess) {
         engine_free(e);
@@ -243,6 +253,11 @@ extern "C" int chub_set_hub_classes(chub_engine *e, const chub_hub_class *classe
         e->hub_class.assign(hub_class, hub_class + e->H);
         CK(dalloc(&e->cls, (size_t) e->Hpad));
         CK(cudaMemcpy(e->cls, hub_class, sizeof(int32_t) * e->H, cudaMemcpyHostToDevice));
+    }
+    e->na_row.clear();
+    if (n_classes > 1) {
+        e->na_row.resize(e->H);
+        for (int h = 0; h < e->H; ++h) e->na_row[h] = classes[hub_class[h]].n_piles[0] + classes[hub_class[h]].n_piles[1];
     }
     e->cfg.n_classes = n_classes;
     e->have_classes = true;
@@ -545,10 +560,69 @@ extern "C" int chub_situation(chub_engine *e, float *out_dev, void *stream) {
     return CHUB_OK;
 }
 
-// Host-buffer step.  The batch is cut into hub ranges that flow through three streams -- actions host->device,
-// step kernel, obs/reward/done device->host -- so the two PCIe directions and the kernel overlap; hubs are
-// independent, so stepping them range by range is the same computation as one launch.
-#define CHUB_HOST_CHUNKS 8
+// Packed-action step: one 16-byte record per hub instead of a float row -- what a policy that already emits
+// switch decisions (or the host pipeline below) hands over.
+extern "C" int chub_step_packed(chub_engine *e, const void *packed_dev, void *stream) {
+    if (!e || !packed_dev) return fail(CHUB_ERR_ARG, "chub_step_packed: null argument");
+    if (reinterpret_cast<uintptr_t>(packed_dev) & 15u) return fail(CHUB_ERR_ARG, "chub_step_packed: records must be 16-byte aligned");
+    CK(cudaSetDevice(e->cfg.device));
+    ChubParams P;
+    int rc = fill_params(e, P);
+    if (rc) return rc;
+    P.act_packed = (const uint4 *) packed_dev;
+    cudaStream_t s = (cudaStream_t) stream;
+    CK(chub_launch_step(P, s));
+    chub_launch_tick(e->step_index, 1, s);
+    CK(cudaGetLastError());
+    e->launches += 1;
+    return CHUB_OK;
+}
+
+// Threads that pack the caller's rows inside chub_step_host; 0 sends the float rows over the bus as they are.
+extern "C" int chub_set_host_threads(chub_engine *e, int32_t n_threads, int32_t n_ranges) {
+    if (!e || n_threads < 0 || n_threads > 64) return fail(CHUB_ERR_ARG, "chub_set_host_threads: threads must be in [0, 64]");
+    if (n_ranges < 0 || n_ranges > CHUB_PACK_MAX_RANGES) return fail(CHUB_ERR_ARG, "chub_set_host_threads: too many ranges");
+    if (e->pool && chub_pack_pool_threads(e->pool) != n_threads) { chub_pack_pool_destroy(e->pool); e->pool = nullptr; }
+    e->host_threads = n_threads;
+    if (n_ranges) e->host_ranges = n_ranges;
+    return CHUB_OK;
+}
+
+static int host_pipeline_setup(chub_engine *e) {
+    if (e->host_threads < 0) {
+        const char *t = getenv("CHUB_HOST_THREADS"), *r = getenv("CHUB_HOST_RANGES");
+        int hw = (int) std::thread::hardware_concurrency();
+        e->host_threads = t ? atoi(t) : std::max(1, std::min(hw - 1, 16));
+        if (e->host_threads < 0 || e->host_threads > 64) e->host_threads = 1;
+        if (r && atoi(r) >= 1 && atoi(r) <= CHUB_PACK_MAX_RANGES) e->host_ranges = atoi(r);
+    }
+    if (!e->host_streams[0]) {
+        for (int i = 0; i < 3; ++i) CK(cudaStreamCreateWithFlags(&e->host_streams[i], cudaStreamNonBlocking));
+        for (int i = 0; i < 2 * CHUB_PACK_MAX_RANGES + 2; ++i) CK(cudaEventCreateWithFlags(&e->host_events[i], cudaEventDisableTiming));
+    }
+    if (e->host_threads == 0) {
+        if (!e->actions_stage) CK(dalloc(&e->actions_stage, (size_t) e->Hpad * (size_t) e->cfg.action_stride));
+        return CHUB_OK;
+    }
+    if (!e->pool) e->pool = chub_pack_pool_create(e->host_threads);
+    if (!e->packed_stage) CK(dalloc(&e->packed_stage, (size_t) e->Hpad));
+    if (!e->packed_host) CK(cudaHostAlloc((void **) &e->packed_host, sizeof(uint4) * (size_t) e->Hpad, cudaHostAllocDefault));
+    return CHUB_OK;
+}
+
+// The packing alone (host rows -> host records), for callers that want to overlap it themselves and for the tests.
+extern "C" int chub_pack_actions(chub_engine *e, const float *actions_host, void *packed_host) {
+    if (!e || !actions_host || !packed_host || !e->have_classes) return fail(CHUB_ERR_ARG, "chub_pack_actions: bad argument");
+    const ChubClass &c0 = e->classes[0];
+    chub_pack_rows(actions_host, e->cfg.action_stride, e->na_row.empty() ? nullptr : e->na_row.data(), c0.n[0] + c0.n[1], e->H,
+                   packed_host);
+    return CHUB_OK;
+}
+
+// Host-buffer step.  The batch is cut into hub ranges that flow through a pipeline -- rows thresholded into packed
+// records by the pool's threads (chub_hostpack.cpp), records host->device, step kernel, obs/reward/done device->host --
+// so the host's memory reads, both PCIe directions and the kernel overlap; hubs are independent, so stepping them
+// range by range is the same computation as one launch.
 extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *obs_host, float *reward_host,
                               uint8_t *done_host, void *stream) {
     if (!e || !actions_host) return fail(CHUB_ERR_ARG, "chub_step_host: null argument");
@@ -557,25 +631,37 @@ extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *
     ChubParams P;
     int rc = fill_params(e, P);
     if (rc) return rc;
-    P.actions = e->actions_stage;
-    if (!e->host_streams[0]) {
-        for (int i = 0; i < 3; ++i) CK(cudaStreamCreateWithFlags(&e->host_streams[i], cudaStreamNonBlocking));
-        for (int i = 0; i < 2 * CHUB_HOST_CHUNKS + 2; ++i) CK(cudaEventCreateWithFlags(&e->host_events[i], cudaEventDisableTiming));
-    }
+    rc = host_pipeline_setup(e);
+    if (rc) return rc;
+    const bool packed = e->host_threads > 0;
+    if (packed) P.act_packed = e->packed_stage;
+    else P.actions = e->actions_stage;
+    const int R = e->host_ranges;
     cudaStream_t s_in = e->host_streams[0], s_k = e->host_streams[1], s_out = e->host_streams[2];
-    cudaEvent_t *ev_in = e->host_events, *ev_k = e->host_events + CHUB_HOST_CHUNKS;
-    cudaEvent_t ev_fork = e->host_events[2 * CHUB_HOST_CHUNKS], ev_join = e->host_events[2 * CHUB_HOST_CHUNKS + 1];
-    CK(cudaEventRecord(ev_fork, s));           // everything queued on the caller's stream comes first
+    cudaEvent_t *ev_in = e->host_events, *ev_k = e->host_events + CHUB_PACK_MAX_RANGES;
+    cudaEvent_t ev_fork = e->host_events[2 * CHUB_PACK_MAX_RANGES], ev_join = e->host_events[2 * CHUB_PACK_MAX_RANGES + 1];
+    const int A = e->cfg.action_stride;
+    int per = (e->H + R - 1) / R;
+    per = (per + 1023) / 1024 * 1024;           // whole warps (and whole blocks of any launch shape)
+    if (packed) {                               // the workers start on range 0 while the streams are being forked
+        const ChubClass &c0 = e->classes[0];
+        if (chub_pack_pool_start(e->pool, actions_host, A, e->na_row.empty() ? nullptr : e->na_row.data(), c0.n[0] + c0.n[1],
+                                 e->H, per, e->packed_host) < 0)
+            return fail(CHUB_ERR_STATE, "chub_step_host: range count out of bounds");
+    }
+    CK(cudaEventRecord(ev_fork, s));            // everything queued on the caller's stream comes first
     CK(cudaStreamWaitEvent(s_in, ev_fork, 0));
     CK(cudaStreamWaitEvent(s_k, ev_fork, 0));
     CK(cudaStreamWaitEvent(s_out, ev_fork, 0));
-    const int A = e->cfg.action_stride;
-    int per = (e->H + CHUB_HOST_CHUNKS - 1) / CHUB_HOST_CHUNKS;
-    per = (per + 1023) / 1024 * 1024;           // whole warps (and whole blocks of any launch shape)
     for (int c = 0, b = 0; b < e->H; ++c, b += per) {
         const int n = (b + per <= e->H ? per : e->H - b);
-        CK(cudaMemcpyAsync(e->actions_stage + (size_t) b * A, actions_host + (size_t) b * A, sizeof(float) * (size_t) n * A,
-                           cudaMemcpyHostToDevice, s_in));
+        if (packed) {
+            chub_pack_pool_wait(e->pool, c);
+            CK(cudaMemcpyAsync(e->packed_stage + b, e->packed_host + b, sizeof(uint4) * (size_t) n, cudaMemcpyHostToDevice, s_in));
+        } else {
+            CK(cudaMemcpyAsync(e->actions_stage + (size_t) b * A, actions_host + (size_t) b * A, sizeof(float) * (size_t) n * A,
+                               cudaMemcpyHostToDevice, s_in));
+        }
         CK(cudaEventRecord(ev_in[c], s_in));
         CK(cudaStreamWaitEvent(s_k, ev_in[c], 0));
         P.h_begin = b; P.h_end = b + n;

@@ -668,6 +668,16 @@ __device__ __forceinline__ void load_actions(const ChubParams &P, float *stage, 
     const int h0 = h - lane;
     const int stride = P.action_stride;
     bits = 0ull; a_m2 = 0.0f; a_m1 = 0.0f;
+    if (P.act_packed) {   // packed-action mode: the rows were thresholded by the producer, one 16-byte record per hub
+        if (active) {
+            const uint4 r = __ldcs(P.act_packed + h);
+            bits = (unsigned long long) r.x | ((unsigned long long) r.y << 32);
+            if (na < 64) bits &= (1ull << na) - 1ull;
+            a_m2 = __uint_as_float(r.z);
+            a_m1 = __uint_as_float(r.w);
+        }
+        return;
+    }
     if (P.act_bits) {   // scalar-load mode: chub_dispatch_kernel already turned the two power targets into pile bits
         if (active) {
             bits = P.act_bits[h];

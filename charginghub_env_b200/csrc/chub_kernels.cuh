@@ -65,6 +65,7 @@ struct ChubParams {
     const float *actions;
     float *final_soc;                    // store SOC at the end of the last finished episode (evcssp_manager.py:275-290)
     const unsigned long long *act_bits;  // scalar-load mode: pile on-bits from chub_dispatch_kernel; actions = [H][4] rows
+    const uint4 *act_packed;             // packed-action mode: [H] records {on-bits lo, hi, a[-2], a[-1]} (chub_step_packed)
     float *obs;
     float *reward;
     uint8_t *done;

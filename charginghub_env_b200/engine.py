@@ -198,6 +198,14 @@ class HubEngine(object):
         check(self.lib.chub_step(self.h, _tensor_ptr(actions), self._stream(stream)))
         return self.tensor("obs"), self.tensor("reward"), self.tensor("done")
 
+    def step_packed(self, packed, stream=None):
+        """step(action) on packed records: CUDA int32/uint8 tensor of 16 bytes per hub, {on-bits lo, on-bits hi, a[-2],
+        a[-1]} (include/chub.h chub_step_packed; pack_actions builds them from float rows on the host)."""
+        if packed.numel() * packed.element_size() != 16 * self.n_hubs:
+            raise ValueError("packed must hold 16 bytes per hub")
+        check(self.lib.chub_step_packed(self.h, _tensor_ptr(packed), self._stream(stream)))
+        return self.tensor("obs"), self.tensor("reward"), self.tensor("done")
+
     def step_loads(self, loads, stream=None):
         """The stations' scalar-load step, evs_step(float) (CHS.hpp:1169-1186, 1478-1495).  loads: CUDA float32
         [n_hubs, 4], row = [power target of station 0 in kW, of station 1, a[-2], a[-1]]."""
@@ -269,6 +277,20 @@ class HubEngine(object):
         check(self.lib.chub_step_host(self.h, _dptr(hb["actions"]), _dptr(hb["obs"]), _dptr(hb["reward"]),
                                       _dptr(hb["done"]), ctypes.c_void_p(int(stream))))
         return hb["obs"], hb["reward"], hb["done"]
+
+    def set_host_threads(self, n_threads, n_ranges=0):
+        """Threads that threshold the action rows inside step_host (0: float rows cross PCIe unpacked) and the number of
+        hub ranges of its pipeline (0: keep)."""
+        check(self.lib.chub_set_host_threads(self.h, int(n_threads), int(n_ranges)))
+
+    def pack_actions(self, actions):
+        """Host float rows [n_hubs, action_stride] -> uint32 [n_hubs, 4] records of step_packed."""
+        a = np.ascontiguousarray(actions, np.float32)
+        if a.shape != (self.n_hubs, self.action_stride):
+            raise ValueError("actions must be [%d, %d]" % (self.n_hubs, self.action_stride))
+        out = np.empty((self.n_hubs, 4), np.uint32)
+        check(self.lib.chub_pack_actions(self.h, _dptr(a), _dptr(out)))
+        return out
 
     def reset_host(self, stream=0):
         hb = self.host_buffers()

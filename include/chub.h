@@ -175,11 +175,28 @@ int chub_step(chub_engine *e, const float *actions_dev, void *stream);
  * electrolyser / fuel-cell actions in [-1,1] as in chub_step.  Targets must be finite. */
 int chub_step_loads(chub_engine *e, const float *loads_dev, void *stream);
 
-/* The same through HOST buffers (what a CPU caller of the reference has): copies the actions in,
- * steps, copies obs/reward/done out, and synchronises the stream.  Any out pointer may be NULL. */
+/* step(action) on packed actions: packed_dev = [n_hubs] 16-byte records {uint32 on-bits of piles 0..31, uint32 on-bits of
+ * piles 32..63, float a[-2], float a[-1]}, pile j = entry j of the chub_step row (station 0's piles first); bit j is
+ * what action_to_real (evcssp_manager.py:384-404) makes of row entry j: 1 iff a[j] >= -2^-25.  For producers that
+ * already hold switch decisions, and the device side of chub_step_host.  Must be 16-byte aligned. */
+int chub_step_packed(chub_engine *e, const void *packed_dev, void *stream);
+
+/* The same through HOST buffers (what a CPU caller of the reference has): takes the float action rows of chub_step from
+ * host memory, steps, copies obs/reward/done out, and synchronises the stream.  Any out pointer may be NULL.
+ * PCIe bounds this call, so the rows are thresholded into chub_step_packed records by a pool of host threads and only
+ * those cross the bus (16 instead of 4*action_stride bytes per hub); ranges of hubs flow through pack -> copy in ->
+ * kernel -> copy out concurrently.  chub_set_host_threads chooses the pool size (0 = send the float rows unpacked;
+ * default: CHUB_HOST_THREADS or min(cores - 1, 16)) and the number of ranges (0 = keep; default 8, at most 32).
+ * One process per GPU on a shared host should divide the cores between the ranks.
+ * chub_pack_actions is the packing alone: [n_hubs][action_stride] host rows -> [n_hubs] host records. */
 int chub_step_host(chub_engine *e, const float *actions_host, float *obs_host, float *reward_host,
                    uint8_t *done_host, void *stream);
 int chub_reset_host(chub_engine *e, float *obs_host, void *stream);
+int chub_set_host_threads(chub_engine *e, int32_t n_threads, int32_t n_ranges);
+int chub_pack_actions(chub_engine *e, const float *actions_host, void *packed_host);
+/* The thresholding itself, engine-free (csrc/chub_hostpack.cpp): rows float32 [n_rows][stride]; na_row = per-row number
+ * of pile actions or NULL for na_all everywhere; out = [n_rows] records. */
+void chub_pack_rows(const float *rows, int32_t stride, const int32_t *na_row, int32_t na_all, int64_t n_rows, void *out);
 
 /* n_steps step launches captured once into a CUDA graph and replayed; the action buffer is re-read
  * at every step, so a policy writing into it on the same stream may be captured by the caller

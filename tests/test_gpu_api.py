@@ -165,3 +165,59 @@ def test_situation_matrices_match_the_oracle(tables):
             assert np.array_equal(got[:, s0:], want[:, 1, :s1]), (name, t, 1)
         assert not cols["assign"].any()
         assert car.sum() > H
+
+
+def _hetero_engines(tables, n_eng, H=3000, seed=11, **kw):
+    from charginghub_env_b200 import HubEngine
+    from tests.test_gpu_parity import _hetero_classes
+    rs = np.random.RandomState(seed)
+    classes = _hetero_classes(rs, 12)
+    hub_class = rs.randint(0, len(classes), H).astype(np.int32)
+    traces = C.synth_traces(tables, 400, rs)
+    engs = []
+    for _ in range(n_eng):
+        e = HubEngine(H, classes, hub_class=hub_class, device=0, tables=tables, seed=seed, action_stride=66, auto_reset=True, **kw)
+        e.set_traces(*traces)
+        e.reset()
+        engs.append(e)
+    return engs, rs, H
+
+
+def _same_outputs(a, b):
+    import torch
+    torch.cuda.synchronize()
+    for name in ("obs", "reward", "done", "stats"):
+        assert np.array_equal(a.tensor(name).cpu().numpy(), b.tensor(name).cpu().numpy()), name
+    for name in ("pile_soc", "pile_stay", "pile_charge", "st_line", "hub_uctr", "hub_lcg", "store"):
+        assert np.array_equal(a.get(name), b.get(name)), name
+
+
+def test_packed_step_equals_row_step(tables):
+    """chub_step_packed on records packed by the host packer = chub_step on the float rows (heterogeneous pile counts,
+    actions on both sides of the action_to_real threshold)."""
+    import torch
+    (a_eng, b_eng), rs, H = _hetero_engines(tables, 2)
+    edge = np.array([0.0, -0.0, -2.0 ** -25, -2.0 ** -24, -3e-8, 1.0, -1.0], np.float32)
+    for t in range(120):
+        a = rs.uniform(-1, 1, (H, 66)).astype(np.float32)
+        idx = rs.randint(0, a.size, a.size // 10)
+        a.reshape(-1)[idx] = edge[rs.randint(0, edge.size, idx.size)]
+        a_eng.step(torch.from_numpy(a).cuda())
+        b_eng.step_packed(torch.from_numpy(b_eng.pack_actions(a).view(np.int32)).cuda())
+        if t % 24 == 23:
+            _same_outputs(a_eng, b_eng)
+    assert a_eng.counters()["step_index"] == b_eng.counters()["step_index"] == 120
+
+
+@pytest.mark.parametrize("threads,ranges", [(0, 0), (1, 1), (3, 5), (8, 32)])
+def test_host_pipeline_settings(tables, threads, ranges):
+    """chub_step_host with unpacked rows, one thread, odd range counts: the same bits as the device path."""
+    import torch
+    (a_eng, b_eng), rs, H = _hetero_engines(tables, 2, H=40000 if ranges == 32 else 3000)
+    b_eng.set_host_threads(threads, ranges)
+    for t in range(30):
+        a = rs.uniform(-1, 1, (H, 66)).astype(np.float32)
+        o, r, d = a_eng.step(torch.from_numpy(a).cuda())
+        oh, rh, dh = b_eng.step_host(a)
+        assert np.array_equal(o.cpu().numpy(), oh) and np.array_equal(r.cpu().numpy(), rh) and np.array_equal(d.cpu().numpy(), dh), t
+    _same_outputs(a_eng, b_eng)
