@@ -187,6 +187,10 @@ def main():
     ap.add_argument("--hubs", type=int, default=0, help="override hubs per GPU")
     ap.add_argument("--e2e-steps", type=int, default=24)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--host-threads", type=int, default=-1,
+                    help="threads that pack the action rows inside chub_step_host (0: float rows cross PCIe unpacked; "
+                         "default: the host's cores, less one, divided between the ranks of this box, at most 16)")
+    ap.add_argument("--host-ranges", type=int, default=16, help="hub ranges of the chub_step_host pipeline")
     ap.add_argument("--control", default="piles", choices=["piles", "loads"],
                     help="piles: per-pile action rows (the gym env's step, default); loads: one power target per station "
                          "(the stations' evs_step(float)), which adds the dispatch kernel to every step")
@@ -281,7 +285,10 @@ def main():
     hb = eng.host_buffers()
     hb["actions"][...] = (host_rows if args.control == "loads" else pool[0]).cpu().numpy()
     KE = max(2, min(args.e2e_steps, K))
-    for _ in range(2):
+    local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
+    host_threads = args.host_threads if args.host_threads >= 0 else max(1, min(16, ((os.cpu_count() or 2) - 1) // local_world))
+    eng.set_host_threads(host_threads, args.host_ranges)
+    for _ in range(3):
         eng.step_host()
     barrier()
     t0 = time.perf_counter()
@@ -295,7 +302,7 @@ def main():
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_value = H * world * KE / float(te.item())
     err = eng.counters()["error_or"]
-    per = -(-(-(-H // 8)) // 1024) * 1024  # chub_step_host cuts the batch into <= 8 hub ranges of whole blocks
+    per = -(-(-(-H // args.host_ranges)) // 1024) * 1024  # chub_step_host cuts the batch into hub ranges of whole blocks
     host_chunks = -(-H // per)
 
     if rank == 0:
@@ -315,9 +322,13 @@ def main():
                              % (H * (sum(DEFAULT_KW["station_list"]) * 16 + 80) / 1e6, npool, H * S * 4 / 1e6),
                        "timer": "CUDA events on the launch stream, max over ranks"},
             "clocks": clocks,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(H * S * 4),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(H * (16 if host_threads else S * 4)),
                     "d2h_bytes_per_step": int(H * (13 * 4 + 4 + 1)), "steps": KE,
-                    "api": "chub_step_host: pinned host actions -> device, step, obs/reward/done -> pinned host, pipelined over %d hub ranges" % host_chunks},
+                    "host_rows_bytes_per_step": int(H * S * 4), "host_threads": host_threads,
+                    "api": "chub_step_host: float action rows in pinned host memory -> %s -> device, step, obs/reward/done -> "
+                           "pinned host, pipelined over %d hub ranges"
+                           % ("thresholded into 16-byte records by %d host threads" % host_threads if host_threads
+                              else "copied as they are", host_chunks)},
             "gpu_launches": int(launches) * (3 if args.control == "loads" else 2) + KE * (host_chunks + 1),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_detail": traffic_detail, "peak_source": peak_src, "algorithmic_bytes_per_hub_step": bytes_per_hub,

@@ -28,6 +28,7 @@ static int fail(int code, const std::string &msg) {
             return fail(CHUB_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));        \
     } while (0)
 
+#define CHUB_HOST_KSTREAMS 4   // ranges are independent: their kernels may share the SMs
 struct chub_engine {
     chub_config cfg;
     int H = 0, Hpad = 0, S0 = 0, S1 = 0;
@@ -50,7 +51,7 @@ struct chub_engine {
     uint4 *packed_host = nullptr;    // pinned: where the pool packs the caller's rows
     ChubPackPool *pool = nullptr;
     int host_threads = -1;           // -1: not chosen yet (CHUB_HOST_THREADS or the machine's core count); 0: unpacked rows
-    int host_ranges = 8;             // hub ranges of the chub_step_host pipeline
+    int host_ranges = 16;            // hub ranges of the chub_step_host pipeline
     std::vector<int32_t> na_row;     // per-hub number of pile actions (only with more than one class)
     int exo_mode = 0, n_pv_days = 0, n_wd_days = 0;
     double exo_renew_gain = 1.0, exo_price_gain = 1.0;
@@ -58,7 +59,7 @@ struct chub_engine {
     uint2 *exo_i = nullptr;
     float *final_soc = nullptr;
     unsigned long long *act_bits = nullptr;  // pile on-bits of the scalar-load step (chub_step_loads)
-    cudaStream_t host_streams[3] = {nullptr, nullptr, nullptr};  // chub_step_host pipeline: copy in, step, copy out
+    cudaStream_t host_streams[2 + CHUB_HOST_KSTREAMS] = {};  // chub_step_host pipeline: copy in, copy out, step kernels (round robin)
     cudaEvent_t host_events[2 * CHUB_PACK_MAX_RANGES + 2] = {};
     int trace_len = 0, trace_per_hub = 0;
     bool have_tables = false, have_classes = false, have_traces = false, have_seed = false;
@@ -592,12 +593,12 @@ static int host_pipeline_setup(chub_engine *e) {
     if (e->host_threads < 0) {
         const char *t = getenv("CHUB_HOST_THREADS"), *r = getenv("CHUB_HOST_RANGES");
         int hw = (int) std::thread::hardware_concurrency();
-        e->host_threads = t ? atoi(t) : std::max(1, std::min(hw - 1, 16));
+        e->host_threads = t ? atoi(t) : std::max(1, std::min(std::min(hw - 1, 16), e->H / 8192));  // small batches: one helper
         if (e->host_threads < 0 || e->host_threads > 64) e->host_threads = 1;
         if (r && atoi(r) >= 1 && atoi(r) <= CHUB_PACK_MAX_RANGES) e->host_ranges = atoi(r);
     }
     if (!e->host_streams[0]) {
-        for (int i = 0; i < 3; ++i) CK(cudaStreamCreateWithFlags(&e->host_streams[i], cudaStreamNonBlocking));
+        for (int i = 0; i < 2 + CHUB_HOST_KSTREAMS; ++i) CK(cudaStreamCreateWithFlags(&e->host_streams[i], cudaStreamNonBlocking));
         for (int i = 0; i < 2 * CHUB_PACK_MAX_RANGES + 2; ++i) CK(cudaEventCreateWithFlags(&e->host_events[i], cudaEventDisableTiming));
     }
     if (e->host_threads == 0) {
@@ -637,7 +638,7 @@ extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *
     if (packed) P.act_packed = e->packed_stage;
     else P.actions = e->actions_stage;
     const int R = e->host_ranges;
-    cudaStream_t s_in = e->host_streams[0], s_k = e->host_streams[1], s_out = e->host_streams[2];
+    cudaStream_t s_in = e->host_streams[0], s_out = e->host_streams[1], *s_k = e->host_streams + 2;
     cudaEvent_t *ev_in = e->host_events, *ev_k = e->host_events + CHUB_PACK_MAX_RANGES;
     cudaEvent_t ev_fork = e->host_events[2 * CHUB_PACK_MAX_RANGES], ev_join = e->host_events[2 * CHUB_PACK_MAX_RANGES + 1];
     const int A = e->cfg.action_stride;
@@ -651,9 +652,13 @@ extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *
     }
     CK(cudaEventRecord(ev_fork, s));            // everything queued on the caller's stream comes first
     CK(cudaStreamWaitEvent(s_in, ev_fork, 0));
-    CK(cudaStreamWaitEvent(s_k, ev_fork, 0));
     CK(cudaStreamWaitEvent(s_out, ev_fork, 0));
+    for (int k = 0; k < CHUB_HOST_KSTREAMS; ++k) CK(cudaStreamWaitEvent(s_k[k], ev_fork, 0));
+    int n_ranges = 0, out_begin = 0;
+    const int out_every = std::max(1, ((e->H + per - 1) / per + 7) / 8);
     for (int c = 0, b = 0; b < e->H; ++c, b += per) {
+        cudaStream_t sk = s_k[c % CHUB_HOST_KSTREAMS];
+        n_ranges = c + 1;
         const int n = (b + per <= e->H ? per : e->H - b);
         if (packed) {
             chub_pack_pool_wait(e->pool, c);
@@ -663,23 +668,26 @@ extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *
                                cudaMemcpyHostToDevice, s_in));
         }
         CK(cudaEventRecord(ev_in[c], s_in));
-        CK(cudaStreamWaitEvent(s_k, ev_in[c], 0));
+        CK(cudaStreamWaitEvent(sk, ev_in[c], 0));
         P.h_begin = b; P.h_end = b + n;
-        CK(chub_launch_step(P, s_k));
-        CK(cudaEventRecord(ev_k[c], s_k));
+        CK(chub_launch_step(P, sk));
+        CK(cudaEventRecord(ev_k[c], sk));
         CK(cudaStreamWaitEvent(s_out, ev_k[c], 0));
-        if (obs_host) CK(cudaMemcpyAsync(obs_host + (size_t) b * CHUB_OBS_DIM, e->obs + (size_t) b * CHUB_OBS_DIM,
-                                         sizeof(float) * (size_t) n * CHUB_OBS_DIM, cudaMemcpyDeviceToHost, s_out));
-        if (reward_host) CK(cudaMemcpyAsync(reward_host + b, e->reward + b, sizeof(float) * (size_t) n, cudaMemcpyDeviceToHost, s_out));
-        if (done_host) CK(cudaMemcpyAsync(done_host + b, e->done + b, (size_t) n, cudaMemcpyDeviceToHost, s_out));
+        // results go back in at most 8 pieces: below a few MB a copy costs its set-up, not its bytes
+        if ((c + 1) % out_every != 0 && b + per < e->H) continue;
+        const int ob = out_begin, on = b + n - out_begin;
+        out_begin = b + n;
+        if (obs_host) CK(cudaMemcpyAsync(obs_host + (size_t) ob * CHUB_OBS_DIM, e->obs + (size_t) ob * CHUB_OBS_DIM,
+                                         sizeof(float) * (size_t) on * CHUB_OBS_DIM, cudaMemcpyDeviceToHost, s_out));
+        if (reward_host) CK(cudaMemcpyAsync(reward_host + ob, e->reward + ob, sizeof(float) * (size_t) on, cudaMemcpyDeviceToHost, s_out));
+        if (done_host) CK(cudaMemcpyAsync(done_host + ob, e->done + ob, (size_t) on, cudaMemcpyDeviceToHost, s_out));
     }
-    chub_launch_tick(e->step_index, 1, s_k);    // after the last range: every launch above read the same step index
-    CK(cudaGetLastError());
-    e->launches += 1;
-    CK(cudaEventRecord(ev_join, s_k));
-    CK(cudaStreamWaitEvent(s, ev_join, 0));
+    for (int c = std::max(0, n_ranges - CHUB_HOST_KSTREAMS); c < n_ranges; ++c) CK(cudaStreamWaitEvent(s, ev_k[c], 0));
     CK(cudaEventRecord(ev_join, s_out));
     CK(cudaStreamWaitEvent(s, ev_join, 0));
+    chub_launch_tick(e->step_index, 1, s);      // after the last range: every launch above read the same step index
+    CK(cudaGetLastError());
+    e->launches += 1;
     CK(cudaStreamSynchronize(s));
     return CHUB_OK;
 }

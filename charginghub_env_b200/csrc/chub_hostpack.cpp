@@ -10,6 +10,7 @@
 #include <stdint.h>
 #include <string.h>
 
+#include <algorithm>
 #include <atomic>
 #include <condition_variable>
 #include <mutex>
@@ -31,8 +32,50 @@ static void pack_rows_scalar(const float *rows, int stride, const int32_t *na_ro
 }
 
 #if defined(__x86_64__)
-__attribute__((target("avx2"))) static void pack_rows_avx2(const float *rows, int stride, const int32_t *na_row, int na_all,
-                                                           int64_t n, uint32_t *out) {
+#define CHUB_AVX2 __attribute__((target("avx2")))
+#include <stdlib.h>
+static const int g_prefetch_rows = getenv("CHUB_PACK_PREFETCH") ? atoi(getenv("CHUB_PACK_PREFETCH")) : 16;
+CHUB_AVX2 static inline uint32_t on_bits8(const float *p, __m256 thr) {   // _CMP_GE_OQ: false for NaN, like the kernel's compare
+    return (uint32_t) _mm256_movemask_ps(_mm256_cmp_ps(_mm256_loadu_ps(p), thr, _CMP_GE_OQ));
+}
+
+// Every row has the same na: NB = ceil(na / 8) blocks of eight entries, the last one placed at na - 8 (it overlaps its
+// predecessor unless na is a multiple of 8; OR-ing a bit twice changes nothing).  NB is a compile-time constant so the
+// row body is straight-line code.
+template <int NB>
+CHUB_AVX2 static void pack_rows_avx2_nb(const float *rows, int stride, int na, int64_t n, uint32_t *out) {
+    const __m256 thr = _mm256_set1_ps(-0x1p-25f);
+    const int last = na - 8;
+    const int64_t pf = (int64_t) g_prefetch_rows * stride;
+    for (int64_t r = 0; r < n; ++r) {
+        const float *row = rows + r * stride;
+        if (pf) {   // a core keeps few demand misses in flight; asking early for the lines of a later row adds to them
+            const char *q = (const char *) (row + pf);
+#pragma GCC unroll 4
+            for (int k = 0; k < NB; k += 2) _mm_prefetch(q + 32 * k, _MM_HINT_T0);
+        }
+        uint64_t bits = (uint64_t) on_bits8(row + last, thr) << last;
+#pragma GCC unroll 8
+        for (int b = 0; b < NB - 1; ++b) bits |= (uint64_t) on_bits8(row + 8 * b, thr) << (8 * b);
+        uint64_t tail;
+        memcpy(&tail, row + na, 8);
+        _mm_storeu_si128((__m128i *) (out + 4 * r), _mm_set_epi64x((long long) tail, (long long) bits));
+    }
+}
+
+CHUB_AVX2 static void pack_rows_avx2(const float *rows, int stride, const int32_t *na_row, int na_all, int64_t n, uint32_t *out) {
+    if (!na_row && na_all >= 8) {
+        switch ((na_all + 7) / 8) {
+        case 1: return pack_rows_avx2_nb<1>(rows, stride, na_all, n, out);
+        case 2: return pack_rows_avx2_nb<2>(rows, stride, na_all, n, out);
+        case 3: return pack_rows_avx2_nb<3>(rows, stride, na_all, n, out);
+        case 4: return pack_rows_avx2_nb<4>(rows, stride, na_all, n, out);
+        case 5: return pack_rows_avx2_nb<5>(rows, stride, na_all, n, out);
+        case 6: return pack_rows_avx2_nb<6>(rows, stride, na_all, n, out);
+        case 7: return pack_rows_avx2_nb<7>(rows, stride, na_all, n, out);
+        default: return pack_rows_avx2_nb<8>(rows, stride, na_all, n, out);
+        }
+    }
     const __m256 thr = _mm256_set1_ps(-0x1p-25f);
     for (int64_t r = 0; r < n; ++r) {
         const float *row = rows + r * stride;
@@ -41,12 +84,8 @@ __attribute__((target("avx2"))) static void pack_rows_avx2(const float *rows, in
             pack_row_scalar(row, na, out + 4 * r);
             continue;
         }
-        uint64_t bits = 0;
-        int j = 0;
-        for (; j + 8 <= na; j += 8)   // _CMP_GE_OQ: false for NaN, like the kernel's compare
-            bits |= (uint64_t) (uint32_t) _mm256_movemask_ps(_mm256_cmp_ps(_mm256_loadu_ps(row + j), thr, _CMP_GE_OQ)) << j;
-        if (j < na)                   // the last, overlapping block re-derives bits already set: OR is idempotent
-            bits |= (uint64_t) (uint32_t) _mm256_movemask_ps(_mm256_cmp_ps(_mm256_loadu_ps(row + na - 8), thr, _CMP_GE_OQ)) << (na - 8);
+        uint64_t bits = (uint64_t) on_bits8(row + na - 8, thr) << (na - 8);
+        for (int j = 0; j + 8 < na; j += 8) bits |= (uint64_t) on_bits8(row + j, thr) << j;
         uint32_t *o = out + 4 * r;
         o[0] = (uint32_t) bits;
         o[1] = (uint32_t) (bits >> 32);
@@ -72,11 +111,23 @@ static inline void cpu_relax() {
 #endif
 }
 
+// Work is handed out in blocks of CHUB_PACK_BLOCK rows from a per-range ticket counter, so a thread that the host
+// schedules late (or a busy core) costs one block, not its share of the range; the caller packs along while it waits.
+#define CHUB_PACK_BLOCK 256
+struct alignas(64) PackRange {
+    std::atomic<int64_t> next{0};   // next block of this range to hand out
+    char pad0[56];
+    std::atomic<int64_t> done{0};   // blocks of this range finished
+    int64_t n_blocks = 0;
+    char pad1[48];
+};
+
 struct ChubPackPool {
     std::vector<std::thread> workers;
     std::mutex mu;
     std::condition_variable cv;
     std::atomic<uint64_t> epoch{0};
+    std::atomic<int> idle{0};       // workers that are out of the current job
     bool stop = false;
     // the job (written by the caller before the epoch moves)
     const float *rows = nullptr;
@@ -85,16 +136,20 @@ struct ChubPackPool {
     int64_t n_rows = 0, per = 0;
     uint32_t *out = nullptr;
     int n_ranges = 0;
-    std::atomic<int> done[CHUB_PACK_MAX_RANGES];
-    bool busy = false;   // a job was started and not every range of it has been waited for
+    PackRange range[CHUB_PACK_MAX_RANGES];
 
-    void slice(int worker, int range) {
-        const int T = (int) workers.size();
-        const int64_t b = (int64_t) range * per, n = (b + per <= n_rows ? per : n_rows - b);
-        const int64_t lo = b + n * worker / T, hi = b + n * (worker + 1) / T;
-        if (hi > lo) chub_pack_rows(rows + lo * stride, stride, na_row ? na_row + lo : nullptr, na_all, hi - lo, out + 4 * lo);
+    void work_on(int r) {
+        PackRange &R = range[r];
+        const int64_t b = (int64_t) r * per, n = (b + per <= n_rows ? per : n_rows - b);
+        for (;;) {
+            const int64_t k = R.next.fetch_add(1, std::memory_order_relaxed);
+            if (k >= R.n_blocks) return;
+            const int64_t lo = b + k * CHUB_PACK_BLOCK, hi = std::min(b + n, lo + CHUB_PACK_BLOCK);
+            chub_pack_rows(rows + lo * stride, stride, na_row ? na_row + lo : nullptr, na_all, hi - lo, out + 4 * lo);
+            R.done.fetch_add(1, std::memory_order_release);
+        }
     }
-    void run(int worker) {
+    void run() {
         uint64_t seen = 0;
         for (;;) {
             int spins = 0;
@@ -109,10 +164,8 @@ struct ChubPackPool {
                 if (stop) return;
             }
             seen = epoch.load(std::memory_order_acquire);
-            for (int r = 0; r < n_ranges; ++r) {
-                slice(worker, r);
-                done[r].fetch_add(1, std::memory_order_release);
-            }
+            for (int r = 0; r < n_ranges; ++r) work_on(r);
+            idle.fetch_add(1, std::memory_order_release);
         }
     }
 };
@@ -121,8 +174,8 @@ extern "C" ChubPackPool *chub_pack_pool_create(int32_t n_threads) {
     if (n_threads < 1) n_threads = 1;
     if (n_threads > 64) n_threads = 64;
     ChubPackPool *p = new ChubPackPool();
-    for (auto &d : p->done) d.store(0);
-    for (int i = 0; i < n_threads; ++i) p->workers.emplace_back([p, i] { p->run(i); });
+    p->idle.store(n_threads);
+    for (int i = 0; i < n_threads; ++i) p->workers.emplace_back([p] { p->run(); });
     return p;
 }
 
@@ -138,19 +191,25 @@ extern "C" void chub_pack_pool_destroy(ChubPackPool *p) {
     delete p;
 }
 
-extern "C" void chub_pack_pool_wait(ChubPackPool *p, int32_t r);
 extern "C" int32_t chub_pack_pool_threads(const ChubPackPool *p) { return p ? (int32_t) p->workers.size() : 0; }
 
 // Start packing n_rows rows in ranges of `per` rows (at most CHUB_PACK_MAX_RANGES).  Returns the number of ranges.
 extern "C" int32_t chub_pack_pool_start(ChubPackPool *p, const float *rows, int32_t stride, const int32_t *na_row,
                                         int32_t na_all, int64_t n_rows, int64_t per, void *out) {
-    int n_ranges = (int) ((n_rows + per - 1) / per);
-    if (n_ranges > CHUB_PACK_MAX_RANGES || n_ranges < 1) return -1;
-    if (p->busy) chub_pack_pool_wait(p, p->n_ranges - 1);   // the workers must be out of the previous job
-    p->busy = true;
+    if (per < 1 || n_rows < 1) return -1;
+    const int64_t nr = (n_rows + per - 1) / per;
+    if (nr > CHUB_PACK_MAX_RANGES) return -1;
+    const int n_ranges = (int) nr, T = (int) p->workers.size();
+    while (p->idle.load(std::memory_order_acquire) < T) cpu_relax();   // every worker must be out of the previous job
+    p->idle.store(0, std::memory_order_relaxed);
     p->rows = rows; p->stride = stride; p->na_row = na_row; p->na_all = na_all;
     p->n_rows = n_rows; p->per = per; p->out = (uint32_t *) out; p->n_ranges = n_ranges;
-    for (int r = 0; r < n_ranges; ++r) p->done[r].store(0, std::memory_order_relaxed);
+    for (int r = 0; r < n_ranges; ++r) {
+        const int64_t b = (int64_t) r * per, n = (b + per <= n_rows ? per : n_rows - b);
+        p->range[r].n_blocks = (n + CHUB_PACK_BLOCK - 1) / CHUB_PACK_BLOCK;
+        p->range[r].next.store(0, std::memory_order_relaxed);
+        p->range[r].done.store(0, std::memory_order_relaxed);
+    }
     {
         std::lock_guard<std::mutex> lk(p->mu);
         p->epoch.fetch_add(1, std::memory_order_release);
@@ -159,13 +218,13 @@ extern "C" int32_t chub_pack_pool_start(ChubPackPool *p, const float *rows, int3
     return n_ranges;
 }
 
-// Block until every worker has finished range r.
+// Block until range r is packed; the caller takes blocks of it too instead of idling.
 extern "C" void chub_pack_pool_wait(ChubPackPool *p, int32_t r) {
-    const int T = (int) p->workers.size();
+    p->work_on(r);
+    PackRange &R = p->range[r];
     int spins = 0;
-    while (p->done[r].load(std::memory_order_acquire) < T) {
+    while (R.done.load(std::memory_order_acquire) < R.n_blocks) {
         if (++spins < 20000) cpu_relax();
         else std::this_thread::yield();
     }
-    if (r == p->n_ranges - 1) p->busy = false;   // ranges finish in order on every worker
 }

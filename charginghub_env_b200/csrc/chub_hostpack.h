@@ -15,6 +15,7 @@ void chub_pack_pool_destroy(ChubPackPool *p);
 int32_t chub_pack_pool_threads(const ChubPackPool *p);
 int32_t chub_pack_pool_start(ChubPackPool *p, const float *rows, int32_t stride, const int32_t *na_row, int32_t na_all,
                              int64_t n_rows, int64_t per, void *out);
+// returns when range r (and only range r) is packed; the caller takes blocks of that range while it waits
 void chub_pack_pool_wait(ChubPackPool *p, int32_t r);
 #ifdef __cplusplus
 }
