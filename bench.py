@@ -177,6 +177,89 @@ def run_reference(args, tabs, wl):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
+def run_ppo_loop(args, eng, wl, H, S, rank, world, local, barrier):
+    """BASELINE.json configs[4]: PPO-style rollout loop -- segments of 128 env steps; at every step a torch policy reads the
+    engine's obs tensor (a DLPack view, no copy) and writes the action rows, the engine steps, and obs / reward / done are
+    stored into the segment's rollout buffers.  Policy, step kernel and stores of a whole segment are ONE CUDA graph
+    (torch.cuda.graph around chub_step: the engine launches on torch's capture stream).  The policy is a stand-in (one
+    linear layer + tanh through torch); it is the trainer's code, not this repo's product."""
+    import torch
+    import torch.distributed as dist
+    T = args.segment
+    dev = torch.device("cuda", local)
+    gen = torch.Generator(device="cuda").manual_seed(4321 + rank)
+    Wp = torch.randn((13, S), device=dev, generator=gen) * 0.7
+    bp = torch.randn((S,), device=dev, generator=gen) * 0.3
+    obs, rew, done = eng.tensor("obs"), eng.tensor("reward"), eng.tensor("done")
+    act_buf = torch.empty((T, H, S), device=dev)
+    obs_buf = torch.empty((T, H, 13), device=dev)
+    rew_buf = torch.empty((T, H), device=dev)
+    done_buf = torch.empty((T, H), device=dev, dtype=torch.uint8)
+
+    def segment():
+        for t in range(T):
+            obs_buf[t].copy_(obs)                       # the observation the action is chosen on
+            torch.addmm(bp, obs, Wp, out=act_buf[t])    # policy: obs [H,13] -> action rows [H,S], written in place
+            act_buf[t].tanh_()
+            eng.step(act_buf[t])
+            rew_buf[t].copy_(rew)
+            done_buf[t].copy_(done)
+
+    eng.reset()
+    side = torch.cuda.Stream(device=dev)
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):                       # warm-up outside capture (cuBLAS workspaces, launch shapes)
+        segment()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        segment()
+    nseg_w, nseg = max(1, args.warmup // T), max(1, args.steps // T)
+    for _ in range(nseg_w):
+        g.replay()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(nseg):
+        g.replay()
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    clocks = sampler.stop() if rank == 0 else None
+    tms = torch.tensor([ms], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    ms_max = float(tms.item())
+    K = nseg * T
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        bytes_env = eng.algorithmic_bytes(0)
+        bytes_loop = bytes_env + 13 * 4 * 2 + S * 4 + 13 * 4 + 2 * (4 + 1)   # + obs store, policy read obs / write rows, reward / done stores
+        print(json.dumps({
+            "metric": METRIC, "value": H * world * K / (ms_max * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
+            "warmup": nseg_w * T, "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32 state / f64 arithmetic", "data": "synthetic",
+            "config": {"workload": wl["desc"] + "; PPO-style rollout loop: %d-step segments, torch policy (linear + tanh) on "
+                                                "DLPack views, rollout buffers written every step, one CUDA graph per segment" % T,
+                       "hubs_per_gpu": H, "hubs_total": H * world, "action_stride": S, "segment": T,
+                       "l2": "state + per-step slices of the rollout buffers exceed L2",
+                       "timer": "CUDA events around the graph replays, max over ranks"},
+            "clocks": clocks, "e2e": None,
+            "gpu_launches": K * 2,  # graph nodes of ours replayed in the timed region: one step kernel + one tick per env step
+            "graph_replays": nseg, "kernels_per_replay_note": "per step: 1 step kernel + 1 tick (ours), 1 GEMM + 1 tanh + 3 copies (torch)",
+            "roofline": {"bound": "hbm", "achieved": bytes_loop * H / (ms / K * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": bytes_loop * H / (ms / K * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_hub_step": bytes_loop, "kernel": "whole loop step (policy + chub_step_kernel + stores)"},
+            "hub_error_bits": int(eng.counters()["error_or"])}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -187,6 +270,10 @@ def main():
     ap.add_argument("--hubs", type=int, default=0, help="override hubs per GPU")
     ap.add_argument("--e2e-steps", type=int, default=24)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--loop", default="step", choices=["step", "ppo"],
+                    help="step: bare env steps on pre-drawn actions (default, the headline metric); ppo: configs[4], "
+                         "128-step segments with a torch policy and rollout buffers, one CUDA graph per segment")
+    ap.add_argument("--segment", type=int, default=128)
     ap.add_argument("--host-threads", type=int, default=-1,
                     help="threads that pack the action rows inside chub_step_host (0: float rows cross PCIe unpacked; "
                          "default: the host's cores, less one, divided between the ranks of this box, at most 16)")
@@ -256,6 +343,10 @@ def main():
             gathered = [torch.empty_like(stats) for _ in range(world)] if rank == 0 else None
             dist.gather(stats, gathered, dst=0)
 
+    if args.loop == "ppo":
+        del pool
+        return run_ppo_loop(args, eng, wl, H, S, rank, world, local, barrier)
+
     for i in range(W):
         step(pool[i % npool])
     gather_stats()  # warm-up includes the collective: NCCL sets its channels up on first use
@@ -286,7 +377,9 @@ def main():
     hb["actions"][...] = (host_rows if args.control == "loads" else pool[0]).cpu().numpy()
     KE = max(2, min(args.e2e_steps, K))
     local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
-    host_threads = args.host_threads if args.host_threads >= 0 else max(1, min(16, ((os.cpu_count() or 2) - 1) // local_world))
+    host_threads = args.host_threads if args.host_threads >= 0 else min(16, ((os.cpu_count() or 2) - 1) // local_world)
+    if host_threads < 4:      # too few cores per rank to threshold 98.6 MB of rows faster than PCIe carries them
+        host_threads = 0
     eng.set_host_threads(host_threads, args.host_ranges)
     for _ in range(3):
         eng.step_host()

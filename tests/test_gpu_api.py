@@ -221,3 +221,51 @@ def test_host_pipeline_settings(tables, threads, ranges):
         oh, rh, dh = b_eng.step_host(a)
         assert np.array_equal(o.cpu().numpy(), oh) and np.array_equal(r.cpu().numpy(), rh) and np.array_equal(d.cpu().numpy(), dh), t
     _same_outputs(a_eng, b_eng)
+
+
+def test_policy_and_env_in_one_torch_graph(tables):
+    """BASELINE configs[4] in small: a torch policy on the DLPack obs view + chub_step + rollout-buffer stores, captured with
+    torch.cuda.graph (the engine launches on torch's capture stream) and replayed, equals the same loop run eagerly."""
+    import torch
+    H, S, T = 2000, 47, 16
+    a_eng, rs = _engine(H, tables, seed=9, auto_reset=True)
+    b_eng, _ = _engine(H, tables, seed=9, auto_reset=True)
+    Wp = torch.from_numpy(rs.normal(0, 0.7, (13, S)).astype(np.float32)).cuda()
+    bufs = []
+
+    def segment(eng):
+        obs, rew, done = eng.tensor("obs"), eng.tensor("reward"), eng.tensor("done")
+        act = torch.empty((T, H, S), device="cuda")
+        ob, rb, db = torch.empty((T, H, 13), device="cuda"), torch.empty((T, H), device="cuda"), torch.empty((T, H), device="cuda", dtype=torch.uint8)
+        bufs.append((act, ob, rb, db))
+
+        def run():
+            for t in range(T):
+                ob[t].copy_(obs)
+                torch.mm(obs, Wp, out=act[t])
+                act[t].tanh_()
+                eng.step(act[t])
+                rb[t].copy_(rew)
+                db[t].copy_(done)
+        return run
+
+    run_a, run_b = segment(a_eng), segment(b_eng)
+    a_eng.reset()
+    b_eng.reset()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        run_b()                       # warm-up of the captured loop's libraries; consumes one segment on b ...
+    torch.cuda.current_stream().wait_stream(side)
+    run_a()                           # ... so a runs the same segment eagerly
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        run_b()
+    for rep in range(7):              # 7 x 16 more steps: crosses the day boundary and the auto-reset
+        run_a()
+        g.replay()
+        torch.cuda.synchronize()
+        for x, y in zip(bufs[0], bufs[1]):
+            assert torch.equal(x, y), rep
+    assert a_eng.counters()["step_index"] == b_eng.counters()["step_index"] == 8 * T
+    _same_outputs(a_eng, b_eng)
