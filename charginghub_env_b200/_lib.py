@@ -14,6 +14,7 @@ OBS_DIM = 13
 EL_TABLE = 102
 FCEV_QCAP = 8
 DAY = 96
+REPORT_LEN = 29
 FAST, SLOW = 0, 1
 
 BUF_OBS, BUF_REWARD, BUF_DONE, BUF_STATS, BUF_LAST_STATS, BUF_ERROR, BUF_FINAL_SOC = range(7)
@@ -90,6 +91,7 @@ SYMBOLS = {
     "chub_rollout": (ctypes.c_int, [_vp, _vp]),
     "chub_buffer": (ctypes.c_int, [_vp, _i32, ctypes.POINTER(_vp), ctypes.POINTER(_i64)]),
     "chub_tensor": (ctypes.c_int, [_vp, _i32, ctypes.POINTER(_vp)]),
+    "chub_hub_report": (ctypes.c_int, [_vp, _i32, _vp, _vp]),
     "chub_get_field": (ctypes.c_int, [_vp, _i32, _vp]),
     "chub_state_bytes": (_i64, [_vp]),
     "chub_get_state": (ctypes.c_int, [_vp, _vp]),

@@ -28,6 +28,7 @@ static int fail(int code, const std::string &msg) {
             return fail(CHUB_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));        \
     } while (0)
 
+#define CHUB_HOST_INLINE_PACK 4096   // up to this many hubs the calling thread packs the rows itself: waking a pool costs more
 #define CHUB_HOST_KSTREAMS 4   // ranges are independent: their kernels may share the SMs
 struct chub_engine {
     chub_config cfg;
@@ -53,6 +54,7 @@ struct chub_engine {
     int host_threads = -1;           // -1: not chosen yet (CHUB_HOST_THREADS or the machine's core count); 0: unpacked rows
     int host_ranges = 16;            // hub ranges of the chub_step_host pipeline
     std::vector<int32_t> na_row;     // per-hub number of pile actions (only with more than one class)
+    double *report_dev = nullptr, *report_host = nullptr;   // chub_hub_report: device gather target, pinned landing area
     int exo_mode = 0, n_pv_days = 0, n_wd_days = 0;
     double exo_renew_gain = 1.0, exo_price_gain = 1.0;
     double *exo_d = nullptr, *pv_days = nullptr, *wd_days = nullptr;
@@ -76,6 +78,7 @@ static void engine_free(chub_engine *e) {
     cudaSetDevice(e->cfg.device);
     if (e->pool) chub_pack_pool_destroy(e->pool);
     if (e->packed_host) cudaFreeHost(e->packed_host);
+    if (e->report_host) cudaFreeHost(e->report_host);
     if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
     if (e->graph) cudaGraphDestroy(e->graph);
     for (cudaStream_t st : e->host_streams)
@@ -84,7 +87,7 @@ static void engine_free(chub_engine *e) {
         if (ev) cudaEventDestroy(ev);
     void *ptrs[] = {e->pile, e->arrive, e->hubA, e->store, e->keys, e->occ, e->cls, e->stats, e->last_stats, e->err, e->qsoc,
                     e->d_classes, e->d_el, e->lut, e->s2t_lut, e->pv, e->wd, e->price_tr, e->obs, e->reward, e->done, e->diag,
-                    e->st_power, e->step_index, e->actions_stage, e->exo_d, e->exo_i, e->pv_days, e->wd_days, e->act_bits, e->final_soc, e->packed_stage};
+                    e->st_power, e->step_index, e->actions_stage, e->exo_d, e->exo_i, e->pv_days, e->wd_days, e->act_bits, e->final_soc, e->packed_stage, e->report_dev};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     delete e;
@@ -605,7 +608,7 @@ static int host_pipeline_setup(chub_engine *e) {
         if (!e->actions_stage) CK(dalloc(&e->actions_stage, (size_t) e->Hpad * (size_t) e->cfg.action_stride));
         return CHUB_OK;
     }
-    if (!e->pool) e->pool = chub_pack_pool_create(e->host_threads);
+    if (!e->pool && e->H > CHUB_HOST_INLINE_PACK) e->pool = chub_pack_pool_create(e->host_threads);
     if (!e->packed_stage) CK(dalloc(&e->packed_stage, (size_t) e->Hpad));
     if (!e->packed_host) CK(cudaHostAlloc((void **) &e->packed_host, sizeof(uint4) * (size_t) e->Hpad, cudaHostAllocDefault));
     return CHUB_OK;
@@ -644,7 +647,12 @@ extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *
     const int A = e->cfg.action_stride;
     int per = (e->H + R - 1) / R;
     per = (per + 1023) / 1024 * 1024;           // whole warps (and whole blocks of any launch shape)
-    if (packed) {                               // the workers start on range 0 while the streams are being forked
+    const bool pooled = packed && e->pool != nullptr;
+    if (packed && !pooled) {
+        rc = chub_pack_actions(e, actions_host, e->packed_host);
+        if (rc) return rc;
+    }
+    if (pooled) {                               // the workers start on range 0 while the streams are being forked
         const ChubClass &c0 = e->classes[0];
         if (chub_pack_pool_start(e->pool, actions_host, A, e->na_row.empty() ? nullptr : e->na_row.data(), c0.n[0] + c0.n[1],
                                  e->H, per, e->packed_host) < 0)
@@ -661,7 +669,7 @@ extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *
         n_ranges = c + 1;
         const int n = (b + per <= e->H ? per : e->H - b);
         if (packed) {
-            chub_pack_pool_wait(e->pool, c);
+            if (pooled) chub_pack_pool_wait(e->pool, c);
             CK(cudaMemcpyAsync(e->packed_stage + b, e->packed_host + b, sizeof(uint4) * (size_t) n, cudaMemcpyHostToDevice, s_in));
         } else {
             CK(cudaMemcpyAsync(e->actions_stage + (size_t) b * A, actions_host + (size_t) b * A, sizeof(float) * (size_t) n * A,
@@ -823,6 +831,23 @@ extern "C" int chub_tensor(chub_engine *e, int32_t which, void **dl_managed_tens
 }
 
 // ---- read-back ----
+extern "C" int chub_hub_report(chub_engine *e, int32_t hub, double *host_out, void *stream) {
+    if (!e || !host_out || hub < 0 || hub >= e->H) return fail(CHUB_ERR_ARG, "chub_hub_report: bad argument");
+    CK(cudaSetDevice(e->cfg.device));
+    ChubParams P;
+    int rc = fill_params(e, P);
+    if (rc) return rc;
+    if (!e->report_dev) CK(dalloc(&e->report_dev, (size_t) 32));
+    if (!e->report_host) CK(cudaHostAlloc((void **) &e->report_host, sizeof(double) * 32, cudaHostAllocDefault));
+    cudaStream_t s = (cudaStream_t) stream;
+    chub_launch_report(P, hub, e->report_dev, s);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(e->report_host, e->report_dev, sizeof(double) * CHUB_REPORT_LEN, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    memcpy(host_out, e->report_host, sizeof(double) * CHUB_REPORT_LEN);
+    return CHUB_OK;
+}
+
 extern "C" int chub_get_field(chub_engine *e, int32_t field, void *host_out) {
     if (!e || !host_out || !e->have_classes) return fail(CHUB_ERR_ARG, "chub_get_field: bad argument");
     CK(cudaSetDevice(e->cfg.device));

@@ -1173,6 +1173,29 @@ void chub_launch_situation(const ChubParams &p, float *out, cudaStream_t s) {
     chub_situation_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(p, out);
 }
 
+// One hub's scalars in one place (chub_hub_report): what the single-hub gym wrapper reads back after every step
+// (evcssp_manager.py:364-372 real_state, the attributes set in step()).  out[0..13] = diagnostics columns (0 without
+// diagnostics), [14..19] = min / charge / max power of station 0 then 1, [20..21] = line, [22..23] = flow_in,
+// [24] = t, [25] = store mass (g), [26] = FCEV arrivals, [27] = FCEV backlog, [28] = sticky error bits.
+__global__ void chub_report_kernel(const __grid_constant__ ChubParams P, int h, double *out) {
+    const int k = threadIdx.x;
+    const uint4 a = P.hubA[h];
+    double v = 0.0;
+    if (k < CHUB_D_COUNT) v = P.diag ? P.diag[(size_t) k * P.Hpad + h] : 0.0;
+    else if (k < CHUB_D_COUNT + 6) v = P.st_power ? (double) P.st_power[(size_t) (k - CHUB_D_COUNT) * P.Hpad + h] : 0.0;
+    else if (k == 20) v = (double) ((a.z >> 8) & 0xff);
+    else if (k == 21) v = (double) ((a.z >> 16) & 0xff);
+    else if (k == 22) v = (double) ((int) (a.w & 0xff) - 128);
+    else if (k == 23) v = (double) ((int) ((a.w >> 8) & 0xff) - 128);
+    else if (k == 24) v = (double) (a.z & 0xff);
+    else if (k == 25) v = P.store[h];
+    else if (k == 26) v = (double) (a.w >> 24);
+    else if (k == 27) v = (double) (a.z >> 24);
+    else if (k == 28) v = (double) P.err[h];
+    if (k < CHUB_REPORT_LEN) out[k] = v;
+}
+void chub_launch_report(const ChubParams &p, int h, double *out, cudaStream_t s) { chub_report_kernel<<<1, 32, 0, s>>>(p, h, out); }
+
 cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s) {
     int shape = p.block;
     if (shape == 0) {

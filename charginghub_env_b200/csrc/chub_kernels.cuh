@@ -77,6 +77,7 @@ struct ChubParams {
 cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s);
 void chub_launch_reset(const ChubParams &p, cudaStream_t s);
 void chub_launch_situation(const ChubParams &p, float *out, cudaStream_t s);
+void chub_launch_report(const ChubParams &p, int h, double *out, cudaStream_t s);
 void chub_launch_dispatch(const ChubParams &p, unsigned long long *act_bits, cudaStream_t s);
 void chub_launch_s2t_lut(float *out, cudaStream_t s);
 void chub_launch_tick(long long *step_index, int n, cudaStream_t s);

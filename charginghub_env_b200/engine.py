@@ -298,6 +298,18 @@ class HubEngine(object):
         return hb["obs"]
 
     # ---- read-back ----
+    def hub_report(self, hub=0, stream=0):
+        """One hub's scalars in one call (include/chub.h chub_hub_report): dict of the diagnostics columns plus
+        st_min_power / st_charge_power / st_max_power / st_line / st_flow_in (pairs), t, store, fcev_arrive, fcev_qn, error."""
+        out = np.empty(_lib.REPORT_LEN, np.float64)
+        check(self.lib.chub_hub_report(self.h, int(hub), _dptr(out), ctypes.c_void_p(int(stream))))
+        rep = {name: float(out[k]) for k, name in enumerate(_lib.DIAG)}
+        rep.update(st_min_power=(float(out[14]), float(out[17])), st_charge_power=(float(out[15]), float(out[18])),
+                   st_max_power=(float(out[16]), float(out[19])), st_line=(int(out[20]), int(out[21])),
+                   st_flow_in=(int(out[22]), int(out[23])), t=int(out[24]), store=float(out[25]),
+                   fcev_arrive=int(out[26]), fcev_qn=int(out[27]), error=int(out[28]))
+        return rep
+
     def get(self, name):
         fid, dt, shp = _lib.FIELDS[name]
         out = np.empty((self.n_hubs,) + shp, dtype=dt)

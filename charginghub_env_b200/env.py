@@ -104,14 +104,13 @@ class EvcsspManagerEnv_v6(_EnvBase):
         return [seed]
 
     # the reference's state vector before normalisation (evcssp_manager.py:364-372)
-    def _real_state(self, pv, wd, price):
-        e = self.engine
-        mn, cp, mx, line = e.get("st_min_power")[0], e.get("st_charge_power")[0], e.get("st_max_power")[0], e.get("st_line")[0]
+    def _real_state(self, pv, wd, price, rep=None):
+        rep = rep or self.engine.hub_report(0)   # every scalar of the hub in one device round trip
         rs = [float(self._time), price]
         for s in range(2):
             if self.pile_number[s] > 0:
-                rs += [float(mn[s]), float(cp[s]), float(mx[s]), int(line[s])]
-        rs += [float(e.get("diag_store_soc")[0]), pv, wd]
+                rs += [rep["st_min_power"][s], rep["st_charge_power"][s], rep["st_max_power"][s], rep["st_line"][s]]
+        rs += [rep["store_soc"], pv, wd]
         return np.array(rs)
 
     def reset(self):
@@ -140,28 +139,28 @@ class EvcsspManagerEnv_v6(_EnvBase):
         obs, rew, done = self.engine.step_host(np.asarray(action, np.float32).reshape(1, -1))
         self._k += 1
         self._time = t_next
-        e = self.engine
-        reward = float(e.get("diag_reward")[0])
-        self.income = float(e.get("diag_income")[0])
-        self.fc_power = float(e.get("diag_fc_power")[0])
-        self.re_hy_for_fc = float(e.get("diag_hy_to_use")[0])
-        self.re_hydrogen_power = float(e.get("diag_h2_grid")[0])
-        self.re_hydrogen_power_init = float(e.get("diag_h2_power")[0])
-        self.re_ev_power_list = [float(e.get("diag_ev_grid0")[0]), float(e.get("diag_ev_grid1")[0])]
+        rep = self.engine.hub_report(0)
+        reward = rep["reward"]
+        self.income = rep["income"]
+        self.fc_power = rep["fc_power"]
+        self.re_hy_for_fc = rep["hy_to_use"]
+        self.re_hydrogen_power = rep["h2_grid"]
+        self.re_hydrogen_power_init = rep["h2_power"]
+        self.re_ev_power_list = [rep["ev_grid0"], rep["ev_grid1"]]
         self.re_ev_power_sum = self.real_charging_power = sum(self.re_ev_power_list)
-        self.hy_act = float(e.get("diag_hy_act")[0])
-        self.re_hy_gen = 900.0 * float(e.get("diag_hy_flow")[0])
+        self.hy_act = rep["hy_act"]
+        self.re_hy_gen = 900.0 * rep["hy_flow"]
         self.cumulated_income += self.income
         self.cumulated_draw_ele += self.re_ev_power_list[0] + self.re_ev_power_list[1] + self.re_hydrogen_power
         self.acumulate_reward += reward
-        store_soc = float(e.get("diag_store_soc")[0])
+        store_soc = rep["store_soc"]
         self.deviation = abs(store_soc - self.hy_init_soc)
         if bool(done[0]):  # evcssp_manager.py:275-290: computed and kept, the reward deduction itself is commented out
             cap_g = 0.089 * 200 * (5000.0 if self._kw["hydro_store_vlt"] is None else self._kw["hydro_store_vlt"]) * 1000
             dev = (store_soc - self.hy_init_soc) if self.use_lagrangian else abs(store_soc - self.hy_init_soc)
             self.test_penalty = abs(dev * cap_g / 1000 / 0.2)
         self.re_pv_power, self.re_wd_power = pv, wd
-        self.real_state = self._real_state(pv, wd, price)
+        self.real_state = self._real_state(pv, wd, price, rep)
         self.state = np.array(obs[0, : self._n_obs], dtype=np.float64)
         return self.state, reward, bool(done[0]), {}
 

@@ -221,6 +221,15 @@ enum chub_situation_column {
 int chub_situation_width(chub_engine *e, int32_t *s0, int32_t *s1);
 int chub_situation(chub_engine *e, float *out_dev, void *stream);
 
+/* One hub's scalars in one stream-ordered call -- what the single-hub gym wrapper reads after every step (the reference's
+ * real_state, evcssp_manager.py:364-372, and the attributes step() sets, evcssp_manager.py:229-297) -- instead of one
+ * chub_get_field round trip per quantity.  host_out[CHUB_REPORT_LEN] doubles: [0..13] diagnostics columns (enum
+ * chub_diag_id; 0 unless diagnostics=1), [14..16] min / charge / max power of station 0, [17..19] of station 1 (0 unless
+ * diagnostics=1), [20..21] line, [22..23] flow_in_number, [24] t, [25] store mass in g, [26] FCEV arrivals of the step,
+ * [27] FCEV backlog, [28] sticky error bits.  Synchronises the stream. */
+#define CHUB_REPORT_LEN 29
+int chub_hub_report(chub_engine *e, int32_t hub, double *host_out, void *stream);
+
 /* Parity / checkpoint read-back (synchronises). */
 int chub_get_field(chub_engine *e, int32_t field, void *host_out);
 int64_t chub_state_bytes(chub_engine *e);

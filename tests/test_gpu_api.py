@@ -213,7 +213,7 @@ def test_packed_step_equals_row_step(tables):
 def test_host_pipeline_settings(tables, threads, ranges):
     """chub_step_host with unpacked rows, one thread, odd range counts: the same bits as the device path."""
     import torch
-    (a_eng, b_eng), rs, H = _hetero_engines(tables, 2, H=40000 if ranges == 32 else 3000)
+    (a_eng, b_eng), rs, H = _hetero_engines(tables, 2, H=40000 if ranges == 32 else 6000)
     b_eng.set_host_threads(threads, ranges)
     for t in range(30):
         a = rs.uniform(-1, 1, (H, 66)).astype(np.float32)
@@ -269,3 +269,23 @@ def test_policy_and_env_in_one_torch_graph(tables):
             assert torch.equal(x, y), rep
     assert a_eng.counters()["step_index"] == b_eng.counters()["step_index"] == 8 * T
     _same_outputs(a_eng, b_eng)
+
+
+def test_hub_report_equals_field_reads(tables):
+    """chub_hub_report (one call) returns what the per-field read-backs return."""
+    import torch
+    from charginghub_env_b200 import _lib
+    eng, rs = _engine(100, tables, seed=4, diagnostics=True)
+    eng.reset()
+    for t in range(30):
+        eng.step(torch.from_numpy(rs.uniform(-1, 1, (100, 47)).astype(np.float32)).cuda())
+    for h in (0, 37, 99):
+        rep = eng.hub_report(h)
+        for name in _lib.DIAG:
+            assert rep[name] == float(eng.get("diag_" + name)[h]), name
+        for name in ("st_min_power", "st_charge_power", "st_max_power", "st_line", "st_flow_in"):
+            assert tuple(rep[name]) == tuple(float(x) if "power" in name else int(x) for x in eng.get(name)[h]), name
+        assert rep["t"] == int(eng.get("hub_t")[h]) and rep["store"] == float(eng.get("store")[h])
+        assert rep["fcev_arrive"] == int(eng.get("fcev_arrive")[h]) and rep["fcev_qn"] == int(eng.get("fcev_qn")[h])
+    with pytest.raises(Exception):
+        eng.hub_report(100)
