@@ -112,12 +112,12 @@ def measured_peak():
 
 def measured_traffic(workload, H):
     """DRAM bytes of one step-kernel launch from the committed ncu capture (profiles/), or None."""
-    p = os.path.join(ROOT, "profiles", "r01i_traffic.json")
+    p = os.path.join(ROOT, "profiles", "r01j_traffic.json")
     try:
         d = json.load(open(p))
         if d["workload"] == workload and d["hubs"] == H:
             return d["busy_hour_bytes"], {"busy_hour": d["busy_hour_bytes"], "quiet_hour": d["quiet_hour_bytes"],
-                                          "source": "profiles/r01i_traffic.json (ncu --set full, one launch)"}
+                                          "source": "profiles/r01j_traffic.json (ncu --set full, one launch)"}
     except Exception:
         pass
     return None, None
