@@ -652,11 +652,16 @@ extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *
         rc = chub_pack_actions(e, actions_host, e->packed_host);
         if (rc) return rc;
     }
+    struct Drain {   // whatever path leaves this function, nobody reads the caller's rows afterwards
+        ChubPackPool *p;
+        ~Drain() { if (p) chub_pack_pool_drain(p); }
+    } drain{nullptr};
     if (pooled) {                               // the workers start on range 0 while the streams are being forked
         const ChubClass &c0 = e->classes[0];
         if (chub_pack_pool_start(e->pool, actions_host, A, e->na_row.empty() ? nullptr : e->na_row.data(), c0.n[0] + c0.n[1],
                                  e->H, per, e->packed_host) < 0)
             return fail(CHUB_ERR_STATE, "chub_step_host: range count out of bounds");
+        drain.p = e->pool;
     }
     CK(cudaEventRecord(ev_fork, s));            // everything queued on the caller's stream comes first
     CK(cudaStreamWaitEvent(s_in, ev_fork, 0));

@@ -218,6 +218,17 @@ extern "C" int32_t chub_pack_pool_start(ChubPackPool *p, const float *rows, int3
     return n_ranges;
 }
 
+// Block until every worker is out of the current job (the caller's rows are no longer being read).
+extern "C" void chub_pack_pool_drain(ChubPackPool *p) {
+    const int T = (int) p->workers.size();
+    for (int r = 0; r < p->n_ranges; ++r) p->work_on(r);
+    int spins = 0;
+    while (p->idle.load(std::memory_order_acquire) < T) {
+        if (++spins < 20000) cpu_relax();
+        else std::this_thread::yield();
+    }
+}
+
 // Block until range r is packed; the caller takes blocks of it too instead of idling.
 extern "C" void chub_pack_pool_wait(ChubPackPool *p, int32_t r) {
     p->work_on(r);

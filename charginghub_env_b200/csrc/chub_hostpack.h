@@ -17,6 +17,8 @@ int32_t chub_pack_pool_start(ChubPackPool *p, const float *rows, int32_t stride,
                              int64_t n_rows, int64_t per, void *out);
 // returns when range r (and only range r) is packed; the caller takes blocks of that range while it waits
 void chub_pack_pool_wait(ChubPackPool *p, int32_t r);
+// returns when no worker reads the job's rows any more (error paths of the caller)
+void chub_pack_pool_drain(ChubPackPool *p);
 #ifdef __cplusplus
 }
 #endif
