@@ -277,7 +277,7 @@ def main():
     ap.add_argument("--host-threads", type=int, default=-1,
                     help="threads that pack the action rows inside chub_step_host (0: float rows cross PCIe unpacked; "
                          "default: the host's cores, less one, divided between the ranks of this box, at most 16)")
-    ap.add_argument("--host-ranges", type=int, default=16, help="hub ranges of the chub_step_host pipeline")
+    ap.add_argument("--host-ranges", type=int, default=0, help="hub ranges of the chub_step_host pipeline")
     ap.add_argument("--control", default="piles", choices=["piles", "loads"],
                     help="piles: per-pile action rows (the gym env's step, default); loads: one power target per station "
                          "(the stations' evs_step(float)), which adds the dispatch kernel to every step")
@@ -373,20 +373,23 @@ def main():
     value = H * world * K / (ms_max * 1e-3)
 
     # ---- end to end through the host-buffer C ABI call (pinned host memory both ways) ----
-    hb = eng.host_buffers()
-    hb["actions"][...] = (host_rows if args.control == "loads" else pool[0]).cpu().numpy()
+    # three pinned action matrices in rotation (296 MB at config 5: beyond any host cache), fresh values in each
+    nhost = 3
+    host_pool = [eng.host_buffers()["actions"]] + [eng.pinned_actions() for _ in range(nhost - 1)]
+    for j, a in enumerate(host_pool):
+        a[...] = (host_rows if args.control == "loads" else pool[j % npool]).cpu().numpy()
     KE = max(2, min(args.e2e_steps, K))
     local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
     host_threads = args.host_threads if args.host_threads >= 0 else min(16, ((os.cpu_count() or 2) - 1) // local_world)
     if host_threads < 4:      # too few cores per rank to threshold 98.6 MB of rows faster than PCIe carries them
         host_threads = 0
     eng.set_host_threads(host_threads, args.host_ranges)
-    for _ in range(3):
-        eng.step_host()
+    for j in range(3):
+        eng.step_host(host_pool[j % nhost], copy=False)
     barrier()
     t0 = time.perf_counter()
-    for _ in range(KE):
-        obs, rew, done = eng.step_host()
+    for j in range(KE):
+        obs, rew, done = eng.step_host(host_pool[j % nhost], copy=False)
         _ = float(rew[0])
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
@@ -395,7 +398,8 @@ def main():
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_value = H * world * KE / float(te.item())
     err = eng.counters()["error_or"]
-    per = -(-(-(-H // args.host_ranges)) // 1024) * 1024  # chub_step_host cuts the batch into hub ranges of whole blocks
+    n_ranges = args.host_ranges or (16 if host_threads else 8)
+    per = -(-(-(-H // n_ranges)) // 1024) * 1024  # chub_step_host cuts the batch into hub ranges of whole blocks
     host_chunks = -(-H // per)
 
     if rank == 0:

@@ -52,7 +52,7 @@ struct chub_engine {
     uint4 *packed_host = nullptr;    // pinned: where the pool packs the caller's rows
     ChubPackPool *pool = nullptr;
     int host_threads = -1;           // -1: not chosen yet (CHUB_HOST_THREADS or the machine's core count); 0: unpacked rows
-    int host_ranges = 16;            // hub ranges of the chub_step_host pipeline
+    int host_ranges = 0;             // hub ranges of the chub_step_host pipeline
     std::vector<int32_t> na_row;     // per-hub number of pile actions (only with more than one class)
     double *report_dev = nullptr, *report_host = nullptr;   // chub_hub_report: device gather target, pinned landing area
     int exo_mode = 0, n_pv_days = 0, n_wd_days = 0;
@@ -640,7 +640,7 @@ extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *
     const bool packed = e->host_threads > 0;
     if (packed) P.act_packed = e->packed_stage;
     else P.actions = e->actions_stage;
-    const int R = e->host_ranges;
+    const int R = e->host_ranges ? e->host_ranges : (packed ? 16 : 8);   // whole rows over PCIe: fewer, larger copies
     cudaStream_t s_in = e->host_streams[0], s_out = e->host_streams[1], *s_k = e->host_streams + 2;
     cudaEvent_t *ev_in = e->host_events, *ev_k = e->host_events + CHUB_PACK_MAX_RANGES;
     cudaEvent_t ev_fork = e->host_events[2 * CHUB_PACK_MAX_RANGES], ev_join = e->host_events[2 * CHUB_PACK_MAX_RANGES + 1];

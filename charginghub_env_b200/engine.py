@@ -269,12 +269,30 @@ class HubEngine(object):
             self._host = dict(ptrs=[pa, po, pr, pd], actions=a, obs=o, reward=r, done=d)
         return self._host
 
-    def step_host(self, actions=None, stream=0):
-        """Host-buffer step: H2D actions, step, D2H obs/reward/done, synchronise."""
+    def pinned_actions(self):
+        """One more pinned [n_hubs, action_stride] float32 array (kept alive by the engine) for callers that rotate
+        their action buffers; pass it to step_host(..., copy=False)."""
+        p = ctypes.c_void_p()
+        n = self.n_hubs * self.action_stride
+        check(self.lib.chub_alloc_host(n * 4, ctypes.byref(p)))
+        a = np.ctypeslib.as_array((ctypes.c_float * n).from_address(p.value)).reshape(self.n_hubs, self.action_stride)
+        self.host_buffers()["ptrs"].append(p)
+        return a
+
+    def step_host(self, actions=None, stream=0, copy=True):
+        """Host-buffer step: action rows from host memory, step, obs/reward/done back to pinned host arrays, synchronise.
+        actions=None steps on host_buffers()["actions"]; copy=False hands the given C-contiguous float32 array to the
+        engine as it is (pinned_actions() arrays, or any host memory) instead of copying it into the engine's own."""
         hb = self.host_buffers()
+        src = hb["actions"]
         if actions is not None:
-            hb["actions"][...] = actions
-        check(self.lib.chub_step_host(self.h, _dptr(hb["actions"]), _dptr(hb["obs"]), _dptr(hb["reward"]),
+            if copy:
+                hb["actions"][...] = actions
+            else:
+                if actions.dtype != np.float32 or not actions.flags["C_CONTIGUOUS"] or actions.shape != src.shape:
+                    raise ValueError("copy=False needs a C-contiguous float32 [%d, %d] array" % src.shape)
+                src = actions
+        check(self.lib.chub_step_host(self.h, _dptr(src), _dptr(hb["obs"]), _dptr(hb["reward"]),
                                       _dptr(hb["done"]), ctypes.c_void_p(int(stream))))
         return hb["obs"], hb["reward"], hb["done"]
 

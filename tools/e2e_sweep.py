@@ -19,16 +19,18 @@ eng = HubEngine(H, wl["classes"], action_stride=wl["stride"], auto_reset=True, t
 eng.set_traces(*bench.year_traces(tabs, 35041))
 eng.reset()
 hb = eng.host_buffers()
-hb["actions"][...] = np.random.RandomState(0).uniform(-1, 1, hb["actions"].shape).astype(np.float32)
+bufs = [hb["actions"], eng.pinned_actions(), eng.pinned_actions()]   # rotated: 296 MB, beyond the host's caches
+for k, b in enumerate(bufs):
+    b[...] = np.random.RandomState(k).uniform(-1, 1, b.shape).astype(np.float32)
 print("cores", os.cpu_count())
 for th in [int(x) for x in a.threads.split(",")]:
     for rg in [int(x) for x in a.ranges.split(",")]:
         eng.set_host_threads(th, rg)
-        for _ in range(3):
-            eng.step_host()
+        for k in range(3):
+            eng.step_host(bufs[k % 3], copy=False)
         t0 = time.perf_counter()
-        for _ in range(a.steps):
-            o, r, d = eng.step_host()
+        for k in range(a.steps):
+            o, r, d = eng.step_host(bufs[k % 3], copy=False)
             _ = float(r[0])
         dt = (time.perf_counter() - t0) / a.steps
         print("threads %2d ranges %2d: %.3f ms/step  %.4g hub-steps/s" % (th, rg, dt * 1e3, H / dt), flush=True)
