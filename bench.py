@@ -179,8 +179,8 @@ def run_reference(args, tabs, wl):
 
 def run_ppo_loop(args, eng, wl, H, S, rank, world, local, barrier):
     """BASELINE.json configs[4]: PPO-style rollout loop -- segments of 128 env steps; at every step a torch policy reads the
-    engine's obs tensor (a DLPack view, no copy) and writes the action rows, the engine steps, and obs / reward / done are
-    stored into the segment's rollout buffers.  Policy, step kernel and stores of a whole segment are ONE CUDA graph
+    latest observation and writes the action rows, the engine steps, and obs / reward / done land in the segment's rollout
+    buffers.  Policy, step kernel and stores of a whole segment are ONE CUDA graph
     (torch.cuda.graph around chub_step: the engine launches on torch's capture stream).  The policy is a stand-in (one
     linear layer + tanh through torch); it is the trainer's code, not this repo's product."""
     import torch
@@ -190,22 +190,20 @@ def run_ppo_loop(args, eng, wl, H, S, rank, world, local, barrier):
     gen = torch.Generator(device="cuda").manual_seed(4321 + rank)
     Wp = torch.randn((13, S), device=dev, generator=gen) * 0.7
     bp = torch.randn((S,), device=dev, generator=gen) * 0.3
-    obs, rew, done = eng.tensor("obs"), eng.tensor("reward"), eng.tensor("done")
     act_buf = torch.empty((T, H, S), device=dev)
-    obs_buf = torch.empty((T, H, 13), device=dev)
+    obs_buf = torch.empty((T + 1, H, 13), device=dev)    # obs_buf[t] = the observation action t is chosen on
     rew_buf = torch.empty((T, H), device=dev)
     done_buf = torch.empty((T, H), device=dev, dtype=torch.uint8)
 
     def segment():
+        obs_buf[0].copy_(obs_buf[T])                    # carry the last observation of the previous segment over
         for t in range(T):
-            obs_buf[t].copy_(obs)                       # the observation the action is chosen on
-            torch.addmm(bp, obs, Wp, out=act_buf[t])    # policy: obs [H,13] -> action rows [H,S], written in place
+            torch.addmm(bp, obs_buf[t], Wp, out=act_buf[t])   # policy: obs [H,13] -> action rows [H,S], written in place
             act_buf[t].tanh_()
-            eng.step(act_buf[t])
-            rew_buf[t].copy_(rew)
-            done_buf[t].copy_(done)
+            # the engine writes obs / reward / done of this step straight into the rollout storage (chub_step_into)
+            eng.step_into(act_buf[t], obs_buf[t + 1], rew_buf[t], done_buf[t])
 
-    eng.reset()
+    obs_buf[T].copy_(eng.reset())
     side = torch.cuda.Stream(device=dev)
     side.wait_stream(torch.cuda.current_stream())
     with torch.cuda.stream(side):                       # warm-up outside capture (cuBLAS workspaces, launch shapes)
@@ -239,7 +237,7 @@ def run_ppo_loop(args, eng, wl, H, S, rank, world, local, barrier):
     if rank == 0:
         peak, peak_src = measured_peak()
         bytes_env = eng.algorithmic_bytes(0)
-        bytes_loop = bytes_env + 13 * 4 * 2 + S * 4 + 13 * 4 + 2 * (4 + 1)   # + obs store, policy read obs / write rows, reward / done stores
+        bytes_loop = bytes_env + 13 * 4 + S * 4 + 2 * S * 4   # + policy: read obs, write rows, tanh in place (read + write)
         print(json.dumps({
             "metric": METRIC, "value": H * world * K / (ms_max * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
             "warmup": nseg_w * T, "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak",
@@ -251,7 +249,7 @@ def run_ppo_loop(args, eng, wl, H, S, rank, world, local, barrier):
                        "timer": "CUDA events around the graph replays, max over ranks"},
             "clocks": clocks, "e2e": None,
             "gpu_launches": K * 2,  # graph nodes of ours replayed in the timed region: one step kernel + one tick per env step
-            "graph_replays": nseg, "kernels_per_replay_note": "per step: 1 step kernel + 1 tick (ours), 1 GEMM + 1 tanh + 3 copies (torch)",
+            "graph_replays": nseg, "kernels_per_replay_note": "per step: 1 step kernel + 1 tick (ours), 1 GEMM + 1 tanh (torch); results land in the rollout buffers directly",
             "roofline": {"bound": "hbm", "achieved": bytes_loop * H / (ms / K * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": bytes_loop * H / (ms / K * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
                          "algorithmic_bytes_per_hub_step": bytes_loop, "kernel": "whole loop step (policy + chub_step_kernel + stores)"},

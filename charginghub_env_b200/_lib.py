@@ -78,6 +78,7 @@ SYMBOLS = {
     "chub_seed_explicit": (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp]),
     "chub_reset": (ctypes.c_int, [_vp, _vp, _i64, _vp]),
     "chub_step": (ctypes.c_int, [_vp, _vp, _vp]),
+    "chub_step_into": (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "chub_step_loads": (ctypes.c_int, [_vp, _vp, _vp]),
     "chub_situation_width": (ctypes.c_int, [_vp, _vp, _vp]),
     "chub_situation": (ctypes.c_int, [_vp, _vp, _vp]),

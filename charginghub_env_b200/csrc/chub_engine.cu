@@ -523,6 +523,25 @@ extern "C" int chub_step(chub_engine *e, const float *actions_dev, void *stream)
     return CHUB_OK;
 }
 
+extern "C" int chub_step_into(chub_engine *e, const float *actions_dev, float *obs_out_dev, float *reward_out_dev,
+                              uint8_t *done_out_dev, void *stream) {
+    if (!e || !actions_dev) return fail(CHUB_ERR_ARG, "chub_step_into: null argument");
+    CK(cudaSetDevice(e->cfg.device));
+    ChubParams P;
+    int rc = fill_params(e, P);
+    if (rc) return rc;
+    P.actions = actions_dev;
+    if (obs_out_dev) P.obs = obs_out_dev;
+    if (reward_out_dev) P.reward = reward_out_dev;
+    if (done_out_dev) P.done = done_out_dev;
+    cudaStream_t s = (cudaStream_t) stream;
+    CK(chub_launch_step(P, s));
+    chub_launch_tick(e->step_index, 1, s);
+    CK(cudaGetLastError());
+    e->launches += 1;
+    return CHUB_OK;
+}
+
 // Scalar-load step: rows [load0 kW, load1 kW, a[-2], a[-1]]; the dispatch kernel turns the two station power targets
 // into pile on-bits (evs_step(float), CHS.hpp:1169-1186 / 1478-1495), then the ordinary step kernel runs on them.
 extern "C" int chub_step_loads(chub_engine *e, const float *loads_dev, void *stream) {

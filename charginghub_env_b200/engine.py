@@ -198,6 +198,20 @@ class HubEngine(object):
         check(self.lib.chub_step(self.h, _tensor_ptr(actions), self._stream(stream)))
         return self.tensor("obs"), self.tensor("reward"), self.tensor("done")
 
+    def step_into(self, actions, obs_out=None, reward_out=None, done_out=None, stream=None):
+        """step(action) with obs / reward / done written straight into the caller's CUDA tensors (float32 [H, 13],
+        float32 [H], uint8 [H]; contiguous) -- e.g. the slices of a rollout buffer.  None keeps the engine's own."""
+        import torch
+        if tuple(actions.shape) != (self.n_hubs, self.action_stride):
+            raise ValueError("actions must be [%d, %d]" % (self.n_hubs, self.action_stride))
+        for t, shape, dt in ((obs_out, (self.n_hubs, _lib.OBS_DIM), torch.float32), (reward_out, (self.n_hubs,), torch.float32),
+                             (done_out, (self.n_hubs,), torch.uint8)):
+            if t is not None and (tuple(t.shape) != shape or t.dtype != dt or not t.is_contiguous()):
+                raise ValueError("output tensors must be contiguous %r %s" % (shape, dt))
+        check(self.lib.chub_step_into(self.h, _tensor_ptr(actions), _tensor_ptr(obs_out) if obs_out is not None else None,
+                                      _tensor_ptr(reward_out) if reward_out is not None else None,
+                                      _tensor_ptr(done_out) if done_out is not None else None, self._stream(stream)))
+
     def step_packed(self, packed, stream=None):
         """step(action) on packed records: CUDA int32/uint8 tensor of 16 bytes per hub, {on-bits lo, on-bits hi, a[-2],
         a[-1]} (include/chub.h chub_step_packed; pack_actions builds them from float rows on the host)."""

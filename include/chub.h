@@ -167,6 +167,13 @@ int chub_reset(chub_engine *e, const uint8_t *mask_dev, int64_t step_index, void
  * in [-1,1] exactly as the reference's action vector.  Fills obs / reward / done buffers. */
 int chub_step(chub_engine *e, const float *actions_dev, void *stream);
 
+/* chub_step with the results written straight into buffers of the caller -- the slices of a trainer's rollout storage
+ * (obs_out_dev float32 [n_hubs][13], reward_out_dev float32 [n_hubs], done_out_dev uint8 [n_hubs]; NULL = the engine's
+ * own buffer, which is then the only one updated for that quantity).  Saves the copy kernels of a rollout loop; with
+ * auto-reset the obs written is the first obs of the next episode, as in chub_step. */
+int chub_step_into(chub_engine *e, const float *actions_dev, float *obs_out_dev, float *reward_out_dev,
+                   uint8_t *done_out_dev, void *stream);
+
 /* The stations' scalar-load step, evs_step(float) (CHS.hpp:1169-1186 slow, 1478-1495 fast; bound in main.cpp:196-197):
  * each station gets ONE power target in kW instead of per-pile switches; it is clamped to [min_power, max_power]
  * (catch_load, CHS.hpp:358-366) and handed out to the cars in order of urgency (assign_on_off / rank_power_add,

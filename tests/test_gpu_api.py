@@ -289,3 +289,31 @@ def test_hub_report_equals_field_reads(tables):
         assert rep["fcev_arrive"] == int(eng.get("fcev_arrive")[h]) and rep["fcev_qn"] == int(eng.get("fcev_qn")[h])
     with pytest.raises(Exception):
         eng.hub_report(100)
+
+
+def test_step_into_equals_step(tables):
+    """chub_step_into: results written into the caller's tensors are what chub_step leaves in the engine's buffers."""
+    import torch
+    H = 1500
+    a_eng, rs = _engine(H, tables, seed=12, auto_reset=True)
+    b_eng, _ = _engine(H, tables, seed=12, auto_reset=True)
+    a_eng.reset()
+    b_eng.reset()
+    T = 100
+    ob = torch.empty((T, H, 13), device="cuda")
+    rb = torch.empty((T, H), device="cuda")
+    db = torch.empty((T, H), device="cuda", dtype=torch.uint8)
+    for t in range(T):
+        a = torch.from_numpy(rs.uniform(-1, 1, (H, 47)).astype(np.float32)).cuda()
+        o, r, d = a_eng.step(a)
+        if t % 3 == 0:
+            b_eng.step_into(a, ob[t], rb[t], db[t])
+        else:   # mixed: only some outputs redirected
+            b_eng.step_into(a, ob[t], None, db[t])
+            rb[t].copy_(b_eng.tensor("reward"))
+        assert torch.equal(o, ob[t]) and torch.equal(r, rb[t]) and torch.equal(d, db[t]), t
+    _same_outputs_state = ("pile_soc", "pile_stay", "st_line", "hub_uctr", "hub_lcg", "store")
+    for name in _same_outputs_state:
+        assert np.array_equal(a_eng.get(name), b_eng.get(name)), name
+    with pytest.raises(ValueError):
+        b_eng.step_into(a, ob[0][:, :12])
