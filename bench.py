@@ -378,9 +378,11 @@ def main():
         a[...] = (host_rows if args.control == "loads" else pool[j % npool]).cpu().numpy()
     KE = max(2, min(args.e2e_steps, K))
     local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
-    host_threads = args.host_threads if args.host_threads >= 0 else min(16, ((os.cpu_count() or 2) - 1) // local_world)
-    if host_threads < 4:      # too few cores per rank to threshold 98.6 MB of rows faster than PCIe carries them
-        host_threads = 0
+    host_threads = args.host_threads
+    if host_threads < 0:
+        host_threads = min(16, ((os.cpu_count() or 2) - 1) // local_world)
+        if host_threads < 4:  # too few cores per rank to threshold 98.6 MB of rows faster than PCIe carries them
+            host_threads = 0
     eng.set_host_threads(host_threads, args.host_ranges)
     for j in range(3):
         eng.step_host(host_pool[j % nhost], copy=False)
