@@ -124,3 +124,73 @@ def test_launch_shape_and_sharding_do_not_change_a_bit(tables):
     half = H_FULL // 2 + 5                 # an unaligned split: the upper part as its own engine (another "rank")
     upper = _rollout(_engine(H_FULL - half, tables, seed, base=half), steps, 7, H_FULL, offset=half)
     assert torch.equal(ref[half:], upper)
+
+
+def test_long_horizon_rollout_matches_the_oracle(tables):
+    """Config 4 in small: 21 simulated days (2,016 steps) of auto-reset episodes on 20,000 hubs, the shared traces a ring of
+    7 days that the absolute step index wraps around three times, actions from a fixed pool, the engine driven by
+    CUDA-graph segments of 32 steps; the oracle follows two windows of hubs step by step.  Integers must agree bit for
+    bit at every check, floats within RTOL -- a drift would compound over two thousand steps."""
+    import torch
+    from oracle import oracle as O
+    from charginghub_env_b200 import HubEngine
+    seed, H, DAYS, RING, SEG = 0xABCDE, 20000, 21, 7 * 96, 32
+    t = np.arange(RING, dtype=np.float64)
+    pv = 210.0 * np.maximum(0.0, np.sin(np.pi * ((t % 96) - 24) / 48.0)) * (1 + 0.3 * np.cos(2 * np.pi * (t // 96) / 7.0))
+    wd = np.clip(46 + 40 * np.sin(2 * np.pi * t / RING * 3) + 10 * np.sin(2 * np.pi * t / 32.0), 0, 98)
+    price = tables["price"][(t.astype(np.int64) - 1) % 96] * (1 + 0.1 * np.sin(2 * np.pi * (t // 96) / 7.0))
+    eng = HubEngine(H, [C.DEFAULT_KW], device=0, diagnostics=True, tables=tables, seed=seed, auto_reset=True)
+    eng.set_traces(pv, wd, price)
+    bases = [0, H - 64]
+    orcs = []
+    for b in bases:
+        o = O.Oracle(64, [C.DEFAULT_KW], tables=C.oracle_tables(tables))
+        o.seed_base(seed, b)
+        o.reset(pv[0], wd[0], price[0])
+        orcs.append(o)
+    rs = np.random.RandomState(8)
+    pool = rs.uniform(-1, 1, (SEG, H, 47)).astype(np.float32)     # step j of every segment uses pool[j]
+    pool_dev = torch.from_numpy(pool).cuda()
+    eng.reset()
+    side = torch.cuda.Stream()
+    g = torch.cuda.CUDAGraph()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.graph(g, stream=side):
+        for j in range(SEG):
+            eng.step(pool_dev[j])
+    steps = 0
+    returns = [np.zeros(64), np.zeros(64)]
+    for seg in range(DAYS * 96 // SEG):
+        g.replay()
+        for j in range(SEG):
+            k = steps + j + 1                                      # absolute index of the state being entered
+            for w, (b, o) in enumerate(zip(bases, orcs)):
+                o.step(pool[j, b:b + 64], pv[k % RING], wd[k % RING], price[k % RING])
+                if o.get("hub_done").all():
+                    returns[w] = o.get("ep_return").copy()
+                    o.reset(pv[k % RING], wd[k % RING], price[k % RING])
+        steps += SEG
+        torch.cuda.synchronize()
+        deep = seg % 9 == 0 or steps == DAYS * 96
+        obs = eng.tensor("obs").cpu().numpy()
+        for name in (C.INT_FIELDS if deep else ["st_line", "hub_uctr", "hub_lcg", "hub_t"]):
+            a = eng.get(name)
+            for b, o in zip(bases, orcs):
+                x, y = a[b:b + 64], o.get(name)
+                if name in ("hub_uctr", "hub_lcg"):
+                    x, y = x.astype(np.uint32), y.astype(np.uint32)
+                assert np.array_equal(x, y), (name, steps, b)
+        for b, o in zip(bases, orcs):
+            assert C.close(obs[b:b + 64], o.get("obs"), atol=C.RTOL).all(), ("obs", steps, b)
+        if deep:
+            for name in C.PILE_FLOATS + ["store"]:
+                a = eng.get(name)
+                for b, o in zip(bases, orcs):
+                    y = o.get(name)
+                    if name == "pile_power":
+                        y = y * o.get("pile_car")
+                    assert C.close(a[b:b + 64], y, atol=C.RTOL).all(), (name, steps, b)
+    assert eng.counters()["step_index"] == DAYS * 96 and eng.counters()["error_or"] == 0
+    last = eng.tensor("last_stats").cpu().numpy()
+    for w, b in enumerate(bases):
+        assert np.allclose(last[b:b + 64, 0], returns[w], rtol=1e-4, atol=1e-4)
