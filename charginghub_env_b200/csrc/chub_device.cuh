@@ -152,7 +152,7 @@ __device__ __noinline__ uint2 draw_mk_soc(uint32_t lcg) {
     const double x = 2.0 * canon_d_of(chub_minstd_next(s0), chub_minstd_jump(s0, CHUB_MINSTD_A2)) - 1.0;
     const double y = 2.0 * canon_d_of(chub_minstd_jump(s0, CHUB_MINSTD_A3), lcg) - 1.0;
     const double r2 = x * x + y * y;
-    double mult = sqrt(chub_div(-2.0 * chub_log(r2, log_tab<LT>()), r2));
+    double mult = sqrt(chub_div(-2.0 * chub_log_r2(r2, log_tab<LT>()), r2));
     float de = (float) ((y * mult) * 3.0 + 7.0);
     de = fminf(fmaxf(de, 1.0f), 10.0f);
     return make_uint2(__float_as_uint((float) (75.0 - 5.0 * (double) de)), lcg);
@@ -197,7 +197,7 @@ __device__ __forceinline__ float mk_soc_from(uint32_t s0) {
     const double x = 2.0 * canon_d_of(chub_minstd_next(s0), chub_minstd_jump(s0, CHUB_MINSTD_A2)) - 1.0;
     const double y = 2.0 * canon_d_of(chub_minstd_jump(s0, CHUB_MINSTD_A3), chub_minstd_jump(s0, CHUB_MINSTD_A4)) - 1.0;
     const double r2 = x * x + y * y;
-    const double mult = sqrt(chub_div(-2.0 * chub_log(r2, log_tab<LT>()), r2));
+    const double mult = sqrt(chub_div(-2.0 * chub_log_r2(r2, log_tab<LT>()), r2));
     float de = (float) ((y * mult) * 3.0 + 7.0);
     de = fminf(fmaxf(de, 1.0f), 10.0f);
     return (float) (75.0 - 5.0 * (double) de);
@@ -207,7 +207,7 @@ template <int LT>
 __device__ __forceinline__ int late_time_from(uint32_t s0) {
     const float x = 2.0f * canon_f_of(chub_minstd_next(s0)) - 1.0f, y = 2.0f * canon_f_of(chub_minstd_jump(s0, CHUB_MINSTD_A2)) - 1.0f;
     const float r2 = x * x + y * y;
-    const float lg = (float) chub_log((double) r2, log_tab<LT>());
+    const float lg = (float) chub_log_r2((double) r2, log_tab<LT>());
     const float v = (y * sqrtf(-2.0f * lg / r2)) * 2.0f + 2.0f;
     const int d = (int) roundf(v);
     return d > 0 ? d : 0;
@@ -224,7 +224,7 @@ __device__ __noinline__ uint2 draw_normal_f(uint32_t lcg, float mean, float sd) 
         y = 2.0f * canon_f(lcg) - 1.0f;
         r2 = x * x + y * y;
     } while (r2 > 1.0f || r2 == 0.0f);
-    float lg = (float) chub_log((double) r2, log_tab<LT>());
+    float lg = (float) chub_log_r2((double) r2, log_tab<LT>());
     float mult = sqrtf(-2.0f * lg / r2);
     float ret = y * mult;
     return make_uint2(__float_as_uint(ret * sd + mean), lcg);

@@ -60,6 +60,11 @@ CHUB_FM double chub_log(double x, const ChubLogEntry *tab) {
     return hi + fma(r2, p, lo);
 }
 
+// log of the polar method's r2 in (0, 1].  glibc's log / logf return exactly +0 for 1, and the normal variate then is
+// y * sqrt(-0) = 0; the table path above returns 1.8e-18 there, whose square root argument is NEGATIVE -> NaN.  r2 == 1
+// happens once in about 2^24 float attempts (x^2 + y^2 rounds to 1.0f), i.e. every few steps somewhere in a large batch.
+CHUB_FM double chub_log_r2(double r2, const ChubLogEntry *tab) { return r2 == 1.0 ? 0.0 : chub_log(r2, tab); }
+
 // @region chub_exp
 // exp(a) for |a| < 700 (no overflow / underflow handling).
 CHUB_FM double chub_exp(double a) {

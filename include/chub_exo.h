@@ -32,7 +32,7 @@ CHUB_HD double chub_xnormal(uint32_t key0, uint32_t key1, uint32_t *counter, con
         const double xx = x * x, yy = y * y;
         r2 = xx + yy;
     } while (r2 >= 1.0 || r2 == 0.0);
-    return x * sqrt(chub_div(-2.0 * chub_log(r2, log_table), r2));
+    return x * sqrt(chub_div(-2.0 * chub_log_r2(r2, log_table), r2));
 }
 
 #endif /* CHUB_EXO_H */

@@ -56,7 +56,26 @@ int main(int argc, char **argv) {
         double den = 0.5 + 40 * U(g);
         bad_div += chub_div(num, den) != num / den;
     }
-    printf("{\"n\": %ld, \"log_curve_max_ulp\": %.3f, \"log_normal_max_relerr_eps\": %.3f, \"exp_max_ulp\": %.3f, "
+    // the float polar normal exactly as the kernel forms it (csrc/chub_device.cuh late_time_from), on EVERY float r2 of
+    // the last 2^16 below and including 1.0f and on the smallest ones: x^2 + y^2 rounds to exactly 1.0f once in about
+    // 2^24 attempts, where log must be +0 (glibc) and not the table path's 1.8e-18 (sqrt of a negative: NaN)
+    long bad_edge = 0;
+    for (int k = 0; k < 65536 + 4096; ++k) {
+        float r2f = k < 65536 ? std::nextafterf(1.0f, 0.0f) : 1e-38f;
+        if (k < 65536) { r2f = 1.0f; for (int j = 0; j < k; ++j) r2f = std::nextafterf(r2f, 0.0f); if (k > 64) r2f = 1.0f - k * 5.9604645e-08f; }
+        else r2f = std::ldexp(1.0f + (k - 65536) / 4096.0f, -120 + (k % 97));
+        for (float y : {0.94084024f, -0.3f, 1e-3f}) {
+            float lg1 = (float) chub_log_r2((double) r2f, tab), lg0 = logf(r2f);
+            float v1 = (y * sqrtf(-2.0f * lg1 / r2f)) * 2.0f + 2.0f, v0 = (y * sqrtf(-2.0f * lg0 / r2f)) * 2.0f + 2.0f;
+            // the variate is only ever used rounded to an integer (CHS.hpp:828, 835); glibc's logf is one ulp off the
+            // correctly rounded value on a few arguments, which moves v by an ulp but not its rounding
+            bad_edge += std::isnan(v1) || std::isnan(v0) || std::fabs(v1) > 1e5f ? std::isnan(v1) : (int) roundf(v1) != (int) roundf(v0);
+            if (getenv("CHUB_VERBOSE") && std::isnan(v1)) fprintf(stderr, "k %d r2 %.9g y %g lg1 %.9g lg0 %.9g v1 %.9g v0 %.9g\n", k, r2f, y, lg1, lg0, v1, v0);
+        }
+    }
+    bad_edge += chub_log_r2(1.0, tab) != 0.0 || std::isnan(std::sqrt(chub_div(-2.0 * chub_log_r2(1.0, tab), 1.0)));
+    printf("{\"normal_edge_mismatch\": %ld, ", bad_edge);
+    printf("\"n\": %ld, \"log_curve_max_ulp\": %.3f, \"log_normal_max_relerr_eps\": %.3f, \"exp_max_ulp\": %.3f, "
            "\"float_mismatch_log\": %ld, \"float_mismatch_normal\": %ld, \"float_mismatch_exp\": %ld, \"div_mismatch\": %ld}\n",
            n, max_log_a, max_log_b, max_exp, f_log, f_norm, f_exp, bad_div);
     return 0;

@@ -16,3 +16,4 @@ def test_fastmath_against_libm(tmp_path):
     # what matters to parity: after the reference's fp32 narrowing nothing differs
     assert out["float_mismatch_log"] == 0 and out["float_mismatch_exp"] == 0 and out["float_mismatch_normal"] == 0
     assert out["div_mismatch"] == 0
+    assert out["normal_edge_mismatch"] == 0   # r2 == 1.0f and its neighbours, tiny r2: no NaN, same fp32 variate as libm

@@ -167,3 +167,41 @@ def test_action_row_layouts(tables, stride, offset, H):
                         done=done.cpu().numpy())
     assert not mm, str(mm)
     assert eng.counters()["error_or"] == 0
+
+
+def test_config3_ten_days_heterogeneous_auto_reset(tables):
+    """Config 3 in small: heterogeneous hubs (4..32 piles per station, all four station-type orders,
+    constant-power classes, H2 sizes, permeate up to 0.05), padded action rows of 66, fused auto-reset, 10 x 96 steps with
+    per-hub traces; the scalar-load step takes every fifth step.  The oracle is reset by hand at every done."""
+    import torch
+    rs = np.random.RandomState(33)
+    classes = _hetero_classes(rs, 16)
+    H, T = 384, 10 * 96
+    hub_class = rs.randint(0, len(classes), H).astype(np.int32)
+    eng, orc, (pv, wd, price) = _pair(H, classes, hub_class, tables, 777, True, T + 1, rs, auto_reset=True, stride=66)
+    caps = np.array([[40.0 * n for n in classes[k]["station_list"]] for k in hub_class], np.float32)
+    eng.reset()
+    orc.reset(pv[0], wd[0], price[0])
+    mm = C.Mismatch()
+    for t in range(T):
+        if t % 5 == 4:
+            loads = np.concatenate([rs.uniform(0, 1, (H, 2)).astype(np.float32) ** 2 * caps,
+                                    rs.uniform(-1, 1, (H, 2)).astype(np.float32)], axis=1)
+            obs, rew, done = eng.step_loads(torch.from_numpy(loads).cuda())
+            orc.set_load_mode(True)
+            orc.step(loads, pv[t + 1], wd[t + 1], price[t + 1])
+        else:
+            a = rs.uniform(-1, 1, (H, 66)).astype(np.float32)
+            obs, rew, done = eng.step(torch.from_numpy(a).cuda())
+            orc.set_load_mode(False)
+            orc.step(a, pv[t + 1], wd[t + 1], price[t + 1])
+        want_rew, want_done = orc.get("reward"), orc.get("hub_done")
+        if want_done.all():
+            orc.reset(pv[t + 1], wd[t + 1], price[t + 1])
+        if (t + 1) % 24 == 0 or want_done.any():
+            torch.cuda.synchronize()
+            assert np.array_equal(done.cpu().numpy().astype(np.int32), want_done), t
+            assert C.close(rew.cpu().numpy(), want_rew, atol=C.RTOL).all(), t
+            C.compare_state(eng, orc, 0, mm, C.SCALE, obs=obs.cpu().numpy())
+            assert not mm, "t=%d %s" % (t, mm)
+    assert eng.counters()["error_or"] == int(np.bitwise_or.reduce(orc.get("hub_err")))
