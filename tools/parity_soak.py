@@ -17,6 +17,7 @@ ap.add_argument("--classes", type=int, default=0, help="0: default hubs; N: N ra
 ap.add_argument("--seed", type=int, default=2024)
 ap.add_argument("--every", type=int, default=8)
 ap.add_argument("--threads", type=int, default=os.cpu_count() or 4)
+ap.add_argument("--loads-every", type=int, default=0, help="N: every Nth step is a scalar-load step (chub_step_loads)")
 a = ap.parse_args()
 tabs = load_tables()
 rs = np.random.RandomState(a.seed)
@@ -48,10 +49,23 @@ FIELDS = ["hub_lcg", "hub_uctr", "st_line", "st_flow_in", "pile_car", "pile_char
 FLOATS = ["pile_soc", "pile_power", "pile_target", "store"]
 
 
+caps = torch.tensor([[40.0 * n for n in classes[0 if hub_class is None else k]["station_list"]]
+                     for k in (range(1) if hub_class is None else hub_class)], device="cuda")
+
+
+def is_load_step(t):
+    return a.loads_every > 0 and t % a.loads_every == a.loads_every - 1
+
+
 def orc_steps(o, lo, hi, acts, t0):
     for j in range(acts.shape[0]):
         t = t0 + j
-        o.step(acts[j, lo:hi], pv[t + 1], wd[t + 1], price[t + 1])
+        if is_load_step(t):
+            o.set_load_mode(True)
+            o.step(np.ascontiguousarray(acts[j, lo:hi, :4]), pv[t + 1], wd[t + 1], price[t + 1])
+            o.set_load_mode(False)
+        else:
+            o.step(acts[j, lo:hi], pv[t + 1], wd[t + 1], price[t + 1])
         if o.get("hub_done").all():
             o.reset(pv[t + 1], wd[t + 1], price[t + 1])
 
@@ -62,7 +76,11 @@ for t0 in range(0, T, a.every):
     n = min(a.every, T - t0)
     acts = torch.rand((n, H, S), device="cuda", generator=gen) * 2 - 1
     for j in range(n):
-        eng.step(acts[j])
+        if is_load_step(t0 + j):   # columns 0..1 become power targets in kW, 2..3 stay the analog actions
+            acts[j, :, :2] = ((acts[j, :, :2] + 1) * 0.5) ** 2 * caps
+            eng.step_loads(acts[j, :, :4].contiguous())
+        else:
+            eng.step(acts[j])
     acts_h = acts.cpu().numpy()
     th = [threading.Thread(target=orc_steps, args=(o, lo, hi, acts_h, t0)) for lo, hi, o in orcs]
     [x.start() for x in th]
