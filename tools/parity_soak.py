@@ -17,6 +17,8 @@ ap.add_argument("--classes", type=int, default=0, help="0: default hubs; N: N ra
 ap.add_argument("--seed", type=int, default=2024)
 ap.add_argument("--every", type=int, default=8)
 ap.add_argument("--threads", type=int, default=os.cpu_count() or 4)
+ap.add_argument("--exogenous", default="traces", choices=["traces", "device"],
+                help="device: the on-device PV / wind / price generator against oracle/exo_oracle.c (default hubs only)")
 ap.add_argument("--loads-every", type=int, default=0, help="N: every Nth step is a scalar-load step (chub_step_loads)")
 a = ap.parse_args()
 tabs = load_tables()
@@ -31,7 +33,11 @@ else:
 pv, wd, price = C.synth_traces(tabs, T + 1, rs)
 eng = HubEngine(H, classes, hub_class=hub_class, device=0, diagnostics=False, tables=tabs, seed=a.seed, auto_reset=True,
                 action_stride=S)
-eng.set_traces(pv, wd, price)
+GEN = a.exogenous == "device"
+if GEN:
+    eng.set_exogenous_generator(tabs, 0.25, 0.1)
+else:
+    eng.set_traces(pv, wd, price)
 nt = max(1, min(a.threads, H // 64))
 per = -(-H // nt)
 orcs = []
@@ -40,7 +46,12 @@ for k in range(nt):
     o = O.Oracle(hi - lo, classes, hub_class=None if hub_class is None else np.ascontiguousarray(hub_class[lo:hi]),
                  tables=C.oracle_tables(tabs))
     o.seed_base(a.seed, lo)
-    o.reset(pv[0], wd[0], price[0])
+    if GEN:
+        o.exo = O.ExoOracle(hi - lo, tabs, 0.25, 0.1)
+        o.exo.seed_base(a.seed, lo)
+        o.reset(*o.exo.reset())
+    else:
+        o.reset(pv[0], wd[0], price[0])
     orcs.append((lo, hi, o))
 eng.reset()
 gen = torch.Generator(device="cuda").manual_seed(a.seed)
@@ -64,10 +75,15 @@ def orc_steps(o, lo, hi, acts, t0):
             o.set_load_mode(True)
             o.step(np.ascontiguousarray(acts[j, lo:hi, :4]), pv[t + 1], wd[t + 1], price[t + 1])
             o.set_load_mode(False)
+        elif GEN:
+            o.step(acts[j, lo:hi], *o.exo.step(o.get("hub_t")))
         else:
             o.step(acts[j, lo:hi], pv[t + 1], wd[t + 1], price[t + 1])
         if o.get("hub_done").all():
-            o.reset(pv[t + 1], wd[t + 1], price[t + 1])
+            if GEN:
+                o.reset(*o.exo.reset())
+            else:
+                o.reset(pv[t + 1], wd[t + 1], price[t + 1])
 
 
 t_start = time.time()
