@@ -8,7 +8,10 @@ one-thread tick kernel that advances the trace index).  Workloads (BASELINE.json
                      fill a B200 -- reported for completeness)
   config3          : 262,144 heterogeneous hubs, auto-reset
 Metric value = hubs x steps / max-over-ranks device time, inputs already resident in HBM.
-e2e = the same through chub_step_host: pinned host actions in, obs/reward/done out, every step.
+e2e = the same through chub_step_host, the call a host caller of the reference makes: float action rows in pinned host
+      memory in (three matrices in rotation, so they come from DRAM), obs/reward/done out to pinned host memory, every
+      step; the rows are thresholded into 16-byte records by host threads before they cross PCIe (--host-threads 0: not).
+--loop ppo = BASELINE configs[4]: torch policy + env + rollout buffers, one CUDA graph per 128-step segment.
 --impl reference times the CPU restatement of the reference path (oracle/, "port") on the host cores.
 """
 import argparse
