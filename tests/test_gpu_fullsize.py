@@ -194,3 +194,15 @@ def test_long_horizon_rollout_matches_the_oracle(tables):
     last = eng.tensor("last_stats").cpu().numpy()
     for w, b in enumerate(bases):
         assert np.allclose(last[b:b + 64, 0], returns[w], rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("extra", [[], ["--classes", "8", "--loads-every", "3"], ["--exogenous", "device"]])
+def test_parity_soak_tool_small(extra):
+    """tools/parity_soak.py (the large GPU-vs-checker soak whose results are in profiles/) in small, so that it stays runnable."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "tools", "parity_soak.py"), "--hubs", "2048", "--days", "2",
+                          "--threads", "4"] + extra, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert "soak passed: 2048 hubs x 192 steps" in out.stdout
