@@ -615,6 +615,8 @@ static int host_pipeline_setup(chub_engine *e) {
     if (e->host_threads < 0) {
         const char *t = getenv("CHUB_HOST_THREADS"), *r = getenv("CHUB_HOST_RANGES");
         int hw = (int) std::thread::hardware_concurrency();
+        const char *lw = getenv("LOCAL_WORLD_SIZE");   // one process per GPU (torchrun): the ranks share the host's cores
+        if (lw && atoi(lw) > 1) hw = std::max(2, hw / atoi(lw));
         e->host_threads = t ? atoi(t) : std::max(1, std::min(std::min(hw - 1, 16), e->H / 8192));  // small batches: one helper
         if (e->host_threads < 0 || e->host_threads > 64) e->host_threads = 1;
         if (r && atoi(r) >= 1 && atoi(r) <= CHUB_PACK_MAX_RANGES) e->host_ranges = atoi(r);

@@ -194,7 +194,7 @@ int chub_step_packed(chub_engine *e, const void *packed_dev, void *stream);
  * those cross the bus (16 instead of 4*action_stride bytes per hub); ranges of hubs flow through pack -> copy in ->
  * kernel -> copy out concurrently.  chub_set_host_threads chooses the pool size (0 = send the float rows unpacked;
  * default: CHUB_HOST_THREADS or min(cores - 1, 16)) and the number of ranges (0 = keep; default 16 packed, 8 unpacked; at most 32).
- * One process per GPU on a shared host should divide the cores between the ranks.
+ * One process per GPU on a shared host should divide the cores between the ranks (the default does, by LOCAL_WORLD_SIZE).
  * chub_pack_actions is the packing alone: [n_hubs][action_stride] host rows -> [n_hubs] host records. */
 int chub_step_host(chub_engine *e, const float *actions_host, float *obs_host, float *reward_host,
                    uint8_t *done_host, void *stream);
