@@ -19,6 +19,7 @@ ap.add_argument("--every", type=int, default=8)
 ap.add_argument("--threads", type=int, default=os.cpu_count() or 4)
 ap.add_argument("--exogenous", default="traces", choices=["traces", "device"],
                 help="device: the on-device PV / wind / price generator against oracle/exo_oracle.c (default hubs only)")
+ap.add_argument("--host", action="store_true", help="drive the per-pile steps through chub_step_host (host rows, pack pool)")
 ap.add_argument("--loads-every", type=int, default=0, help="N: every Nth step is a scalar-load step (chub_step_loads)")
 a = ap.parse_args()
 tabs = load_tables()
@@ -95,6 +96,8 @@ for t0 in range(0, T, a.every):
         if is_load_step(t0 + j):   # columns 0..1 become power targets in kW, 2..3 stay the analog actions
             acts[j, :, :2] = ((acts[j, :, :2] + 1) * 0.5) ** 2 * caps
             eng.step_loads(acts[j, :, :4].contiguous())
+        elif a.host:
+            eng.step_host(acts[j].cpu().numpy())
         else:
             eng.step(acts[j])
     acts_h = acts.cpu().numpy()
