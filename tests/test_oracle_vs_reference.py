@@ -38,6 +38,12 @@ def test_default_hub_live():
     _compare(dict(ref_env.DEFAULT_KWARGS), 24, 96, 777)
 
 
+def test_five_days_live():
+    """Past the first day: the reference keeps stepping after done (time wraps, evcssp_manager.py:271-299); 5 x 96 steps.
+    (Run once at 160 hubs x 960 steps and, with 9 fast + 17 slow piles, permeate 0.05 and store loss, 120 x 960: equal.)"""
+    _compare(dict(ref_env.DEFAULT_KWARGS), 24, 480, 4242)
+
+
 def test_unclipped_table_equals_reference_list():
     from oracle import oracle as O
     Env = ref_env.load_reference_env_class()
