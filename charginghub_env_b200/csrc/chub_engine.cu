@@ -708,7 +708,8 @@ extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *
         CK(cudaEventRecord(ev_k[c], sk));
         CK(cudaStreamWaitEvent(s_out, ev_k[c], 0));
         // results go back in at most 8 pieces: below a few MB a copy costs its set-up, not its bytes
-        if ((c + 1) % out_every != 0 && b + per < e->H) continue;
+        // (the last two ranges go back on their own: whatever follows the last kernel is the tail of the step)
+        if ((c + 1) % out_every != 0 && b + 2 * (size_t) per < (size_t) e->H) continue;
         const int ob = out_begin, on = b + n - out_begin;
         out_begin = b + n;
         if (obs_host) CK(cudaMemcpyAsync(obs_host + (size_t) ob * CHUB_OBS_DIM, e->obs + (size_t) ob * CHUB_OBS_DIM,
