@@ -311,7 +311,7 @@ def main():
     K, W = args.steps, max(args.warmup, 3)
     eng = HubEngine(H, wl["classes"], hub_class=wl["hub_class"], device=local, hub_id_base=rank * H,
                     action_stride=S, auto_reset=wl["auto_reset"], diagnostics=False, tables=tabs, seed=0x5EED)
-    L = 35040 + 1
+    L = 35040   # a whole year of days: the engine wraps around the trace
     if args.exogenous == "device":
         eng.set_exogenous_generator(tabs, 0.0, 0.0)
         wl["desc"] += ", exogenous inputs generated on the device"

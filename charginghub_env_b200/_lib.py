@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libchub.so")
 MAX_PILES = 32
 OBS_DIM = 13
 EL_TABLE = 102
-FCEV_QCAP = 8
+FCEV_QCAP = 16
 DAY = 96
 REPORT_LEN = 29
 FAST, SLOW = 0, 1
@@ -98,6 +98,12 @@ SYMBOLS = {
     "chub_get_state": (ctypes.c_int, [_vp, _vp]),
     "chub_set_state": (ctypes.c_int, [_vp, _vp]),
     "chub_counters": (ctypes.c_int, [_vp, ctypes.POINTER(_i64), ctypes.POINTER(_i64), ctypes.POINTER(ctypes.c_uint32)]),
+    "chub_gather_stats": (ctypes.c_int, [_vp, _vp, _i32, _vp, _vp, _vp]),
+    "chub_gather_wait": (ctypes.c_int, [_vp, _vp]),
+    "chub_reduce_stats": (ctypes.c_int, [_vp, _vp, _vp, _vp]),
+    "chub_set_timing": (ctypes.c_int, [_vp, _i32]),
+    "chub_step_times": (ctypes.c_int, [_vp, _vp, _i32, ctypes.POINTER(_i32)]),
+    "chub_debug_curve": (ctypes.c_int, [_vp, _i32, ctypes.c_uint32, _i64, _vp, _vp]),
     "chub_alloc_host": (ctypes.c_int, [_i64, ctypes.POINTER(_vp)]),
     "chub_free_host": (ctypes.c_int, [_vp]),
     "chub_algorithmic_bytes": (_i64, [_vp, _i32]),

@@ -258,7 +258,10 @@ __device__ __forceinline__ int rng_init_cars(HubRng &r, int mu) {  // CHS.hpp:83
 __device__ __forceinline__ float slow_s2t(float s) {
     if (s < 0.0f) return 0.0f;
     double d = (double) s;
-    if (d <= 73.89239629561729) return (float) (d * fma(kC.slow_stt1_a, d, 0.1295));
+    // a s^2 + 0.1295 s with the square and the linear term rounded on their own, as the reference's pow(soc, 2) form
+    // does: the shorter d * fma(a, d, 0.1295) differs from glibc on ONE reachable argument (61.03515625f), this form on
+    // none (tests/test_gpu_curves.py walks all of them)
+    if (d <= 73.89239629561729) return (float) fma(kC.slow_stt1_a, d * d, 0.1295 * d);
     if (d <= 100.0) {
         double p = fma(fma(fma(fma(kC.slow_stt2_a, d, -0.001529), d, 0.1871), d, -10.15), d, 213.1);
         float q = (float) (p + 0.1787983924863248);
@@ -314,6 +317,15 @@ __device__ __forceinline__ float fast_s2t(float s) {
     double den = fma(fma(z, 1.0, (double) -23.9f), z, (double) 56.48f) * z2 + q3z + (double) 18.96f;
     return (float) chub_div(num, den);
 }
+// a_part2 (CHS.hpp:688-690), the quartic power fit of the fast charger's second segment.  It falls to zero at 51.2
+// minutes, where its terms (~1500 each) cancel down to ~0.02: there the rounding of every partial result shows in the
+// float32 value, and the fma-Horner chain differs from the reference on six reachable arguments.  Evaluated in the
+// reference's own order -- powers by repeated multiplication, terms added left to right -- it equals glibc's pow form
+// on every float32 argument of the segment (exhaustive: tests/test_gpu_curves.py).
+__device__ __forceinline__ float fast_a2(double x) {
+    const double x2 = x * x, x3 = x2 * x, x4 = x2 * x2;
+    return (float) ((((0.0002253 * x4 - 0.03572 * x3) + 2.016 * x2) - 48.76 * x) + 457.7);
+}
 __device__ __forceinline__ float fast_aa2(double x) {
     double p = x * fma(fma(fma(fma(0.0002253 / 5, x, -(0.03572 / 4)), x, 2.016 / 3), x, -(48.76 / 2)), x, 457.7);
     return (float) (p + (double) kC.fast_aa2_c);
@@ -331,7 +343,7 @@ __device__ __forceinline__ void fast_step(float t, float &soc, float &power) {
         power = (float) (0.7194 * ex + 47.78);
     } else if ((double) t < 51.2 / 15) {
         soc = fast_aa2(x) * kC.fast_scale;
-        power = (float) fma(fma(fma(fma(0.0002253, x, -0.03572), x, 2.016), x, -48.76), x, 457.7);
+        power = fast_a2(x);
     } else {
         soc = 100.0f;
         power = 0.0f;
@@ -340,7 +352,7 @@ __device__ __forceinline__ void fast_step(float t, float &soc, float &power) {
 __device__ __forceinline__ float fast_t2p(float t) {
     double x = (double) (t * 15.0f), td = (double) t;
     if (td >= 0.0 && td < 28.7 / 15) return (float) (0.7194 * chub_exp(0.053 * x) + 47.78);
-    if (td >= 0.0 && td < 51.2 / 15) return (float) fma(fma(fma(fma(0.0002253, x, -0.03572), x, 2.016), x, -48.76), x, 457.7);
+    if (td >= 0.0 && td < 51.2 / 15) return fast_a2(x);
     return 0.0f;
 }
 

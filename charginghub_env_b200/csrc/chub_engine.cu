@@ -5,6 +5,9 @@
 // the reference computes at run time), launches the step / reset kernels stream-ordered, and
 // exposes outputs as raw device pointers and DLPack tensors.  No CPU stepping path exists here:
 // if CUDA is unavailable every entry point fails with CHUB_ERR_CUDA.
+#include <dlfcn.h>
+#include <nvtx3/nvToolsExt.h>
+
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -30,6 +33,7 @@ static int fail(int code, const std::string &msg) {
 
 #define CHUB_HOST_INLINE_PACK 4096   // up to this many hubs the calling thread packs the rows itself: waking a pool costs more
 #define CHUB_HOST_KSTREAMS 4   // ranges are independent: their kernels may share the SMs
+#define CHUB_TIMER_RING 128
 struct chub_engine {
     chub_config cfg;
     int H = 0, Hpad = 0, S0 = 0, S1 = 0;
@@ -41,7 +45,7 @@ struct chub_engine {
     ChubParams P;
     // device
     uint4 *pile = nullptr; float *arrive = nullptr; uint4 *hubA = nullptr; double *store = nullptr;
-    uint2 *keys = nullptr, *occ = nullptr; int *cls = nullptr; float4 *stats = nullptr, *last_stats = nullptr;
+    uint2 *keys = nullptr, *occ = nullptr; int *cls = nullptr; double2 *stats = nullptr; float4 *last_stats = nullptr;
     uint32_t *err = nullptr; float *qsoc = nullptr; ChubClass *d_classes = nullptr; double *d_el = nullptr;
     uint16_t *lut = nullptr; float *s2t_lut = nullptr; double *pv = nullptr, *wd = nullptr, *price_tr = nullptr;
     float *obs = nullptr, *reward = nullptr; uint8_t *done = nullptr; double *diag = nullptr; float *st_power = nullptr;
@@ -69,7 +73,26 @@ struct chub_engine {
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t graph_exec = nullptr;
     int graph_steps = 0;
+    // the one collective of the path (chub_gather_stats / chub_reduce_stats): snapshot + communication stream
+    float4 *stats_stage = nullptr;
+    double *stats_partial = nullptr, *stats_sums = nullptr;
+    cudaStream_t comm_stream = nullptr;
+    cudaEvent_t comm_ready = nullptr, comm_done = nullptr;
+    bool comm_pending = false;
+    // per-launch timers (chub_set_timing / chub_step_times): CUDA events around the most recent step launches
+    bool timing = false;
+    cudaEvent_t time_ev[2 * CHUB_TIMER_RING] = {};
+    long long timed = 0;
 };
+struct NvtxRange {   // shows up in nsys / ncu --nvtx; costs a pointer test when no tool is attached
+    explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
+static void drop_graph(chub_engine *e) {   // a captured rollout bakes device pointers and launch parameters
+    if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
+    if (e->graph) { cudaGraphDestroy(e->graph); e->graph = nullptr; }
+    e->graph_steps = 0;
+}
 
 extern "C" const char *chub_last_error(void) { return g_err.c_str(); }
 extern "C" int chub_version(void) { return 100; }
@@ -85,9 +108,15 @@ static void engine_free(chub_engine *e) {
         if (st) cudaStreamDestroy(st);
     for (cudaEvent_t ev : e->host_events)
         if (ev) cudaEventDestroy(ev);
+    for (cudaEvent_t ev : e->time_ev)
+        if (ev) cudaEventDestroy(ev);
+    if (e->comm_stream) cudaStreamDestroy(e->comm_stream);
+    if (e->comm_ready) cudaEventDestroy(e->comm_ready);
+    if (e->comm_done) cudaEventDestroy(e->comm_done);
     void *ptrs[] = {e->pile, e->arrive, e->hubA, e->store, e->keys, e->occ, e->cls, e->stats, e->last_stats, e->err, e->qsoc,
                     e->d_classes, e->d_el, e->lut, e->s2t_lut, e->pv, e->wd, e->price_tr, e->obs, e->reward, e->done, e->diag,
-                    e->st_power, e->step_index, e->actions_stage, e->exo_d, e->exo_i, e->pv_days, e->wd_days, e->act_bits, e->final_soc, e->packed_stage, e->report_dev};
+                    e->st_power, e->step_index, e->actions_stage, e->exo_d, e->exo_i, e->pv_days, e->wd_days, e->act_bits, e->final_soc, e->packed_stage, e->report_dev,
+                    e->stats_stage, e->stats_partial, e->stats_sums};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     delete e;
@@ -123,7 +152,7 @@ extern "C" int chub_create(const chub_config *cfg, chub_engine **out) {
     cudaError_t r = cudaSuccess;
     auto A = [&](cudaError_t x) { if (r == cudaSuccess) r = x; };
     A(dalloc(&e->hubA, Hp)); A(dalloc(&e->store, Hp)); A(dalloc(&e->keys, Hp)); A(dalloc(&e->occ, Hp));
-    A(dalloc(&e->stats, Hp)); A(dalloc(&e->last_stats, Hp)); A(dalloc(&e->err, Hp)); A(dalloc(&e->final_soc, Hp));
+    A(dalloc(&e->stats, 2 * Hp)); A(dalloc(&e->last_stats, Hp)); A(dalloc(&e->err, Hp)); A(dalloc(&e->final_soc, Hp));
     A(dalloc(&e->qsoc, Hp * CHUB_FCEV_QCAP)); A(dalloc(&e->lut, (size_t) 96 * 1000)); A(dalloc(&e->s2t_lut, (size_t) 4000));
     A(dalloc(&e->obs, Hp * CHUB_OBS_DIM)); A(dalloc(&e->reward, Hp)); A(dalloc(&e->done, Hp));
     A(dalloc(&e->step_index, 1));
@@ -214,6 +243,8 @@ extern "C" int chub_set_hub_classes(chub_engine *e, const chub_hub_class *classe
     if (!e || !classes || n_classes < 1) return fail(CHUB_ERR_ARG, "chub_set_hub_classes: bad argument");
     if (n_classes > 1 && !hub_class) return fail(CHUB_ERR_ARG, "chub_set_hub_classes: hub_class required");
     CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    drop_graph(e);   // the pile arrays are reallocated below
     int S0 = 0, S1 = 0;
     e->classes.assign(n_classes, ChubClass());
     e->el_tables.assign((size_t) n_classes * CHUB_EL_TABLE, 0.0);
@@ -359,6 +390,7 @@ extern "C" int chub_set_traces(chub_engine *e, const double *pv, const double *w
     if (!e || !pv || !wd || !price || length < 1) return fail(CHUB_ERR_ARG, "chub_set_traces: bad argument");
     CK(cudaSetDevice(e->cfg.device));
     CK(cudaDeviceSynchronize());
+    drop_graph(e);   // a captured rollout holds the old trace pointers
     for (double **p : {&e->pv, &e->wd, &e->price_tr})
         if (*p) { cudaFree(*p); *p = nullptr; }
     const size_t row = per_hub ? (size_t) e->Hpad : 1;
@@ -386,6 +418,7 @@ extern "C" int chub_set_exogenous_generator(chub_engine *e, const double *pv_day
         return fail(CHUB_ERR_ARG, "chub_set_exogenous_generator: bad argument (1..1023 days per table)");
     CK(cudaSetDevice(e->cfg.device));
     CK(cudaDeviceSynchronize());
+    drop_graph(e);
     for (double **p : {&e->pv_days, &e->wd_days, &e->exo_d})
         if (*p) { cudaFree(*p); *p = nullptr; }
     if (e->exo_i) { cudaFree(e->exo_i); e->exo_i = nullptr; }
@@ -490,6 +523,31 @@ static int fill_params(chub_engine *e, ChubParams &P) {
     return CHUB_OK;
 }
 
+// One step launch (+ the tick that advances the trace index), with the optional per-launch timer around the step kernel.
+static int run_step(chub_engine *e, const ChubParams &P, cudaStream_t s) {
+    NvtxRange range("chub_step");
+    int slot = -1;
+    if (e->timing) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        cudaStreamIsCapturing(s, &cs);
+        if (cs == cudaStreamCaptureStatusNone) {   // events inside a capture carry no time
+            slot = (int) (e->timed % CHUB_TIMER_RING);
+            for (int k = 0; k < 2; ++k)
+                if (!e->time_ev[2 * slot + k]) CK(cudaEventCreate(&e->time_ev[2 * slot + k]));
+            CK(cudaEventRecord(e->time_ev[2 * slot], s));
+        }
+    }
+    CK(chub_launch_step(P, s));
+    if (slot >= 0) {
+        CK(cudaEventRecord(e->time_ev[2 * slot + 1], s));
+        e->timed += 1;
+    }
+    chub_launch_tick(e->step_index, 1, s);
+    CK(cudaGetLastError());
+    e->launches += 1;
+    return CHUB_OK;
+}
+
 extern "C" int chub_reset(chub_engine *e, const uint8_t *mask_dev, int64_t step_index, void *stream) {
     if (!e) return fail(CHUB_ERR_ARG, "chub_reset: null engine");
     CK(cudaSetDevice(e->cfg.device));
@@ -503,6 +561,7 @@ extern "C" int chub_reset(chub_engine *e, const uint8_t *mask_dev, int64_t step_
         CK(cudaStreamSynchronize(s));  // v lives on this stack frame
     }
     P.reset_mask = mask_dev;
+    NvtxRange range("chub_reset");
     chub_launch_reset(P, s);
     CK(cudaGetLastError());
     return CHUB_OK;
@@ -516,11 +575,7 @@ extern "C" int chub_step(chub_engine *e, const float *actions_dev, void *stream)
     if (rc) return rc;
     P.actions = actions_dev;
     cudaStream_t s = (cudaStream_t) stream;
-    CK(chub_launch_step(P, s));
-    chub_launch_tick(e->step_index, 1, s);
-    CK(cudaGetLastError());
-    e->launches += 1;
-    return CHUB_OK;
+    return run_step(e, P, s);
 }
 
 extern "C" int chub_step_into(chub_engine *e, const float *actions_dev, float *obs_out_dev, float *reward_out_dev,
@@ -535,11 +590,7 @@ extern "C" int chub_step_into(chub_engine *e, const float *actions_dev, float *o
     if (reward_out_dev) P.reward = reward_out_dev;
     if (done_out_dev) P.done = done_out_dev;
     cudaStream_t s = (cudaStream_t) stream;
-    CK(chub_launch_step(P, s));
-    chub_launch_tick(e->step_index, 1, s);
-    CK(cudaGetLastError());
-    e->launches += 1;
-    return CHUB_OK;
+    return run_step(e, P, s);
 }
 
 // Scalar-load step: rows [load0 kW, load1 kW, a[-2], a[-1]]; the dispatch kernel turns the two station power targets
@@ -558,11 +609,7 @@ extern "C" int chub_step_loads(chub_engine *e, const float *loads_dev, void *str
     cudaStream_t s = (cudaStream_t) stream;
     chub_launch_dispatch(P, e->act_bits, s);
     P.act_bits = e->act_bits;
-    CK(chub_launch_step(P, s));
-    chub_launch_tick(e->step_index, 1, s);
-    CK(cudaGetLastError());
-    e->launches += 1;
-    return CHUB_OK;
+    return run_step(e, P, s);
 }
 
 extern "C" int chub_situation_width(chub_engine *e, int32_t *s0, int32_t *s1) {
@@ -594,11 +641,7 @@ extern "C" int chub_step_packed(chub_engine *e, const void *packed_dev, void *st
     if (rc) return rc;
     P.act_packed = (const uint4 *) packed_dev;
     cudaStream_t s = (cudaStream_t) stream;
-    CK(chub_launch_step(P, s));
-    chub_launch_tick(e->step_index, 1, s);
-    CK(cudaGetLastError());
-    e->launches += 1;
-    return CHUB_OK;
+    return run_step(e, P, s);
 }
 
 // Threads that pack the caller's rows inside chub_step_host; 0 sends the float rows over the bus as they are.
@@ -658,6 +701,7 @@ extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *
     if (rc) return rc;
     rc = host_pipeline_setup(e);
     if (rc) return rc;
+    NvtxRange range("chub_step_host");
     const bool packed = e->host_threads > 0;
     if (packed) P.act_packed = e->packed_stage;
     else P.actions = e->actions_stage;
@@ -743,8 +787,7 @@ extern "C" int chub_rollout_capture(chub_engine *e, const float *actions_dev, in
     int rc = fill_params(e, P);
     if (rc) return rc;
     P.actions = actions_dev;
-    if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
-    if (e->graph) { cudaGraphDestroy(e->graph); e->graph = nullptr; }
+    drop_graph(e);
     cudaStream_t s = (cudaStream_t) stream;
     cudaStream_t cap = s;
     bool own = false;
@@ -769,6 +812,7 @@ extern "C" int chub_rollout_capture(chub_engine *e, const float *actions_dev, in
 extern "C" int chub_rollout(chub_engine *e, void *stream) {
     if (!e || !e->graph_exec) return fail(CHUB_ERR_STATE, "chub_rollout: capture a rollout first");
     CK(cudaSetDevice(e->cfg.device));
+    NvtxRange range("chub_rollout");
     CK(cudaGraphLaunch(e->graph_exec, (cudaStream_t) stream));
     e->launches += e->graph_steps;
     return CHUB_OK;
@@ -802,7 +846,7 @@ static bool buf_info(chub_engine *e, int which, BufInfo &b) {
         case CHUB_BUF_OBS: b = {e->obs, H * CHUB_OBS_DIM * 4, 2, {H, CHUB_OBS_DIM}, 2, 32}; return true;
         case CHUB_BUF_REWARD: b = {e->reward, H * 4, 1, {H, 1}, 2, 32}; return true;
         case CHUB_BUF_DONE: b = {e->done, H, 1, {H, 1}, 1, 8}; return true;
-        case CHUB_BUF_STATS: b = {e->stats, H * 16, 2, {H, 4}, 2, 32}; return true;
+        case CHUB_BUF_STATS: b = {e->stats, H * 32, 2, {H, 4}, 2, 64}; return true;
         case CHUB_BUF_LAST_STATS: b = {e->last_stats, H * 16, 2, {H, 4}, 2, 32}; return true;
         case CHUB_BUF_ERROR: b = {e->err, H * 4, 1, {H, 1}, 1, 32}; return true;
         case CHUB_BUF_FINAL_SOC: b = {e->final_soc, H * 4, 1, {H, 1}, 2, 32}; return true;
@@ -972,31 +1016,53 @@ extern "C" int chub_get_field(chub_engine *e, int32_t field, void *host_out) {
     return CHUB_OK;
 }
 
-// ---- checkpoint blob: every mutable state array, in a fixed order ----
+// ---- checkpoint blob: a header, then every mutable state array and the outputs of the last step, in a fixed order ----
+struct StateHeader {
+    uint32_t magic, version;
+    int32_t H, Hpad, S0, S1, n_classes, exo, diagnostics, reserved;
+    int64_t bytes;       // of the whole blob, header included
+    int64_t pad[2];
+};
+#define CHUB_STATE_MAGIC 0x42554843u   // "CHUB"
+#define CHUB_STATE_VERSION 2u
 struct Seg { void *p; size_t bytes; };
 static std::vector<Seg> state_segments(chub_engine *e) {
     const size_t Hp = e->Hpad, slots = (size_t) (e->S0 + e->S1) * Hp;
     std::vector<Seg> v = {{e->pile, slots * sizeof(uint4)}, {e->arrive, slots * sizeof(float)}, {e->hubA, Hp * sizeof(uint4)},
-            {e->store, Hp * sizeof(double)}, {e->keys, Hp * sizeof(uint2)}, {e->occ, Hp * sizeof(uint2)}, {e->stats, Hp * sizeof(float4)},
+            {e->store, Hp * sizeof(double)}, {e->keys, Hp * sizeof(uint2)}, {e->occ, Hp * sizeof(uint2)}, {e->stats, 2 * Hp * sizeof(double2)},
             {e->last_stats, Hp * sizeof(float4)}, {e->err, Hp * sizeof(uint32_t)},
-            {e->qsoc, Hp * CHUB_FCEV_QCAP * sizeof(float)}, {e->step_index, sizeof(long long)}};
+            {e->qsoc, Hp * CHUB_FCEV_QCAP * sizeof(float)}, {e->step_index, sizeof(long long)},
+            // what the last step returned: a trainer that resumes mid-episode feeds obs to its policy before it steps again
+            {e->obs, Hp * CHUB_OBS_DIM * sizeof(float)}, {e->reward, Hp * sizeof(float)}, {e->done, Hp}, {e->final_soc, Hp * sizeof(float)}};
     if (e->exo_d) {   // generator state travels with the checkpoint
         v.push_back({e->exo_d, 7 * Hp * sizeof(double)});
         v.push_back({e->exo_i, Hp * sizeof(uint2)});
     }
     return v;
 }
+static StateHeader state_header(chub_engine *e) {
+    StateHeader h;
+    memset(&h, 0, sizeof h);
+    h.magic = CHUB_STATE_MAGIC; h.version = CHUB_STATE_VERSION;
+    h.H = e->H; h.Hpad = e->Hpad; h.S0 = e->S0; h.S1 = e->S1; h.n_classes = (int32_t) e->classes.size();
+    h.exo = e->exo_d ? 1 : 0; h.diagnostics = e->cfg.diagnostics;
+    size_t n = sizeof(StateHeader);
+    for (const Seg &s : state_segments(e)) n += s.bytes;
+    h.bytes = (int64_t) n;
+    return h;
+}
 extern "C" int64_t chub_state_bytes(chub_engine *e) {
     if (!e || !e->have_classes) return -1;
-    size_t n = 0;
-    for (const Seg &s : state_segments(e)) n += s.bytes;
-    return (int64_t) n;
+    return state_header(e).bytes;
 }
 extern "C" int chub_get_state(chub_engine *e, void *host_blob) {
     if (!e || !host_blob || !e->have_classes) return fail(CHUB_ERR_ARG, "chub_get_state: bad argument");
     CK(cudaSetDevice(e->cfg.device));
     CK(cudaDeviceSynchronize());
     char *o = (char *) host_blob;
+    const StateHeader h = state_header(e);
+    memcpy(o, &h, sizeof h);
+    o += sizeof h;
     for (const Seg &s : state_segments(e)) {
         CK(cudaMemcpy(o, s.p, s.bytes, cudaMemcpyDeviceToHost));
         o += s.bytes;
@@ -1008,11 +1074,171 @@ extern "C" int chub_set_state(chub_engine *e, const void *host_blob) {
     CK(cudaSetDevice(e->cfg.device));
     CK(cudaDeviceSynchronize());
     const char *o = (const char *) host_blob;
+    StateHeader got;
+    memcpy(&got, o, sizeof got);
+    const StateHeader want = state_header(e);
+    if (got.magic != CHUB_STATE_MAGIC) return fail(CHUB_ERR_ARG, "chub_set_state: not a chub state blob");
+    if (got.version != CHUB_STATE_VERSION) return fail(CHUB_ERR_ARG, "chub_set_state: blob written by another layout version");
+    if (got.H != want.H || got.Hpad != want.Hpad || got.S0 != want.S0 || got.S1 != want.S1 || got.n_classes != want.n_classes ||
+        got.exo != want.exo || got.bytes != want.bytes)
+        return fail(CHUB_ERR_ARG, "chub_set_state: blob belongs to an engine of another shape (hubs, piles, classes or generator)");
+    o += sizeof got;
     for (const Seg &s : state_segments(e)) {
         CK(cudaMemcpy(s.p, o, s.bytes, cudaMemcpyHostToDevice));
         o += s.bytes;
     }
     e->have_seed = true;
+    return CHUB_OK;
+}
+
+// ---- per-launch timers ----
+extern "C" int chub_set_timing(chub_engine *e, int32_t on) {
+    if (!e) return fail(CHUB_ERR_ARG, "chub_set_timing: null engine");
+    e->timing = on != 0;
+    e->timed = 0;
+    return CHUB_OK;
+}
+extern "C" int chub_step_times(chub_engine *e, float *ms_out, int32_t max_n, int32_t *n_out) {
+    if (!e || !ms_out || !n_out || max_n < 0) return fail(CHUB_ERR_ARG, "chub_step_times: bad argument");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    const long long have = e->timed < CHUB_TIMER_RING ? e->timed : CHUB_TIMER_RING;
+    const int n = (int) (have < max_n ? have : max_n);
+    for (int j = 0; j < n; ++j) {   // oldest first
+        const int slot = (int) ((e->timed - n + j) % CHUB_TIMER_RING);
+        CK(cudaEventElapsedTime(&ms_out[j], e->time_ev[2 * slot], e->time_ev[2 * slot + 1]));
+    }
+    *n_out = n;
+    return CHUB_OK;
+}
+
+// ---- curve sweep (parity instrument) ----
+extern "C" int chub_debug_curve(chub_engine *e, int32_t which, uint32_t first_bits, int64_t n, float *out_dev, void *stream) {
+    if (!e || !out_dev || n < 1 || which < 0 || which > 15) return fail(CHUB_ERR_ARG, "chub_debug_curve: bad argument");
+    if (!e->have_tables) return fail(CHUB_ERR_STATE, "chub_debug_curve: call chub_set_tables first (curve constants)");
+    CK(cudaSetDevice(e->cfg.device));
+    chub_launch_curve_sweep(which, first_bits, (long long) n, out_dev, (cudaStream_t) stream);
+    CK(cudaGetLastError());
+    return CHUB_OK;
+}
+
+// ---- the one collective of the path: episode statistics, once per rollout (the quantities mirror
+// evcssp_manager.py:259-297).  NCCL is resolved at run time from the library the caller's communicator came from
+// (libnccl.so.2 already in the process, else the system one), so libchub.so itself links no NCCL. ----
+typedef struct ncclComm *chub_nccl_comm;
+struct NcclApi {
+    int (*GroupStart)();
+    int (*GroupEnd)();
+    int (*Send)(const void *, size_t, int, int, chub_nccl_comm, cudaStream_t);
+    int (*Recv)(void *, size_t, int, int, chub_nccl_comm, cudaStream_t);
+    int (*AllReduce)(const void *, void *, size_t, int, int, chub_nccl_comm, cudaStream_t);
+    int (*CommCount)(chub_nccl_comm, int *);
+    int (*CommUserRank)(chub_nccl_comm, int *);
+    const char *(*GetErrorString)(int);
+    bool ok = false;
+};
+#define CHUB_NCCL_FLOAT32 7   // ncclFloat32 (nccl.h ncclDataType_t)
+#define CHUB_NCCL_FLOAT64 8   // ncclFloat64
+#define CHUB_NCCL_SUM 0       // ncclSum
+static NcclApi g_nccl;
+static int nccl_load() {
+    if (g_nccl.ok) return CHUB_OK;
+    void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);   // the copy the communicator's owner (e.g. torch) loaded
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW);
+    if (!h) return fail(CHUB_ERR_UNSUPPORTED, std::string("NCCL not available: ") + dlerror());
+    bool all = true;
+    auto sym = [&](const char *name) { void *p = dlsym(h, name); if (!p) all = false; return p; };
+    g_nccl.GroupStart = (int (*)()) sym("ncclGroupStart");
+    g_nccl.GroupEnd = (int (*)()) sym("ncclGroupEnd");
+    g_nccl.Send = (int (*)(const void *, size_t, int, int, chub_nccl_comm, cudaStream_t)) sym("ncclSend");
+    g_nccl.Recv = (int (*)(void *, size_t, int, int, chub_nccl_comm, cudaStream_t)) sym("ncclRecv");
+    g_nccl.AllReduce = (int (*)(const void *, void *, size_t, int, int, chub_nccl_comm, cudaStream_t)) sym("ncclAllReduce");
+    g_nccl.CommCount = (int (*)(chub_nccl_comm, int *)) sym("ncclCommCount");
+    g_nccl.CommUserRank = (int (*)(chub_nccl_comm, int *)) sym("ncclCommUserRank");
+    g_nccl.GetErrorString = (const char *(*)(int)) sym("ncclGetErrorString");
+    if (!all) return fail(CHUB_ERR_UNSUPPORTED, "NCCL library lacks a needed symbol");
+    g_nccl.ok = true;
+    return CHUB_OK;
+}
+#define NK(call)                                                                                   \
+    do {                                                                                           \
+        int r_ = (call);                                                                           \
+        if (r_ != 0) return fail(CHUB_ERR_CUDA, std::string(#call) + ": " + g_nccl.GetErrorString(r_)); \
+    } while (0)
+
+static int comm_setup(chub_engine *e) {
+    if (!e->comm_stream) {
+        CK(cudaStreamCreateWithFlags(&e->comm_stream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&e->comm_ready, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&e->comm_done, cudaEventDisableTiming));
+    }
+    if (!e->stats_stage) CK(dalloc(&e->stats_stage, (size_t) e->Hpad));
+    return CHUB_OK;
+}
+
+extern "C" int chub_gather_stats(chub_engine *e, void *nccl_comm, int32_t root, const int32_t *hubs_per_rank, float *recv_dev,
+                                 void *stream) {
+    if (!e || !nccl_comm) return fail(CHUB_ERR_ARG, "chub_gather_stats: null argument");
+    CK(cudaSetDevice(e->cfg.device));
+    int rc = nccl_load();
+    if (rc) return rc;
+    rc = comm_setup(e);
+    if (rc) return rc;
+    NvtxRange range("chub_gather_stats");
+    chub_nccl_comm comm = (chub_nccl_comm) nccl_comm;
+    int nranks = 0, rank = 0;
+    NK(g_nccl.CommCount(comm, &nranks));
+    NK(g_nccl.CommUserRank(comm, &rank));
+    if (root < 0 || root >= nranks) return fail(CHUB_ERR_ARG, "chub_gather_stats: root outside the communicator");
+    if (rank == root && !recv_dev) return fail(CHUB_ERR_ARG, "chub_gather_stats: the root needs a receive buffer");
+    if (hubs_per_rank && hubs_per_rank[rank] != e->H) return fail(CHUB_ERR_ARG, "chub_gather_stats: hubs_per_rank disagrees with this engine");
+    cudaStream_t s = (cudaStream_t) stream;
+    if (e->comm_pending) CK(cudaStreamWaitEvent(s, e->comm_done, 0));   // the previous gather still reads the snapshot
+    // snapshot on the caller's stream (a few microseconds), transfer on the engine's communication stream: the steps
+    // the caller queues next overlap the transfer and may finish episodes without disturbing what is being sent
+    CK(cudaMemcpyAsync(e->stats_stage, e->last_stats, sizeof(float4) * (size_t) e->H, cudaMemcpyDeviceToDevice, s));
+    CK(cudaEventRecord(e->comm_ready, s));
+    CK(cudaStreamWaitEvent(e->comm_stream, e->comm_ready, 0));
+    NK(g_nccl.GroupStart());
+    if (rank == root) {
+        size_t at = 0;
+        for (int r = 0; r < nranks; ++r) {
+            const size_t n = (size_t) (hubs_per_rank ? hubs_per_rank[r] : e->H) * 4;
+            if (r == rank) CK(cudaMemcpyAsync(recv_dev + at, e->stats_stage, n * sizeof(float), cudaMemcpyDeviceToDevice, e->comm_stream));
+            else NK(g_nccl.Recv(recv_dev + at, n, CHUB_NCCL_FLOAT32, r, comm, e->comm_stream));
+            at += n;
+        }
+    } else {
+        NK(g_nccl.Send(e->stats_stage, (size_t) e->H * 4, CHUB_NCCL_FLOAT32, root, comm, e->comm_stream));
+    }
+    NK(g_nccl.GroupEnd());
+    CK(cudaEventRecord(e->comm_done, e->comm_stream));
+    e->comm_pending = true;
+    return CHUB_OK;
+}
+
+extern "C" int chub_gather_wait(chub_engine *e, void *stream) {
+    if (!e) return fail(CHUB_ERR_ARG, "chub_gather_wait: null engine");
+    if (!e->comm_pending) return CHUB_OK;
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaStreamWaitEvent((cudaStream_t) stream, e->comm_done, 0));
+    e->comm_pending = false;
+    return CHUB_OK;
+}
+
+extern "C" int chub_reduce_stats(chub_engine *e, void *nccl_comm, double *sums_dev, void *stream) {
+    if (!e || !sums_dev) return fail(CHUB_ERR_ARG, "chub_reduce_stats: null argument");
+    CK(cudaSetDevice(e->cfg.device));
+    if (!e->stats_partial) CK(dalloc(&e->stats_partial, (size_t) 4 * CHUB_STATS_BLOCKS));
+    NvtxRange range("chub_reduce_stats");
+    cudaStream_t s = (cudaStream_t) stream;
+    chub_launch_stats_sums(e->last_stats, e->H, e->stats_partial, sums_dev, s);
+    CK(cudaGetLastError());
+    if (nccl_comm) {
+        int rc = nccl_load();
+        if (rc) return rc;
+        NK(g_nccl.AllReduce(sums_dev, sums_dev, 4, CHUB_NCCL_FLOAT64, CHUB_NCCL_SUM, (chub_nccl_comm) nccl_comm, s));
+    }
     return CHUB_OK;
 }
 

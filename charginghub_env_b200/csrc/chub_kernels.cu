@@ -524,8 +524,19 @@ __device__ __forceinline__ void hub_store(const ChubParams &P, int h, const HubV
     if (v.err) P.err[h] |= v.err;
 }
 
-__device__ __forceinline__ void trace_at(const ChubParams &P, int h, long long k, double &pv, double &wd, double &pr) {
-    size_t i = (size_t) (k % (long long) P.trace_len);
+// Exogenous traces are addressed by (the hub's day, the hub's time of day): slot = 96 * floor((k - t) / 96) + t', where k
+// is the absolute step index, t the hub's time slot when step k starts and t' = t (state being left) or t + 1 (state
+// being entered; 96 = slot 0 of the next day).  For hubs that run in lock step with the step index (reset at a multiple
+// of 96, every test against the reference) this is simply k or k + 1.  A hub that was reset in the middle of a day
+// (masked reset, TimeLimit truncation, a de-phased batch) keeps reading the slot that belongs to ITS time of day, so PV
+// follows its sun and the price its tariff table (evcssp_manager.py:344-361 shows table[t - 1] at time t).
+__device__ __forceinline__ void trace_at(const ChubParams &P, int h, long long k, int t, int t_read, double &pv, double &wd,
+                                         double &pr) {
+    const long long d = k - (long long) t;
+    const long long day = d >= 0 ? d / CHUB_DAY : -((CHUB_DAY - 1 - d) / CHUB_DAY);
+    long long m = (day * CHUB_DAY + (long long) t_read) % (long long) P.trace_len;
+    if (m < 0) m += P.trace_len;
+    size_t i = (size_t) m;
     if (P.trace_per_hub) i = i * (size_t) P.Hpad + h;
     pv = __ldg(&P.pv[i]); wd = __ldg(&P.wd[i]); pr = __ldg(&P.price_tr[i]);
 }
@@ -633,7 +644,8 @@ __device__ __noinline__ void hub_reset_full(const ChubParams &P, int h, long lon
     v.occ0 = s0.occ; v.occ1 = s1.occ;
     v.qn = 0; v.fline = 0; v.farr = 0;
     v.store = c.init_mass;
-    P.stats[h] = make_float4(0.f, 0.f, 0.f, 0.f);
+    P.stats[2 * h] = make_double2(0.0, 0.0);
+    P.stats[2 * h + 1] = make_double2(0.0, 0.0);
     double pv, wd, pr;
     if (P.exo_mode) {
         ExoState g;
@@ -641,7 +653,7 @@ __device__ __noinline__ void hub_reset_full(const ChubParams &P, int h, long lon
         exo_reset(P, g, v.rng.k0, v.rng.k1, pv, wd, pr);
         exo_store(P, h, g, pv, wd, pr);
     } else {
-        trace_at(P, h, k_obs, pv, wd, pr);
+        trace_at(P, h, k_obs, 0, 0, pv, wd, pr);
     }
     write_obs(P, h, c, 0, s0, s1, c.init_soc, pv, wd, pr);
     if (P.diag) {
@@ -816,7 +828,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     const long long k = *P.step_index + P.step_offset;
     double pv_t, wd_t, pr_t;
     if (P.exo_mode) exo_current(P, h, pv_t, wd_t, pr_t);
-    else trace_at(P, h, k, pv_t, wd_t, pr_t);
+    else trace_at(P, h, k, v.t, v.t, pv_t, wd_t, pr_t);
     const float a_m2 = S->am[0][lane_], a_m1 = S->am[1][lane_];
     v.line0 = s0.line; v.line1 = s1.line;
     v.flow0 = s0.flow; v.flow1 = s1.flow;
@@ -929,6 +941,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     const double income = inc_hys + inc_evs + serve + hy_cost;
     const double reward = DIVC(inc_hys + inc_evs + serve + hy_cost + 1.0 * hy_loss + nm_loss, 50.0);
     const bool done = v.t + 1 >= CHUB_DAY;
+    const int t_left = v.t;
     v.t = (v.t + 1) % CHUB_DAY;
 
     if (P.diag) {  // fp64 columns for the parity tests
@@ -944,17 +957,20 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     }
 
     // ---- episode statistics (evcssp_manager.py:259-269, CHS.hpp:916-921) ----
-    float4 st = P.stats[h];
-    st.x += (float) reward;
-    st.y += (float) income;
-    st.z += (float) (l0 + l1 + h2_grid);
-    st.w += (float) (s0.incomplete + s1.incomplete);
+    // accumulated in fp64 like the reference's Python floats (acumulate_reward, cumulated_income, cumulated_draw_ele)
+    double2 sa = P.stats[2 * h], sb = P.stats[2 * h + 1];
+    sa.x += reward;
+    sa.y += income;
+    sb.x += l0 + l1 + h2_grid;
+    sb.y += (double) (s0.incomplete + s1.incomplete);
     if (done) {
         P.final_soc[h] = (float) store_soc;
-        P.last_stats[h] = st;
-        st = make_float4(0.f, 0.f, 0.f, 0.f);
+        P.last_stats[h] = make_float4((float) sa.x, (float) sa.y, (float) sb.x, (float) sb.y);
+        sa = make_double2(0.0, 0.0);
+        sb = make_double2(0.0, 0.0);
     }
-    P.stats[h] = st;
+    P.stats[2 * h] = sa;
+    P.stats[2 * h + 1] = sb;
     P.reward[h] = (float) reward;
     P.done[h] = done ? 1 : 0;
     hub_store(P, h, v);
@@ -965,7 +981,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
         exo_values(P, g, v.rng.k0, v.rng.k1, v.t, kC.price[(v.t + CHUB_DAY - 1) % CHUB_DAY], pv_n, wd_n, pr_n);
         exo_store(P, h, g, pv_n, wd_n, pr_n);
     } else if (!(done && P.auto_reset)) {
-        trace_at(P, h, k + 1, pv_n, wd_n, pr_n);
+        trace_at(P, h, k, t_left, t_left + 1, pv_n, wd_n, pr_n);
     }
     if (done && P.auto_reset) {  // fused auto-reset: the returned obs is the first one of the next episode
         hub_reset_full(P, h, k + 1);
@@ -979,8 +995,17 @@ __global__ void __launch_bounds__(128) chub_reset_kernel(const __grid_constant__
     const int h = blockIdx.x * blockDim.x + threadIdx.x;
     if (h >= P.H) return;
     if (P.reset_mask && !P.reset_mask[h]) return;
-    P.reward[h] = 0.0f;
-    P.done[h] = 0;
+    if (P.reset_mask) {
+        // A masked reset cuts episodes short (TimeLimit truncation): what the last step returned -- reward, done -- stays
+        // as it is, and the statistics of the episode that ends here become the "last finished episode" like at done.
+        const double2 sa = P.stats[2 * h], sb = P.stats[2 * h + 1];
+        P.last_stats[h] = make_float4((float) sa.x, (float) sa.y, (float) sb.x, (float) sb.y);
+        const ChubClass &c0 = P.classes[P.cls ? __ldg(&P.cls[h]) : 0];
+        P.final_soc[h] = (float) chub_div_const(P.store[h], c0.cap_mass, c0.r_cap_mass);
+    } else {
+        P.reward[h] = 0.0f;
+        P.done[h] = 0;
+    }
     if (P.diag) {
         const int ci = P.cls ? __ldg(&P.cls[h]) : 0;
         const size_t s = (size_t) P.Hpad;
@@ -1195,6 +1220,73 @@ __global__ void chub_report_kernel(const __grid_constant__ ChubParams P, int h, 
     if (k < CHUB_REPORT_LEN) out[k] = v;
 }
 void chub_launch_report(const ChubParams &p, int h, double *out, cudaStream_t s) { chub_report_kernel<<<1, 32, 0, s>>>(p, h, out); }
+
+// ---- curve sweep (parity instrument, tests/test_gpu_curves.py): the charging curves exactly as the step kernel compiles
+// them, evaluated for `n` consecutive float32 bit patterns starting at `first_bits`, so that a test can walk EVERY
+// reachable argument and compare with glibc (CHS.hpp:495-588, 621-725).  which: 0 slow t2p (add_car), 1 slow car_step
+// soc, 2 slow s2t, 3 fast t2p, 4 fast car_step soc, 5 fast s2t, 6 slow car_step power, 7 fast car_step power;
+// +8 = the constant-power variants.
+// @region curve sweep
+template <int TYPE, int CP>
+__device__ __forceinline__ float sweep_eval(int f, float x) {
+    if (f == 0) return curve_t2p<TYPE, CP>(x);
+    if (f == 2) return curve_s2t<TYPE, CP>(x);
+    float soc, power;
+    if (curve_seg<TYPE, CP>(x) == 0) curve_step<TYPE, CP, 0>(x, soc, power);
+    else curve_step<TYPE, CP, 1>(x, soc, power);
+    return f == 1 ? soc : power;
+}
+__global__ void __launch_bounds__(256) chub_curve_kernel(int which, uint32_t first_bits, long long n, float *out) {
+    for (int i = threadIdx.x; i < CHUB_LOG_N * 4; i += 256)   // slow_step reads the log table from shared memory
+        reinterpret_cast<uint32_t *>(chub_smem)[i] = reinterpret_cast<const uint32_t *>(kLogTab)[i];
+    __syncthreads();
+    const int cp = which >> 3, w = which & 7;
+    const int type = (w == 0 || w == 1 || w == 2 || w == 6) ? CHUB_SLOW : CHUB_FAST;
+    const int f = (w == 0 || w == 3) ? 0 : (w == 2 || w == 5) ? 2 : (w == 1 || w == 4) ? 1 : 3;
+    for (long long i = (long long) blockIdx.x * 256 + threadIdx.x; i < n; i += (long long) gridDim.x * 256) {
+        const float x = __uint_as_float(first_bits + (uint32_t) i);
+        float y;
+        if (type == CHUB_SLOW) y = cp ? sweep_eval<CHUB_SLOW, 1>(f, x) : sweep_eval<CHUB_SLOW, 0>(f, x);
+        else y = cp ? sweep_eval<CHUB_FAST, 1>(f, x) : sweep_eval<CHUB_FAST, 0>(f, x);
+        out[i] = y;
+    }
+}
+void chub_launch_curve_sweep(int which, uint32_t first_bits, long long n, float *out, cudaStream_t s) {
+    long long blocks = (n + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    chub_curve_kernel<<<(unsigned) blocks, 256, CHUB_LOG_N * 16, s>>>(which, first_bits, n, out);
+}
+
+// Column sums of the episode statistics (the 32-byte variant of the gather): fixed grid and a fixed summation order,
+// so the result does not depend on scheduling.  fp64 accumulators over float4 rows.
+// @region stats sums
+__global__ void __launch_bounds__(256) chub_stats_partial_kernel(const float4 *stats, int H, double *partial) {
+    __shared__ double sh[4][256];
+    double a = 0.0, b = 0.0, c = 0.0, d = 0.0;
+    for (int h = blockIdx.x * 256 + threadIdx.x; h < H; h += CHUB_STATS_BLOCKS * 256) {
+        const float4 v = stats[h];
+        a += (double) v.x; b += (double) v.y; c += (double) v.z; d += (double) v.w;
+    }
+    sh[0][threadIdx.x] = a; sh[1][threadIdx.x] = b; sh[2][threadIdx.x] = c; sh[3][threadIdx.x] = d;
+    __syncthreads();
+    for (int w = 128; w > 0; w >>= 1) {
+        if ((int) threadIdx.x < w)
+            for (int k = 0; k < 4; ++k) sh[k][threadIdx.x] += sh[k][threadIdx.x + w];
+        __syncthreads();
+    }
+    if (threadIdx.x < 4) partial[threadIdx.x * CHUB_STATS_BLOCKS + blockIdx.x] = sh[threadIdx.x][0];
+}
+__global__ void chub_stats_final_kernel(const double *partial, double *sums) {
+    const int k = threadIdx.x;
+    if (k >= 4) return;
+    double a = 0.0;
+    for (int j = 0; j < CHUB_STATS_BLOCKS; ++j) a += partial[k * CHUB_STATS_BLOCKS + j];
+    sums[k] = a;
+}
+void chub_launch_stats_sums(const float4 *stats, int H, double *partial, double *sums, cudaStream_t s) {
+    chub_stats_partial_kernel<<<CHUB_STATS_BLOCKS, 256, 0, s>>>(stats, H, partial);
+    chub_stats_final_kernel<<<1, 32, 0, s>>>(partial, sums);
+}
 
 cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s) {
     int shape = p.block;

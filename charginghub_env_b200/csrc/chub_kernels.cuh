@@ -11,7 +11,8 @@
 //   store[h]                  double hydrogen store mass in grams
 //   keys[h]                   uint2  U-stream keys (read only)
 //   occ[h]                    uint2  occupancy masks of the two stations: the step only touches pile rows that hold a car
-//   stats[h], last_stats[h]   float4 {episode return, income, grid energy, incomplete departures}
+//   stats[2h], stats[2h+1]    double2 x 2 {episode return, income | grid energy, incomplete departures}, running (fp64 like
+//                             the reference's Python accumulators); last_stats[h] float4: the same at the last `done`
 //   qsoc[(j) * Hpad + h]      float  FCEV backlog arrival SOCs (cold; touched only when a backlog exists)
 // packed pile word : bits 0-5 stay_time, 6-11 already_stay_time, 12 car, 13 charge, 14 urgent,
 //                    15-19 ceil(needed_time) cache (0 = needed_time <= 0), 20-29 target draw u (target = u/999*20+80)
@@ -48,7 +49,8 @@ struct ChubParams {
     const uint2 *keys;
     uint2 *occ;                       // per hub: occupancy bit mask of station 0 / station 1 piles (bit i = a car on pile i)
     const int *cls;                   // NULL when n_classes == 1
-    float4 *stats, *last_stats;
+    double2 *stats;
+    float4 *last_stats;
     uint32_t *err;
     float *qsoc;
     const ChubClass *classes;
@@ -81,4 +83,7 @@ void chub_launch_report(const ChubParams &p, int h, double *out, cudaStream_t s)
 void chub_launch_dispatch(const ChubParams &p, unsigned long long *act_bits, cudaStream_t s);
 void chub_launch_s2t_lut(float *out, cudaStream_t s);
 void chub_launch_tick(long long *step_index, int n, cudaStream_t s);
+#define CHUB_STATS_BLOCKS 296
+void chub_launch_stats_sums(const float4 *stats, int H, double *partial, double *sums, cudaStream_t s);
+void chub_launch_curve_sweep(int which, uint32_t first_bits, long long n, float *out, cudaStream_t s);
 cudaError_t chub_upload_const(const ChubConst &c);

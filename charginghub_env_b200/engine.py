@@ -63,12 +63,18 @@ def _dptr(a):
     return a.ctypes.data_as(ctypes.c_void_p) if a is not None else None
 
 
-def _tensor_ptr(t):
-    """Device pointer of a torch CUDA tensor (float32/uint8, contiguous) or a raw int."""
+def _tensor_ptr(t, dtype=None, device=None):
+    """Device pointer of a contiguous torch CUDA tensor (or a raw int).  dtype: torch dtype or tuple of dtypes the
+    kernel may reinterpret the bytes as; device: the engine's CUDA ordinal -- the reference would have converted a
+    wrong-typed array, the kernel would silently read garbage, so both are checked here."""
     if isinstance(t, int):
         return ctypes.c_void_p(t)
     if not t.is_cuda or not t.is_contiguous():
         raise ValueError("expected a contiguous CUDA tensor")
+    if dtype is not None and t.dtype not in (dtype if isinstance(dtype, tuple) else (dtype,)):
+        raise ValueError("expected a %s tensor, got %s" % (dtype, t.dtype))
+    if device is not None and t.device.index != device:
+        raise ValueError("tensor lives on cuda:%s, the engine on cuda:%d" % (t.device.index, device))
     return ctypes.c_void_p(t.data_ptr())
 
 
@@ -180,6 +186,10 @@ class HubEngine(object):
         check(self.lib.chub_seed_explicit(self.h, _dptr(a[0]), _dptr(a[1]), _dptr(c), _dptr(a[2])))
 
     # ---- device path ----
+    def _f32(self, t):
+        import torch
+        return _tensor_ptr(t, torch.float32, self.device)
+
     def _stream(self, stream):
         if stream is not None:
             return ctypes.c_void_p(int(stream))
@@ -187,7 +197,10 @@ class HubEngine(object):
 
     def reset(self, mask=None, step_index=0, stream=None):
         """reset() of every hub (or of hubs whose mask byte is set; mask = CUDA uint8 tensor)."""
-        m = _tensor_ptr(mask) if mask is not None else None
+        import torch
+        if mask is not None and not isinstance(mask, int) and tuple(mask.shape) != (self.n_hubs,):
+            raise ValueError("mask must be [%d]" % self.n_hubs)
+        m = _tensor_ptr(mask, (torch.uint8, torch.bool), self.device) if mask is not None else None
         check(self.lib.chub_reset(self.h, m, int(step_index), self._stream(stream)))
         return self.tensor("obs")
 
@@ -195,7 +208,7 @@ class HubEngine(object):
         """step(action) of every hub.  actions: CUDA float32 [n_hubs, action_stride] in [-1, 1]."""
         if tuple(actions.shape) != (self.n_hubs, self.action_stride):
             raise ValueError("actions must be [%d, %d]" % (self.n_hubs, self.action_stride))  # evcssp_manager.py:148
-        check(self.lib.chub_step(self.h, _tensor_ptr(actions), self._stream(stream)))
+        check(self.lib.chub_step(self.h, self._f32(actions), self._stream(stream)))
         return self.tensor("obs"), self.tensor("reward"), self.tensor("done")
 
     def step_into(self, actions, obs_out=None, reward_out=None, done_out=None, stream=None):
@@ -208,16 +221,19 @@ class HubEngine(object):
                              (done_out, (self.n_hubs,), torch.uint8)):
             if t is not None and (tuple(t.shape) != shape or t.dtype != dt or not t.is_contiguous()):
                 raise ValueError("output tensors must be contiguous %r %s" % (shape, dt))
-        check(self.lib.chub_step_into(self.h, _tensor_ptr(actions), _tensor_ptr(obs_out) if obs_out is not None else None,
-                                      _tensor_ptr(reward_out) if reward_out is not None else None,
-                                      _tensor_ptr(done_out) if done_out is not None else None, self._stream(stream)))
+        check(self.lib.chub_step_into(self.h, self._f32(actions), self._f32(obs_out) if obs_out is not None else None,
+                                      self._f32(reward_out) if reward_out is not None else None,
+                                      _tensor_ptr(done_out, torch.uint8, self.device) if done_out is not None else None,
+                                      self._stream(stream)))
 
     def step_packed(self, packed, stream=None):
         """step(action) on packed records: CUDA int32/uint8 tensor of 16 bytes per hub, {on-bits lo, on-bits hi, a[-2],
         a[-1]} (include/chub.h chub_step_packed; pack_actions builds them from float rows on the host)."""
+        import torch
         if packed.numel() * packed.element_size() != 16 * self.n_hubs:
             raise ValueError("packed must hold 16 bytes per hub")
-        check(self.lib.chub_step_packed(self.h, _tensor_ptr(packed), self._stream(stream)))
+        check(self.lib.chub_step_packed(self.h, _tensor_ptr(packed, (torch.int32, torch.uint8, torch.float32), self.device),
+                                        self._stream(stream)))
         return self.tensor("obs"), self.tensor("reward"), self.tensor("done")
 
     def step_loads(self, loads, stream=None):
@@ -225,7 +241,7 @@ class HubEngine(object):
         [n_hubs, 4], row = [power target of station 0 in kW, of station 1, a[-2], a[-1]]."""
         if tuple(loads.shape) != (self.n_hubs, 4):
             raise ValueError("loads must be [%d, 4]" % self.n_hubs)
-        check(self.lib.chub_step_loads(self.h, _tensor_ptr(loads), self._stream(stream)))
+        check(self.lib.chub_step_loads(self.h, self._f32(loads), self._stream(stream)))
         return self.tensor("obs"), self.tensor("reward"), self.tensor("done")
 
     SITUATION_COLUMNS = ("car", "charge", "emergency", "assign", "power", "soc", "init_soc", "target_soc")
@@ -241,11 +257,13 @@ class HubEngine(object):
             out = torch.empty(shape, dtype=torch.float32, device="cuda:%d" % self.device)
         if tuple(out.shape) != shape or out.dtype != torch.float32:
             raise ValueError("out must be float32 %r" % (shape,))
-        check(self.lib.chub_situation(self.h, _tensor_ptr(out), self._stream(stream)))
+        check(self.lib.chub_situation(self.h, self._f32(out), self._stream(stream)))
         return {name: out[k] for k, name in enumerate(self.SITUATION_COLUMNS)}, (s0.value, s1.value)
 
     def capture_rollout(self, actions, n_steps, stream=None):
-        check(self.lib.chub_rollout_capture(self.h, _tensor_ptr(actions), int(n_steps), self._stream(stream)))
+        if tuple(actions.shape) != (self.n_hubs, self.action_stride):
+            raise ValueError("actions must be [%d, %d]" % (self.n_hubs, self.action_stride))
+        check(self.lib.chub_rollout_capture(self.h, self._f32(actions), int(n_steps), self._stream(stream)))
 
     def rollout(self, stream=None):
         check(self.lib.chub_rollout(self.h, self._stream(stream)))
@@ -352,6 +370,45 @@ class HubEngine(object):
         s, l, e = ctypes.c_int64(), ctypes.c_int64(), ctypes.c_uint32()
         check(self.lib.chub_counters(self.h, ctypes.byref(s), ctypes.byref(l), ctypes.byref(e)))
         return dict(step_index=s.value, launches=l.value, error_or=e.value)
+
+    # ---- the one collective; timers; parity instrument ----
+    def gather_stats(self, comm_ptr, root=0, hubs_per_rank=None, out=None, stream=None):
+        """Start the gather of the last-finished-episode statistics on rank `root` (include/chub.h chub_gather_stats).
+        comm_ptr: ncclComm_t as an int (torch: ProcessGroupNCCL._comm_ptr()).  out: float32 CUDA [sum of hubs, 4] on the
+        root.  The transfer runs on the engine's communication stream; gather_wait() joins it."""
+        hp = np.ascontiguousarray(hubs_per_rank, np.int32) if hubs_per_rank is not None else None
+        check(self.lib.chub_gather_stats(self.h, ctypes.c_void_p(int(comm_ptr)), int(root), _dptr(hp),
+                                         self._f32(out) if out is not None else None, self._stream(stream)))
+
+    def gather_wait(self, stream=None):
+        check(self.lib.chub_gather_wait(self.h, self._stream(stream)))
+
+    def reduce_stats(self, comm_ptr=None, out=None, stream=None):
+        """Column sums of the statistics over all hubs of all ranks (fp64 [4], CUDA); comm_ptr None = local hubs only."""
+        import torch
+        if out is None:
+            out = torch.empty(4, dtype=torch.float64, device="cuda:%d" % self.device)
+        check(self.lib.chub_reduce_stats(self.h, ctypes.c_void_p(int(comm_ptr)) if comm_ptr else None,
+                                         _tensor_ptr(out, torch.float64, self.device), self._stream(stream)))
+        return out
+
+    def set_timing(self, on=True):
+        check(self.lib.chub_set_timing(self.h, int(bool(on))))
+
+    def step_times(self, max_n=128):
+        """Durations (ms, oldest first) of the most recent step-kernel launches, from CUDA events on their own stream."""
+        out, n = np.zeros(max_n, np.float32), ctypes.c_int32(0)
+        check(self.lib.chub_step_times(self.h, _dptr(out), int(max_n), ctypes.byref(n)))
+        return out[: n.value].copy()
+
+    def debug_curve(self, which, first_bits, n, out=None, stream=None):
+        """The curves as the step kernel compiles them, on n consecutive float32 bit patterns (chub_debug_curve)."""
+        import torch
+        if out is None:
+            out = torch.empty(int(n), dtype=torch.float32, device="cuda:%d" % self.device)
+        check(self.lib.chub_debug_curve(self.h, int(which), ctypes.c_uint32(int(first_bits)), int(n), self._f32(out),
+                                        self._stream(stream)))
+        return out
 
     def get_state(self):
         n = int(self.lib.chub_state_bytes(self.h))

@@ -236,8 +236,10 @@ class VectorHubEnv(object):
     step(a) -> (obs, reward, terminated, truncated, info), everything CUDA tensors.
 
     max_episode_steps: the reference registers the env under a TimeLimit of 999 steps (evcssp_env_cpp/__init__.py:3-8),
-        which never fires because an episode ends after 96; a smaller value truncates (masked reset) like TimeLimit would
-        (use traces="device" then: shared traces are addressed by the global step index and would lose their phase).
+        which never fires because an episode ends after 96; a smaller value truncates (masked reset) like TimeLimit would.
+        The reward returned with the truncating step is that step's reward (a masked reset leaves reward / done alone),
+        the cut episode's statistics land in info["episode_stats"], and traces stay aligned with each hub's own time of
+        day (include/chub.h chub_set_traces).
     soc_penalty: the end-of-episode hydrogen-store penalty the reference computes but leaves commented out
         (evcssp_manager.py:275-297): None (as shipped), "abs" (reward -= test_penalty) or "lagrangian"
         (reward -= signed deviation * lagrangian_factor).  deviation = (SOC_end - init_soc) * capacity_kg / 0.2.

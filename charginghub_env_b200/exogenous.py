@@ -63,8 +63,12 @@ class HubExogenous(object):
         self.price_count = 0
 
 
-def synthetic_year(tables, length=35041):
-    """Shared synthetic traces of SURVEY.md section 8d (config 4): PV, wind, price over `length` steps."""
+def synthetic_year(tables, length=35040):
+    """Shared synthetic traces of SURVEY.md section 8d (config 4): PV, wind, price over `length` steps.  The engine
+    addresses traces modulo their length (include/chub.h chub_set_traces), so `length` is a whole number of days: a
+    rollout that runs past the year wraps onto slot 0 with the time of day intact."""
+    if length % 96:
+        raise ValueError("length must be a multiple of 96 (the engine wraps around the trace)")
     t = np.arange(length, dtype=np.float64)
     tau, d = t % 96, t // 96
     pv = 210.0 * np.maximum(0.0, np.sin(np.pi * (tau - 24) / 48.0)) * (1 + 0.3 * np.cos(2 * np.pi * d / 365.0))
@@ -74,12 +78,12 @@ def synthetic_year(tables, length=35041):
 
 
 def sampled_days(tables, n_days, rs, n_hubs=None):
-    """Noise-free traces stitched from random PV / wind days of the data set: [96*n_days + 1] or per hub."""
+    """Noise-free traces stitched from random PV / wind days of the data set: [96*n_days] or per hub (a ring: the engine
+    wraps around it)."""
     shape = (n_days,) if n_hubs is None else (n_days, n_hubs)
     pd, wdd = rs.randint(0, len(tables["pv_days"]), shape), rs.randint(0, len(tables["wd_days"]), shape)
     pv = np.moveaxis(tables["pv_days"][pd], -1, 1).reshape((96 * n_days,) + shape[1:]) * SCALE_PV
     wd = np.moveaxis(tables["wd_days"][wdd], -1, 1).reshape((96 * n_days,) + shape[1:])
     price = tables["price"][(np.arange(96 * n_days) - 1) % 96]
     price = price.reshape((-1,) + (1,) * (len(shape) - 1)) * np.ones(shape[1:])
-    pad = lambda a: np.concatenate([a, a[:1]], 0)
-    return pad(pv), pad(wd), pad(price)
+    return np.ascontiguousarray(pv), np.ascontiguousarray(wd), np.ascontiguousarray(price)

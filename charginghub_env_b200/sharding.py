@@ -38,6 +38,45 @@ def hub_streams(base_seed, hub_ids):
     return np.array(k0, np.uint32), np.array(k1, np.uint32), np.array(e0, np.uint32)
 
 
+def nccl_comm_ptr(device=None):
+    """ncclComm_t of torch's default NCCL process group as an int (what include/chub.h's collectives take), or None
+    when the group is not NCCL.  The communicator is created lazily by torch: one collective must have run on it."""
+    import torch
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_backend() != "nccl":
+        return None
+    dev = torch.device("cuda", torch.cuda.current_device() if device is None else device)
+    backend = dist.distributed_c10d._get_default_group()._get_backend(dev)
+    try:
+        return int(backend._comm_ptr())
+    except Exception:
+        return None
+
+
+def gather_engine_stats(engine, n_total=None, dst=0, out=None, wait=True):
+    """The path's one collective through the C ABI (chub_gather_stats): every rank's last-episode statistics on `dst`,
+    [n_total, 4] in global hub order.  NCCL groups use the engine's own communication stream (the next steps overlap the
+    transfer; wait=False leaves the join to engine.gather_wait()); any other group falls back to gather_stats()."""
+    import torch
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return engine.tensor("last_stats")
+    comm = nccl_comm_ptr(engine.device)
+    world, rank = dist.get_world_size(), dist.get_rank()
+    if comm is None:
+        return gather_stats(engine.tensor("last_stats"), n_total if n_total is not None else engine.n_hubs * world, dst)
+    per = None
+    if n_total is not None:
+        per = [shard_range(n_total, r, world)[1] - shard_range(n_total, r, world)[0] for r in range(world)]
+    total = sum(per) if per is not None else engine.n_hubs * world
+    if rank == dst and out is None:
+        out = torch.empty((total, 4), dtype=torch.float32, device="cuda:%d" % engine.device)
+    engine.gather_stats(comm, dst, per, out if rank == dst else None)
+    if wait:
+        engine.gather_wait()
+    return out if rank == dst else None
+
+
 def gather_stats(local_stats, n_total, dst=0):
     """Gather per-hub episode statistics [n_local, K] of every rank on `dst`; returns [n_total, K] there
     (None elsewhere).  Shards may differ in length by one hub, so rows are padded to the longest shard."""

@@ -33,7 +33,7 @@ extern "C" {
 #define CHUB_MAX_PILES 32   /* piles per station (fast or slow) */
 #define CHUB_OBS_DIM 13     /* evcssp_manager.py:74-95 with both stations populated */
 #define CHUB_EL_TABLE 102   /* hy_power_speed_list, hydro_sys.py:154-157 */
-#define CHUB_FCEV_QCAP 8    /* FCEV backlog entries kept per hub (reference list is unbounded) */
+#define CHUB_FCEV_QCAP 16   /* FCEV backlog entries kept per hub (reference list is unbounded); oracle/hub_oracle.c uses the same */
 #define CHUB_DAY 96         /* steps per episode, evcssp_manager.py:53 */
 
 #define CHUB_FAST 0
@@ -90,8 +90,9 @@ enum chub_buffer_id {
     CHUB_BUF_OBS = 0,        /* float32 [n_hubs][13] */
     CHUB_BUF_REWARD = 1,     /* float32 [n_hubs] */
     CHUB_BUF_DONE = 2,       /* uint8   [n_hubs] */
-    CHUB_BUF_STATS = 3,      /* float32 [n_hubs][4]: episode return, income, grid energy drawn (kW-steps), incomplete departures */
-    CHUB_BUF_LAST_STATS = 4, /* float32 [n_hubs][4]: the same, frozen at the last completed episode */
+    CHUB_BUF_STATS = 3,      /* float64 [n_hubs][4]: running episode return, income, grid energy drawn (kW-steps), incomplete
+                              * departures -- fp64 like the reference's accumulators (evcssp_manager.py:259-269) */
+    CHUB_BUF_LAST_STATS = 4, /* float32 [n_hubs][4]: the same, frozen at the last completed episode (the gather's payload) */
     CHUB_BUF_ERROR = 5,      /* uint32  [n_hubs] sticky error bits */
     CHUB_BUF_FINAL_SOC = 6   /* float32 [n_hubs] hydrogen store SOC when the last finished episode ended: what the
                               * reference's end-of-episode SOC deviation / test_penalty is formed from
@@ -129,9 +130,14 @@ int chub_set_tables(chub_engine *e, const chub_tables *t);
 int chub_get_class_table(chub_engine *e, int32_t k, double *out);
 
 /* Exogenous traces (the reference's ReNew + OU noise + price list, renewable.py:21-76,
- * evcssp_manager.py:344-361): value seen in the state at absolute step index s is trace[s % length].
- * pv is the scaled PV power (x5), wd the wind power, price = table[t-1] + noise.
- * per_hub = 0: arrays [length];  per_hub = 1: arrays [length][n_hubs].  Host pointers, copied. */
+ * evcssp_manager.py:344-361).  pv is the scaled PV power (x5), wd the wind power, price = table[t-1] + noise.
+ * Addressing: a hub whose time slot is t when absolute step k starts sees trace[(96 * floor((k - t) / 96) + t) % length]
+ * in the state it leaves and slot + 1 in the state it enters -- for hubs in lock step with the step index (reset at a
+ * multiple of 96: every full reset, every auto-reset) that is simply trace[k % length] and trace[(k + 1) % length];
+ * hubs reset in the middle of a day (masked reset, truncation) keep reading the slots of THEIR time of day.
+ * A rollout longer than the trace wraps around: make `length` a multiple of 96 then.
+ * per_hub = 0: arrays [length];  per_hub = 1: arrays [length][n_hubs].  Host pointers, copied.
+ * Invalidates a captured rollout (chub_rollout_capture), like every setter that reallocates device memory. */
 int chub_set_traces(chub_engine *e, const double *pv, const double *wd, const double *price,
                     int32_t length, int32_t per_hub);
 
@@ -159,7 +165,10 @@ int chub_seed_explicit(chub_engine *e, const uint32_t *key0, const uint32_t *key
 
 /* reset(): EvcsspManagerEnv_v6.reset (evcssp_manager.py:304-316) for every hub, or for hubs whose
  * mask byte is non-zero (mask_dev: device uint8 [n_hubs] or NULL).  Also rewinds the absolute
- * step index to `step_index` (use 0).  Fills the obs buffer. */
+ * step index to `step_index` (use 0; negative = leave it).  Fills the obs buffer.
+ * With a mask (cutting episodes short, TimeLimit-style) the reward / done of the last step stay as they are and the
+ * masked hubs' running statistics become their CHUB_BUF_LAST_STATS (and CHUB_BUF_FINAL_SOC the store's present SOC),
+ * as at `done`; a full reset clears reward and done. */
 int chub_reset(chub_engine *e, const uint8_t *mask_dev, int64_t step_index, void *stream);
 
 /* step(action): EvcsspManagerEnv_v6.step (evcssp_manager.py:136-302) for every hub.
@@ -237,11 +246,42 @@ int chub_situation(chub_engine *e, float *out_dev, void *stream);
 #define CHUB_REPORT_LEN 29
 int chub_hub_report(chub_engine *e, int32_t hub, double *host_out, void *stream);
 
-/* Parity / checkpoint read-back (synchronises). */
+/* Parity / checkpoint read-back (synchronises).  The state blob opens with a header (magic, layout version, hubs, pile
+ * slots, classes, generator flag, total size) that chub_set_state validates, and carries every mutable state array plus
+ * what the last step returned (obs, reward, done, final SOC), so a resumed trainer sees the observation it left. */
 int chub_get_field(chub_engine *e, int32_t field, void *host_out);
 int64_t chub_state_bytes(chub_engine *e);
 int chub_get_state(chub_engine *e, void *host_blob);
 int chub_set_state(chub_engine *e, const void *host_blob);
+
+/* The one collective of the path: the per-hub statistics of the last finished episode -- return, income,
+ * grid energy, incomplete departures; what the reference prints at `done`, evcssp_manager.py:259-297, CHS.hpp:916-921 --
+ * gathered on `root` once per rollout.  nccl_comm is an ncclComm_t (as void*) spanning the ranks' engines; NCCL is
+ * resolved at run time from the libnccl.so.2 already loaded in the process (torch's, when the communicator is torch's:
+ * ProcessGroupNCCL._comm_ptr()), else the system one -- libchub.so links none.
+ * hubs_per_rank: host int32 [nranks] (NULL = every rank holds as many hubs as this engine); recv_dev: device float32
+ * [sum of hubs][4] in rank order, needed on the root only.
+ * The statistics are snapshotted on `stream` and travel on the engine's own communication stream, so steps queued on
+ * `stream` afterwards overlap the transfer; chub_gather_wait(e, stream) makes `stream` wait for its completion (call it
+ * before recv_dev is read, and before the timed region of a measurement ends).
+ * chub_reduce_stats: the 32-byte variant -- column sums over all hubs of all ranks, fp64 [4] in sums_dev on every rank
+ * (fixed summation order; nccl_comm NULL = this engine's hubs only), on `stream`. */
+int chub_gather_stats(chub_engine *e, void *nccl_comm, int32_t root, const int32_t *hubs_per_rank, float *recv_dev, void *stream);
+int chub_gather_wait(chub_engine *e, void *stream);
+int chub_reduce_stats(chub_engine *e, void *nccl_comm, double *sums_dev, void *stream);
+
+/* Per-launch timers: with timing on, every step call records CUDA events around its step kernel on
+ * the stream it launches on; chub_step_times synchronises the device and returns the durations (ms, oldest first) of the
+ * most recent launches, at most 128 and at most max_n.  Calls made while the stream is being captured are not timed. */
+int chub_set_timing(chub_engine *e, int32_t on);
+int chub_step_times(chub_engine *e, float *ms_out, int32_t max_n, int32_t *n_out);
+
+/* Parity instrument: the charging curves exactly as the step kernel compiles them (CHS.hpp:495-588, 621-725), evaluated
+ * for the n consecutive float32 bit patterns starting at first_bits -> out_dev float32 [n].  which: 0 slow time->power (as
+ * add_car uses it), 1 slow car_step SOC, 2 slow SOC->time, 3 fast time->power, 4 fast car_step SOC, 5 fast SOC->time,
+ * 6 slow car_step power, 7 fast car_step power; +8 = constant_charging variants.  tests/test_gpu_curves.py walks every
+ * reachable argument with it. */
+int chub_debug_curve(chub_engine *e, int32_t which, uint32_t first_bits, int64_t n, float *out_dev, void *stream);
 
 /* Absolute step index, number of step kernel launches so far, and sum of sticky error bits. */
 int chub_counters(chub_engine *e, int64_t *step_index, int64_t *launches, uint32_t *error_or);

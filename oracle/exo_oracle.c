@@ -6,7 +6,8 @@
  * price_count = 0, evcssp_manager.py:304-316).  The random numbers come from the per-hub X stream of
  * include/chub_exo.h instead of Python's `random` / numpy's global generator; everything else is the
  * reference's arithmetic, statement by statement.  tests/test_exo_oracle.py pins this file against
- * charginghub_env_b200/exogenous.py (itself checked against the unmodified reference) on identical variates.
+ * charginghub_env_b200/exogenous.py (itself pinned on the reference run live, tests/test_exo_live_reference.py) on
+ * identical variates.
  */
 #include <stdint.h>
 #include <stdlib.h>

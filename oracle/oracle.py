@@ -38,6 +38,7 @@ FIELD = {
     "hy_to_use": (89, np.float64, ()), "demand": (90, np.float64, ()), "ep_return": (91, np.float64, ()),
     "cum_income": (92, np.float64, ()), "cum_draw": (93, np.float64, ()), "ev_grid0": (94, np.float64, ()),
     "ev_grid1": (95, np.float64, ()), "h2_grid": (96, np.float64, ()), "hy_act": (97, np.float64, ()),
+    "test_penalty": (98, np.float64, ()), "deviation": (99, np.float64, ()),
     "obs": (112, np.float64, (OBS,)),
 }
 

@@ -49,6 +49,34 @@ def quiet():
         os.close(devnull)
 
 
+class capture(object):
+    """Like quiet(), but fd 1 goes to a temporary file that can be read back incrementally: the reference reports
+    departures below target only by printing (CHS.hpp:916-921, 1081-1086), so counting them means reading its stdout."""
+
+    def __enter__(self):
+        import tempfile
+        sys.stdout.flush()
+        self._saved = os.dup(1)
+        self._tmp = tempfile.TemporaryFile(mode="w+b")
+        os.dup2(self._tmp.fileno(), 1)
+        self._pos = 0
+        return self
+
+    def new_text(self):
+        sys.stdout.flush()
+        self._tmp.seek(self._pos)
+        data = self._tmp.read()
+        self._pos += len(data)
+        return data.decode("utf-8", "replace")
+
+    def __exit__(self, *exc):
+        sys.stdout.flush()
+        os.dup2(self._saved, 1)
+        os.close(self._saved)
+        self._tmp.close()
+        return False
+
+
 def load_shim(csv_dir=None):
     """Import the pybind11 `pyevstation`.  CHS.hpp:175 reads the arrival CSV from the CWD at load."""
     if "pyevstation" in sys.modules:

@@ -113,8 +113,9 @@ def reference_rollout(kwargs, base_seed, hub_ids, actions, py_seed=0, env=None, 
         out[name] = np.zeros((S, H), np.int64)
     for name in ("store", "store_soc", "reward", "income", "hy_flow", "h2_power", "fc_power", "hy_use",
                  "not_meet", "hy_to_use", "demand", "h2_grid", "hy_act",
-                 "pv", "wd", "price"):
+                 "pv", "wd", "price", "cum_income", "cum_draw", "ep_return", "test_penalty", "deviation"):
         out[name] = np.zeros((S, H), np.float64)
+    out["incomplete"] = np.zeros((S, H), np.int64)   # departures below target since the reset (counted from stdout)
     nobs = len(env.low_state)
     out["obs"] = np.zeros((S, H, nobs), np.float64)
 
@@ -132,11 +133,13 @@ def reference_rollout(kwargs, base_seed, hub_ids, actions, py_seed=0, env=None, 
         out["price"][t, h] = env.real_state[1]
         out["obs"][t, h] = env.state
 
-    with ref_env.quiet():
+    with ref_env.capture() as cap:
         for h in range(H):
             ps.hook_seed(int(k0[h]), int(k1[h]), 0, int(e0[h]))
             env.reset()
             snap(0, h)
+            cap.new_text()
+            ret0 = env.acumulate_reward       # never reset by the reference (evcssp_manager.py:269, 308)
             for t in range(T):
                 if loads is not None:
                     for k, st in enumerate(env.env_aggregator.evcssp_evs_objects):
@@ -156,6 +159,13 @@ def reference_rollout(kwargs, base_seed, hub_ids, actions, py_seed=0, env=None, 
                 out["demand"][t + 1, h] = env.hy_sys.hvs.total_mass_need
                 out["h2_grid"][t + 1, h] = env.re_hydrogen_power
                 out["hy_act"][t + 1, h] = env.hy_act
+                out["cum_income"][t + 1, h] = env.cumulated_income
+                out["cum_draw"][t + 1, h] = env.cumulated_draw_ele
+                out["ep_return"][t + 1, h] = env.acumulate_reward - ret0
+                out["deviation"][t + 1, h] = env.deviation
+                if d:
+                    out["test_penalty"][t + 1, h] = env.test_penalty
+                out["incomplete"][t + 1, h] = out["incomplete"][t, h] + cap.new_text().count("charge is not complete")
     ps.hook_off()
     return out, env
 

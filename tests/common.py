@@ -29,10 +29,14 @@ def synth_traces(tabs, L, rs, H=None):
     return np.ascontiguousarray(pv * np.ones(shape)), np.ascontiguousarray(wd), np.ascontiguousarray(price)
 
 
+ZERO_FLOOR = 1e-12  # absolute floor, used only where the oracle's value is exactly 0
+
+
 def close(a, b, rtol=RTOL, atol=0.0):
+    """|a - b| <= rtol |b| (+ atol where a caller states one); where b is exactly 0, |a| <= max(atol, ZERO_FLOOR)."""
     a = np.asarray(a, np.float64)
     b = np.asarray(b, np.float64)
-    return np.abs(a - b) <= atol + rtol * np.abs(b)
+    return np.abs(a - b) <= np.where(b == 0.0, np.maximum(atol, ZERO_FLOOR), atol + rtol * np.abs(b))
 
 
 class Mismatch(object):
@@ -49,8 +53,11 @@ class Mismatch(object):
         return "; ".join("t=%d %s: %d bad (worst %.3g)" % x for x in self.items[:12])
 
 
-def compare_state(eng, orc, t, mm, scale, obs=None, reward=None, done=None, float_exact_stats=None):
-    """Integers bit-exact; floats within RTOL (absolute floor = RTOL x the quantity's natural scale)."""
+def compare_state(eng, orc, t, mm, scale=None, obs=None, reward=None, done=None, float_exact_stats=None):
+    """Integers bit-exact; fp32 state (per-pile SOC / target / power / arrival SOC, station min / charge / max power)
+    BIT-IDENTICAL -- tests/test_gpu_curves.py proves the curves equal glibc's on every reachable argument and the station
+    sums run in the reference's order; fp64 quantities and the fp32 outputs within RTOL relative (north_star's 1e-5), with
+    an absolute floor only where the oracle's value is exactly 0.  `scale` is unused (kept for the callers' signature)."""
     for name in INT_FIELDS:
         a, b = eng.get(name), orc.get(name)
         if name in ("hub_uctr", "hub_lcg"):
@@ -62,29 +69,30 @@ def compare_state(eng, orc, t, mm, scale, obs=None, reward=None, done=None, floa
         a, b = eng.get(name), orc.get(name)
         if name == "pile_power":
             b = b * orc.get("pile_car")
-        ok = close(a, b, atol=RTOL * scale.get(name, 1.0))
+        bad = a.view(np.uint32) != b.astype(np.float32).view(np.uint32)
+        bad &= ~((a == 0) & (b == 0))       # +0 / -0
         if float_exact_stats is not None:
-            float_exact_stats[name] = float_exact_stats.get(name, 0) + int((a != b).sum())
-        if not ok.all():
-            mm.add(t, name, int((~ok).sum()), float(np.abs(a.astype(np.float64) - b).max()))
+            float_exact_stats[name] = float_exact_stats.get(name, 0) + int(bad.sum())
+        if bad.any():
+            mm.add(t, name, int(bad.sum()), float(np.abs(a.astype(np.float64) - b).max()))
     a, b = eng.get("store"), orc.get("store")
-    ok = close(a, b, atol=RTOL)
+    ok = close(a, b)
     if not ok.all():
         mm.add(t, "store", int((~ok).sum()), float(np.abs(a - b).max()))
     if t > 0:
         for name in DIAG:
             a, b = eng.get("diag_" + name), orc.get(name)
-            ok = close(a, b, atol=RTOL * scale.get(name, 1.0))
+            ok = close(a, b)
             if not ok.all():
                 mm.add(t, name, int((~ok).sum()), float(np.abs(a - b).max()))
     if obs is not None:
         b = orc.get("obs")
-        ok = close(obs, b, atol=RTOL)
+        ok = close(obs, b, atol=1e-7)      # float32 outputs of fp64 values that may cancel to ~0 (normalised powers)
         if not ok.all():
             mm.add(t, "obs", int((~ok).sum()), float(np.abs(obs - b).max()))
     if reward is not None:
         b = orc.get("reward")
-        ok = close(reward, b, atol=RTOL)
+        ok = close(reward, b, atol=1e-7)
         if not ok.all():
             mm.add(t, "reward_f32", int((~ok).sum()), float(np.abs(reward - b).max()))
     if done is not None:

@@ -1,6 +1,7 @@
 """CPU: the exogenous-generator oracle (oracle/exo_oracle.c) against the package's host generator
-(charginghub_env_b200/exogenous.py, which follows the reference's ReNew / OU_Noise / make_state and is checked
-against the unmodified reference in tests/test_gpu_env.py), both fed the same per-hub X stream."""
+(charginghub_env_b200/exogenous.py), both fed the same per-hub X stream.  HubExogenous itself is pinned bit for bit on
+the reference RUN LIVE (renewable.ReNew / OU_Noise, EvcsspManagerEnv_v6.make_state) in
+tests/test_exo_live_reference.py; the device generator is compared with this oracle in tests/test_gpu_exo.py."""
 import numpy as np
 
 from charginghub_env_b200 import exogenous, sharding

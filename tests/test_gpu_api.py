@@ -111,7 +111,7 @@ def test_errors_are_reported_not_printed(tables):
 
 
 def test_fcev_backlog_overflow_sets_error_bit(tables):
-    """A permeate of 1.0 floods the FCEV list; the engine keeps 8 entries and raises the sticky bit."""
+    """A permeate of 1.0 floods the FCEV list; the engine keeps CHUB_FCEV_QCAP entries and raises the sticky bit."""
     import torch
     from charginghub_env_b200 import HubEngine
     eng = HubEngine(64, [dict(C.DEFAULT_KW, fcev_permeate=1.0)], device=0, tables=tables, seed=2)
@@ -317,3 +317,132 @@ def test_step_into_equals_step(tables):
         assert np.array_equal(a_eng.get(name), b_eng.get(name)), name
     with pytest.raises(ValueError):
         b_eng.step_into(a, ob[0][:, :12])
+
+
+def test_checkpoint_carries_the_last_outputs_and_validates_its_header(tables):
+    """a trainer that resumes mid-episode must see the observation it left; a blob of another engine shape
+    must be refused by the C ABI itself (header: magic, layout version, hubs, pile slots, classes, generator flag)."""
+    import torch
+    from charginghub_env_b200 import ChubError, HubEngine
+    eng, rs = _engine(200, tables, seed=9)
+    eng.reset()
+    for _ in range(7):
+        eng.step(torch.from_numpy(rs.uniform(-1, 1, (200, 47)).astype(np.float32)).cuda())
+    torch.cuda.synchronize()
+    want = {n: eng.tensor(n).clone() for n in ("obs", "reward", "done", "final_soc", "stats")}
+    blob = eng.get_state()
+    for _ in range(5):
+        eng.step(torch.from_numpy(rs.uniform(-1, 1, (200, 47)).astype(np.float32)).cuda())
+    eng.set_state(blob)
+    torch.cuda.synchronize()
+    for n, v in want.items():
+        assert torch.equal(eng.tensor(n), v), n
+    other, _ = _engine(232, tables, seed=9)
+    big = other.get_state()
+    with pytest.raises((ChubError, ValueError)):
+        eng.set_state(big)
+    lib = eng.lib
+    import ctypes
+    bad = blob.copy()
+    bad[0] ^= 0xFF                                        # magic
+    assert lib.chub_set_state(eng.h, bad.ctypes.data_as(ctypes.c_void_p)) == -1
+    small = HubEngine(200, [dict(C.DEFAULT_KW, station_list=[20, 24])], device=0, tables=tables, seed=9)
+    sb = small.get_state()
+    assert lib.chub_set_state(eng.h, sb.ctypes.data_as(ctypes.c_void_p)) == -1   # other pile layout: refused by the C ABI
+    assert b"another shape" in lib.chub_last_error()
+
+
+def test_wrong_dtype_or_device_is_refused(tables):
+    """the kernel would silently reinterpret the bytes of a float64 / half / int64 tensor."""
+    import torch
+    eng, rs = _engine(64, tables)
+    eng.reset()
+    for bad in (torch.zeros((64, 47), device="cuda", dtype=torch.float64), torch.zeros((64, 47), device="cuda", dtype=torch.float16),
+                torch.zeros((64, 47), device="cuda", dtype=torch.int64)):
+        with pytest.raises(ValueError):
+            eng.step(bad)
+    with pytest.raises(ValueError):
+        eng.step_loads(torch.zeros((64, 4), device="cuda", dtype=torch.float64))
+    with pytest.raises(ValueError):
+        eng.reset(mask=torch.zeros(64, device="cuda", dtype=torch.float32))
+    with pytest.raises(ValueError):
+        eng.reset(mask=torch.zeros(63, device="cuda", dtype=torch.uint8))
+    with pytest.raises(ValueError):
+        eng.step(torch.zeros((64, 47)))                   # host tensor
+    eng.step(torch.zeros((64, 47), device="cuda"))       # and the right one still works
+
+
+def test_setters_invalidate_a_captured_rollout(tables):
+    """a captured graph bakes trace / pile pointers; replaying it after a setter freed them must fail cleanly."""
+    import torch
+    from charginghub_env_b200 import ChubError
+    eng, rs = _engine(256, tables, seed=4, auto_reset=True)
+    acts = torch.from_numpy(rs.uniform(-1, 1, (256, 47)).astype(np.float32)).cuda()
+    eng.reset()
+    eng.capture_rollout(acts, 4)
+    eng.rollout()
+    eng.set_traces(*C.synth_traces(tables, 96, rs))
+    with pytest.raises(ChubError):
+        eng.rollout()
+    eng.capture_rollout(acts, 4)
+    eng.rollout()
+    torch.cuda.synchronize()
+    assert eng.counters()["step_index"] == 8
+
+
+def test_per_launch_timers(tables):
+    import torch
+    eng, rs = _engine(4096, tables, seed=4)
+    acts = torch.from_numpy(rs.uniform(-1, 1, (4096, 47)).astype(np.float32)).cuda()
+    eng.reset()
+    eng.set_timing(True)
+    for _ in range(10):
+        eng.step(acts)
+    ms = eng.step_times()
+    assert ms.shape == (10,) and (ms > 0).all() and (ms < 50).all()
+    eng.set_timing(False)
+    eng.step(acts)
+    assert eng.step_times().shape == (0,)
+
+
+def test_gather_and_reduce_stats_through_the_c_abi(tables):
+    """chub_gather_stats / chub_reduce_stats on a one-rank NCCL communicator (torch's): the root receives its own
+    statistics, the sums equal a float64 sum of the buffer.  (The multi-rank form runs in bench.py --gpus N.)"""
+    import os
+    import torch
+    import torch.distributed as dist
+    from charginghub_env_b200 import sharding
+    eng, rs = _engine(3000, tables, seed=6, auto_reset=True)
+    acts = torch.from_numpy(rs.uniform(-1, 1, (3000, 47)).astype(np.float32)).cuda()
+    eng.reset()
+    for _ in range(97):
+        eng.step(acts)
+    torch.cuda.synchronize()
+    last = eng.tensor("last_stats")
+    assert (last[:, 0] != 0).all()
+    sums = eng.reduce_stats()                              # no communicator: local sums
+    torch.cuda.synchronize()
+    assert torch.allclose(sums, last.double().sum(0), rtol=1e-12)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29613")
+    created = not dist.is_initialized()
+    if created:
+        dist.init_process_group("nccl", rank=0, world_size=1, device_id=torch.device("cuda", 0))
+    try:
+        dist.all_reduce(torch.zeros(1, device="cuda"))     # torch creates the communicator on first use
+        comm = sharding.nccl_comm_ptr(0)
+        assert comm
+        out = torch.zeros((3000, 4), device="cuda")
+        eng.gather_stats(comm, 0, None, out)
+        eng.step(acts)                                      # overlaps the transfer
+        eng.gather_wait()
+        torch.cuda.synchronize()
+        assert torch.equal(out, last)
+        sums2 = eng.reduce_stats(comm)
+        torch.cuda.synchronize()
+        assert torch.equal(sums2, sums)
+        got = sharding.gather_engine_stats(eng)
+        assert torch.equal(got, last)
+    finally:
+        if created:
+            dist.destroy_process_group()

@@ -167,3 +167,25 @@ def test_vector_env_adapter(tables):
     assert abs(float(o[0, 0])) < 1e-6     # sin(2 pi 0 / 96): back at the first step of a day
     assert int(short._elapsed.max()) == 0
     short.close()
+    # the reward returned with the truncating step is that step's reward, and the cut episode's statistics are kept
+    # (ADVICE r1): an untruncated twin on the same streams and actions is the witness; shared traces this time
+    twin = VectorHubEnv(H, env_kwargs=kw, seed=5)
+    cut = VectorHubEnv(H, env_kwargs=kw, seed=5, max_episode_steps=10)
+    twin.reset(); cut.reset()
+    gen2 = torch.Generator(device="cuda").manual_seed(8)
+    for t in range(10):
+        a = torch.rand((H, twin.env.action_dim), device="cuda", generator=gen2) * 2 - 1
+        _, r_twin, _, _, i_twin = twin.step(a)
+        o_cut, r_cut, term, trunc, i_cut = cut.step(a)
+        assert torch.equal(r_twin, r_cut), t
+    torch.cuda.synchronize()
+    assert trunc.all() and (r_cut != 0).any()
+    assert torch.equal(i_cut["episode_stats"].double(), twin.engine.tensor("stats").float().double())
+    assert (cut.engine.tensor("stats") == 0).all()
+    assert (o_cut[:, 0].abs() < 1e-6).all()
+    a = torch.rand((H, twin.env.action_dim), device="cuda", generator=gen2) * 2 - 1
+    o_next, _, _, _, _ = cut.step(a)
+    # the hubs restarted their day: the PV they see is the trace's slot 1, not slot 11
+    pv, _, _ = __import__("charginghub_env_b200.exogenous", fromlist=["x"]).synthetic_year(twin.env.tables)
+    assert torch.allclose(o_next[:, 11].double(), torch.full((H,), pv[1] / 210.0, dtype=torch.float64, device="cuda"), atol=1e-6)
+    twin.close(); cut.close()

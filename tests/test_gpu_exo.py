@@ -40,7 +40,7 @@ def test_device_generator_three_episodes(tables):
         if (t + 1) % 8 == 0 or want_done.any():
             torch.cuda.synchronize()
             assert np.array_equal(done.cpu().numpy().astype(np.int32), want_done)
-            assert C.close(rew.cpu().numpy(), want_rew, atol=C.RTOL).all()
+            assert C.close(rew.cpu().numpy(), want_rew, atol=1e-7).all()
             C.compare_state(eng, orc, 0, mm, C.SCALE, obs=obs.cpu().numpy())
     assert not mm, str(mm)
     # the generator consumed exactly the oracle's share of the X stream, and the noise is really there

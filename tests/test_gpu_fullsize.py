@@ -52,9 +52,9 @@ def test_windows_of_the_full_shard_match_the_oracle(tables):
         torch.cuda.synchronize()
         for b, o in zip(bases, orcs):
             sl = slice(b, b + WINDOW)
-            assert C.close(obs[sl].cpu().numpy(), o.get("obs"), atol=C.RTOL).all(), ("obs", t, b)
+            assert C.close(obs[sl].cpu().numpy(), o.get("obs"), atol=1e-7).all(), ("obs", t, b)
             if t:
-                assert C.close(rew[sl].cpu().numpy(), o.get("reward"), atol=C.RTOL).all(), ("reward", t, b)
+                assert C.close(rew[sl].cpu().numpy(), o.get("reward"), atol=1e-7).all(), ("reward", t, b)
                 assert np.array_equal(done[sl].cpu().numpy().astype(np.int32), o.get("hub_done")), ("done", t, b)
         if not deep:
             return
@@ -71,7 +71,10 @@ def test_windows_of_the_full_shard_match_the_oracle(tables):
                 y = o.get(name)
                 if name == "pile_power":
                     y = y * o.get("pile_car")
-                assert C.close(a[b:b + WINDOW], y, atol=C.RTOL).all(), (name, t, b)
+                if name == "store":
+                    assert C.close(a[b:b + WINDOW], y).all(), (name, t, b)
+                else:
+                    assert np.array_equal(a[b:b + WINDOW], y), (name, t, b)      # fp32 state: bit-identical
 
     compare(0, obs, None, None, True)
     for t in range(96):
@@ -181,7 +184,7 @@ def test_long_horizon_rollout_matches_the_oracle(tables):
                     x, y = x.astype(np.uint32), y.astype(np.uint32)
                 assert np.array_equal(x, y), (name, steps, b)
         for b, o in zip(bases, orcs):
-            assert C.close(obs[b:b + 64], o.get("obs"), atol=C.RTOL).all(), ("obs", steps, b)
+            assert C.close(obs[b:b + 64], o.get("obs"), atol=1e-7).all(), ("obs", steps, b)
         if deep:
             for name in C.PILE_FLOATS + ["store"]:
                 a = eng.get(name)
@@ -189,11 +192,78 @@ def test_long_horizon_rollout_matches_the_oracle(tables):
                     y = o.get(name)
                     if name == "pile_power":
                         y = y * o.get("pile_car")
-                    assert C.close(a[b:b + 64], y, atol=C.RTOL).all(), (name, steps, b)
+                    if name == "store":
+                        assert C.close(a[b:b + 64], y).all(), (name, steps, b)
+                    else:
+                        assert np.array_equal(a[b:b + 64], y), (name, steps, b)  # fp32 state: bit-identical
     assert eng.counters()["step_index"] == DAYS * 96 and eng.counters()["error_or"] == 0
     last = eng.tensor("last_stats").cpu().numpy()
     for w, b in enumerate(bases):
-        assert np.allclose(last[b:b + 64, 0], returns[w], rtol=1e-4, atol=1e-4)
+        assert C.close(last[b:b + 64, 0], returns[w], rtol=1e-6).all()
+
+
+def test_windows_of_the_full_config3_shard_match_the_oracle(tables):
+    """BASELINE config 3 at full size: 262,144 heterogeneous hubs (minus 7: ragged last warp) of 4,096 parameter classes
+    (bench.py's workload: 4..32 piles per station, H2 sizes, permeate up to 0.05), action rows padded to 66, fused
+    auto-reset; eight oracle windows spread over the hub range follow one and a half episodes, the oracle reset by hand
+    at done.  Integers bit-exact, fp32 pile state bit-identical, fp64 within RTOL."""
+    import torch
+    import bench
+    from charginghub_env_b200 import HubEngine
+    from oracle import oracle as O
+    wl = bench.workload("config3", tables)
+    H, W, seed, S = wl["H"] - 7, 96, 0xC3, wl["stride"]
+    hub_class = np.ascontiguousarray(wl["hub_class"][:H])
+    eng = HubEngine(H, wl["classes"], hub_class=hub_class, device=0, diagnostics=True, tables=tables, seed=seed,
+                    auto_reset=True, action_stride=S)
+    T = 144
+    pv, wd, price = _year(tables, T + 2)
+    eng.set_traces(pv, wd, price)
+    bases = [0, 4097, 65536 - 40, 100003, H // 2, 200000, H - 2 * W - 1, H - W]
+    orcs = []
+    for b in bases:
+        o = O.Oracle(W, wl["classes"], hub_class=hub_class[b:b + W], tables=C.oracle_tables(tables))
+        o.seed_base(seed, b)
+        o.reset(pv[0], wd[0], price[0])
+        orcs.append(o)
+    obs = eng.reset()
+    gen = torch.Generator(device="cuda").manual_seed(6)
+    err_or = 0
+    for t in range(T):
+        a = torch.rand((H, S), device="cuda", generator=gen) * 2 - 1
+        obs, rew, done = eng.step(a)
+        rows = a.cpu().numpy()
+        deep = t in (0, 40, 95, 96, T - 1)
+        if deep or t % 6 == 5:
+            torch.cuda.synchronize()
+            o_h, r_h, d_h = obs.cpu().numpy(), rew.cpu().numpy(), done.cpu().numpy()
+            fields = {n: eng.get(n) for n in (C.INT_FIELDS + C.PILE_FLOATS + ["store"] if deep else ["hub_uctr", "hub_lcg", "st_line"])}
+        for b, o in zip(bases, orcs):
+            o.step(rows[b:b + W], pv[t + 1], wd[t + 1], price[t + 1])
+            want_rew, want_done = o.get("reward"), o.get("hub_done")
+            if want_done.all():
+                err_or |= int(np.bitwise_or.reduce(o.get("hub_err")))
+                o.reset(pv[t + 1], wd[t + 1], price[t + 1])
+            if not (deep or t % 6 == 5):
+                continue
+            sl = slice(b, b + W)
+            assert np.array_equal(d_h[sl].astype(np.int32), want_done), ("done", t, b)
+            assert C.close(r_h[sl], want_rew, atol=1e-7).all(), ("reward", t, b)
+            assert C.close(o_h[sl], o.get("obs"), atol=1e-7).all(), ("obs", t, b)
+            for name, a_all in fields.items():
+                x, y = a_all[sl], o.get(name)
+                if name in ("hub_uctr", "hub_lcg"):
+                    x, y = x.astype(np.uint32), y.astype(np.uint32)
+                if name == "pile_power":
+                    y = y * o.get("pile_car")
+                if name == "store":
+                    assert C.close(x, y).all(), (name, t, b)
+                else:
+                    assert np.array_equal(x, y), (name, t, b)
+    for o in orcs:
+        err_or |= int(np.bitwise_or.reduce(o.get("hub_err")))
+    got_err = eng.tensor("error").cpu().numpy()
+    assert int(np.bitwise_or.reduce(np.concatenate([got_err[b:b + W] for b in bases]))) == err_or
 
 
 @pytest.mark.parametrize("extra", [[], ["--classes", "8", "--loads-every", "3"], ["--exogenous", "device"]])

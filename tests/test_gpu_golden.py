@@ -42,13 +42,13 @@ def test_engine_reproduces_reference_trace(path, tables):
             a, b = z[name][t].astype(np.float64), eng.get(name)
             if name == "pile_power":
                 a = a * z["pile_car"][t]
-            assert C.close(b, a, atol=C.RTOL * C.SCALE.get(name, 1.0)).all(), (name, t)
-        assert C.close(eng.get("store"), z["store"][t], atol=C.RTOL).all(), ("store", t)
-        assert C.close(obs.cpu().numpy()[:, :nobs], z["obs"][t], atol=C.RTOL).all(), ("obs", t)
+            assert np.array_equal(b, a.astype(np.float32)), (name, t)     # fp32 state: bit-identical to the reference's
+        assert C.close(eng.get("store"), z["store"][t]).all(), ("store", t)
+        assert C.close(obs.cpu().numpy()[:, :nobs], z["obs"][t], atol=1e-7).all(), ("obs", t)
         if t:
             for name in DIAG:
-                assert C.close(eng.get("diag_" + name), z[name][t], atol=C.RTOL * C.SCALE.get(name, 1.0)).all(), (name, t)
-            assert C.close(rew.cpu().numpy(), z["reward"][t], atol=C.RTOL).all()
+                assert C.close(eng.get("diag_" + name), z[name][t], atol=0.0).all(), (name, t)
+            assert C.close(rew.cpu().numpy(), z["reward"][t], atol=1e-7).all()
             assert np.array_equal(done.cpu().numpy().astype(np.int64), z["hub_done"][t].astype(np.int64))
 
     check(0, obs)

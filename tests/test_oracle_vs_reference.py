@@ -32,6 +32,16 @@ def _compare(kw, H, T, seed):
         for name in ("store", "store_soc") + (("reward", "income", "demand", "hy_use", "not_meet") if t else ()):
             assert np.allclose(ref[name][t], orc.get(name), rtol=1e-12, atol=1e-12), (name, t)
         assert np.allclose(ref["obs"][t], orc.get("obs")[:, :ref["obs"].shape[2]], rtol=1e-12, atol=1e-12)
+        if 0 < t <= 96:
+            # what the path's one collective carries (evcssp_manager.py:259-297, CHS.hpp:916-921 / 1081-1086): the
+            # reference's own accumulators, and its "charge is not complete" prints counted from its stdout
+            for name in ("cum_income", "cum_draw", "ep_return", "deviation"):
+                assert np.allclose(ref[name][t], orc.get(name), rtol=1e-12, atol=1e-12), (name, t)
+            assert np.array_equal(ref["incomplete"][t], orc.get("st_incomplete").sum(axis=1)), ("incomplete", t)
+            if t == 96:
+                assert ref["hub_done"][t].all()
+                assert np.allclose(ref["test_penalty"][t], orc.get("test_penalty"), rtol=1e-12, atol=0), "test_penalty"
+    return ref
 
 
 def test_default_hub_live():

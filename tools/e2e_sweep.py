@@ -16,7 +16,7 @@ tabs = load_tables()
 wl = bench.workload("config5", tabs)
 H = a.hubs
 eng = HubEngine(H, wl["classes"], action_stride=wl["stride"], auto_reset=True, tables=tabs, seed=1)
-eng.set_traces(*bench.year_traces(tabs, 35041))
+eng.set_traces(*bench.year_traces(tabs, 35040))
 eng.reset()
 hb = eng.host_buffers()
 bufs = [hb["actions"], eng.pinned_actions(), eng.pinned_actions()]   # rotated: 296 MB, beyond the host's caches

@@ -19,7 +19,7 @@ wl = bench.workload(a.workload, tabs)
 H = a.hubs
 hc = None if wl["hub_class"] is None else np.resize(wl["hub_class"], H)
 eng = HubEngine(H, wl["classes"], hub_class=hc, action_stride=wl["stride"], auto_reset=True, tables=tabs, seed=1)
-eng.set_traces(*bench.year_traces(tabs, 35041))
+eng.set_traces(*bench.year_traces(tabs, 35040))
 acts = torch.rand((H, wl["stride"]), device="cuda") * 2 - 1
 eng.reset()
 if a.control == "loads":   # one power target per station: [load0 kW, load1 kW, a[-2], a[-1]]

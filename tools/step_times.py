@@ -7,7 +7,7 @@ tabs = load_tables()
 wl = bench.workload("config5", tabs)
 H = wl["H"]
 eng = HubEngine(H, wl["classes"], action_stride=wl["stride"], auto_reset=True, tables=tabs, seed=1)
-eng.set_traces(*bench.year_traces(tabs, 35041))
+eng.set_traces(*bench.year_traces(tabs, 35040))
 pool = [torch.rand((H, wl["stride"]), device="cuda") * 2 - 1 for _ in range(4)]
 eng.reset()
 for i in range(96):
