@@ -83,6 +83,7 @@ SYMBOLS = {
     "chub_situation_width": (ctypes.c_int, [_vp, _vp, _vp]),
     "chub_situation": (ctypes.c_int, [_vp, _vp, _vp]),
     "chub_step_host": (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
+    "chub_step_host_packed": (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "chub_reset_host": (ctypes.c_int, [_vp, _vp, _vp]),
     "chub_step_packed": (ctypes.c_int, [_vp, _vp, _vp]),
     "chub_set_host_threads": (ctypes.c_int, [_vp, _i32, _i32]),

@@ -8,6 +8,7 @@
 #include <dlfcn.h>
 #include <nvtx3/nvToolsExt.h>
 
+#include <cctype>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -50,6 +51,7 @@ struct chub_engine {
     uint16_t *lut = nullptr; float *s2t_lut = nullptr; double *pv = nullptr, *wd = nullptr, *price_tr = nullptr;
     float *obs = nullptr, *reward = nullptr; uint8_t *done = nullptr; double *diag = nullptr; float *st_power = nullptr;
     long long *step_index = nullptr;
+    unsigned long long *queue = nullptr;   // [0] ticket counter, [1] its value at the start of the epoch (chub_step_kernel)
     int num_sms = 0;
     float *actions_stage = nullptr;  // device copy target of chub_step_host when the rows travel unpacked (host_threads == 0)
     uint4 *packed_stage = nullptr;   // device copy target of chub_step_host: one packed record per hub
@@ -115,7 +117,7 @@ static void engine_free(chub_engine *e) {
     if (e->comm_done) cudaEventDestroy(e->comm_done);
     void *ptrs[] = {e->pile, e->arrive, e->hubA, e->store, e->keys, e->occ, e->cls, e->stats, e->last_stats, e->err, e->qsoc,
                     e->d_classes, e->d_el, e->lut, e->s2t_lut, e->pv, e->wd, e->price_tr, e->obs, e->reward, e->done, e->diag,
-                    e->st_power, e->step_index, e->actions_stage, e->exo_d, e->exo_i, e->pv_days, e->wd_days, e->act_bits, e->final_soc, e->packed_stage, e->report_dev,
+                    e->st_power, e->step_index, e->queue, e->actions_stage, e->exo_d, e->exo_i, e->pv_days, e->wd_days, e->act_bits, e->final_soc, e->packed_stage, e->report_dev,
                     e->stats_stage, e->stats_partial, e->stats_sums};
     for (void *p : ptrs)
         if (p) cudaFree(p);
@@ -155,7 +157,7 @@ extern "C" int chub_create(const chub_config *cfg, chub_engine **out) {
     A(dalloc(&e->stats, 2 * Hp)); A(dalloc(&e->last_stats, Hp)); A(dalloc(&e->err, Hp)); A(dalloc(&e->final_soc, Hp));
     A(dalloc(&e->qsoc, Hp * CHUB_FCEV_QCAP)); A(dalloc(&e->lut, (size_t) 96 * 1000)); A(dalloc(&e->s2t_lut, (size_t) 4000));
     A(dalloc(&e->obs, Hp * CHUB_OBS_DIM)); A(dalloc(&e->reward, Hp)); A(dalloc(&e->done, Hp));
-    A(dalloc(&e->step_index, 1));
+    A(dalloc(&e->step_index, 1)); A(dalloc(&e->queue, 2));
     if (cfg->diagnostics) { A(dalloc(&e->diag, Hp * CHUB_D_COUNT)); A(dalloc(&e->st_power, Hp * 6)); }
     if (r != cudaSuccess) {
         engine_free(e);
@@ -506,6 +508,7 @@ static int fill_params(chub_engine *e, ChubParams &P) {
     P.auto_reset = e->cfg.auto_reset; P.diagnostics = e->cfg.diagnostics;
     P.trace_len = e->trace_len; P.trace_per_hub = e->trace_per_hub;
     P.step_offset = 0; P.step_index = e->step_index; P.num_sms = e->num_sms;
+    P.queue = getenv("CHUB_STATIC_GRID") ? nullptr : e->queue; P.queue_base = e->queue + 1; P.queue_stride = 0;
     {   // experiment knobs (defaults are the measured best)
         const char *b = getenv("CHUB_BLOCK"), *y = getenv("CHUB_PHASE_SYNC");
         P.block = b ? atoi(b) : 0;
@@ -537,12 +540,13 @@ static int run_step(chub_engine *e, const ChubParams &P, cudaStream_t s) {
             CK(cudaEventRecord(e->time_ev[2 * slot], s));
         }
     }
-    CK(chub_launch_step(P, s));
+    unsigned long long tickets = 0;
+    CK(chub_launch_step(P, s, &tickets));
     if (slot >= 0) {
         CK(cudaEventRecord(e->time_ev[2 * slot + 1], s));
         e->timed += 1;
     }
-    chub_launch_tick(e->step_index, 1, s);
+    chub_launch_tick(e->step_index, 1, e->queue + 1, tickets, s);
     CK(cudaGetLastError());
     e->launches += 1;
     return CHUB_OK;
@@ -654,6 +658,30 @@ extern "C" int chub_set_host_threads(chub_engine *e, int32_t n_threads, int32_t 
     return CHUB_OK;
 }
 
+// cpulist ("0-15,32-47") of the NUMA node of a CUDA device, from sysfs; false when unknown or the host has one node
+static bool gpu_local_cpulist(int device, char *out, size_t cap) {
+    char bus[32] = {0};
+    if (cudaDeviceGetPCIBusId(bus, sizeof bus, device) != cudaSuccess) return false;
+    for (char *c = bus; *c; ++c) *c = (char) tolower(*c);
+    char path[128];
+    snprintf(path, sizeof path, "/sys/bus/pci/devices/%s/numa_node", bus);
+    FILE *f = fopen(path, "r");
+    if (!f) return false;
+    int node = -1;
+    const int got = fscanf(f, "%d", &node);
+    fclose(f);
+    if (got != 1 || node < 0) return false;
+    f = fopen("/sys/devices/system/node/node1/cpulist", "r");   // a second node exists?
+    if (!f) return false;
+    fclose(f);
+    snprintf(path, sizeof path, "/sys/devices/system/node/node%d/cpulist", node);
+    f = fopen(path, "r");
+    if (!f) return false;
+    const bool ok = fgets(out, (int) cap, f) != nullptr;
+    fclose(f);
+    return ok;
+}
+
 static int host_pipeline_setup(chub_engine *e) {
     if (e->host_threads < 0) {
         const char *t = getenv("CHUB_HOST_THREADS"), *r = getenv("CHUB_HOST_RANGES");
@@ -672,7 +700,12 @@ static int host_pipeline_setup(chub_engine *e) {
         if (!e->actions_stage) CK(dalloc(&e->actions_stage, (size_t) e->Hpad * (size_t) e->cfg.action_stride));
         return CHUB_OK;
     }
-    if (!e->pool && e->H > CHUB_HOST_INLINE_PACK) e->pool = chub_pack_pool_create(e->host_threads);
+    if (!e->pool && e->H > CHUB_HOST_INLINE_PACK) {
+        // the packing threads read the caller's rows and write the pinned record buffer: keep them on the cores of the
+        // NUMA node the GPU hangs off (no-op on single-node hosts and where sysfs does not say)
+        char cpus[512];
+        e->pool = chub_pack_pool_create_on(e->host_threads, gpu_local_cpulist(e->cfg.device, cpus, sizeof cpus) ? cpus : nullptr);
+    }
     if (!e->packed_stage) CK(dalloc(&e->packed_stage, (size_t) e->Hpad));
     if (!e->packed_host) CK(cudaHostAlloc((void **) &e->packed_host, sizeof(uint4) * (size_t) e->Hpad, cudaHostAllocDefault));
     return CHUB_OK;
@@ -691,9 +724,8 @@ extern "C" int chub_pack_actions(chub_engine *e, const float *actions_host, void
 // records by the pool's threads (chub_hostpack.cpp), records host->device, step kernel, obs/reward/done device->host --
 // so the host's memory reads, both PCIe directions and the kernel overlap; hubs are independent, so stepping them
 // range by range is the same computation as one launch.
-extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *obs_host, float *reward_host,
-                              uint8_t *done_host, void *stream) {
-    if (!e || !actions_host) return fail(CHUB_ERR_ARG, "chub_step_host: null argument");
+static int step_host_impl(chub_engine *e, const float *actions_host, const uint4 *records_host, float *obs_host,
+                          float *reward_host, uint8_t *done_host, void *stream) {
     CK(cudaSetDevice(e->cfg.device));
     cudaStream_t s = (cudaStream_t) stream;
     ChubParams P;
@@ -702,9 +734,10 @@ extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *
     rc = host_pipeline_setup(e);
     if (rc) return rc;
     NvtxRange range("chub_step_host");
-    const bool packed = e->host_threads > 0;
+    const bool packed = records_host != nullptr || e->host_threads > 0;
     if (packed) P.act_packed = e->packed_stage;
     else P.actions = e->actions_stage;
+    if (records_host && !e->packed_stage) CK(dalloc(&e->packed_stage, (size_t) e->Hpad));
     const int R = e->host_ranges ? e->host_ranges : (packed ? 16 : 8);   // whole rows over PCIe: fewer, larger copies
     cudaStream_t s_in = e->host_streams[0], s_out = e->host_streams[1], *s_k = e->host_streams + 2;
     cudaEvent_t *ev_in = e->host_events, *ev_k = e->host_events + CHUB_PACK_MAX_RANGES;
@@ -712,8 +745,9 @@ extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *
     const int A = e->cfg.action_stride;
     int per = (e->H + R - 1) / R;
     per = (per + 1023) / 1024 * 1024;           // whole warps (and whole blocks of any launch shape)
-    const bool pooled = packed && e->pool != nullptr;
-    if (packed && !pooled) {
+    const bool pooled = packed && !records_host && e->pool != nullptr;
+    const uint4 *records = records_host ? records_host : e->packed_host;
+    if (packed && !pooled && !records_host) {
         rc = chub_pack_actions(e, actions_host, e->packed_host);
         if (rc) return rc;
     }
@@ -740,7 +774,7 @@ extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *
         const int n = (b + per <= e->H ? per : e->H - b);
         if (packed) {
             if (pooled) chub_pack_pool_wait(e->pool, c);
-            CK(cudaMemcpyAsync(e->packed_stage + b, e->packed_host + b, sizeof(uint4) * (size_t) n, cudaMemcpyHostToDevice, s_in));
+            CK(cudaMemcpyAsync(e->packed_stage + b, records + b, sizeof(uint4) * (size_t) n, cudaMemcpyHostToDevice, s_in));
         } else {
             CK(cudaMemcpyAsync(e->actions_stage + (size_t) b * A, actions_host + (size_t) b * A, sizeof(float) * (size_t) n * A,
                                cudaMemcpyHostToDevice, s_in));
@@ -748,6 +782,7 @@ extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *
         CK(cudaEventRecord(ev_in[c], s_in));
         CK(cudaStreamWaitEvent(sk, ev_in[c], 0));
         P.h_begin = b; P.h_end = b + n;
+        P.queue = nullptr;                      // ranges run side by side on several streams: static block -> tile mapping
         CK(chub_launch_step(P, sk));
         CK(cudaEventRecord(ev_k[c], sk));
         CK(cudaStreamWaitEvent(s_out, ev_k[c], 0));
@@ -764,11 +799,25 @@ extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *
     for (int c = std::max(0, n_ranges - CHUB_HOST_KSTREAMS); c < n_ranges; ++c) CK(cudaStreamWaitEvent(s, ev_k[c], 0));
     CK(cudaEventRecord(ev_join, s_out));
     CK(cudaStreamWaitEvent(s, ev_join, 0));
-    chub_launch_tick(e->step_index, 1, s);      // after the last range: every launch above read the same step index
+    chub_launch_tick(e->step_index, 1, nullptr, 0, s);      // after the last range: every launch above read the same step index
     CK(cudaGetLastError());
     e->launches += 1;
     CK(cudaStreamSynchronize(s));
     return CHUB_OK;
+}
+
+extern "C" int chub_step_host(chub_engine *e, const float *actions_host, float *obs_host, float *reward_host,
+                              uint8_t *done_host, void *stream) {
+    if (!e || !actions_host) return fail(CHUB_ERR_ARG, "chub_step_host: null argument");
+    return step_host_impl(e, actions_host, nullptr, obs_host, reward_host, done_host, stream);
+}
+
+// The same pipeline for a host producer that already holds switch decisions: 16-byte records in, nothing to threshold.
+extern "C" int chub_step_host_packed(chub_engine *e, const void *records_host, float *obs_host, float *reward_host,
+                                     uint8_t *done_host, void *stream) {
+    if (!e || !records_host) return fail(CHUB_ERR_ARG, "chub_step_host_packed: null argument");
+    if (reinterpret_cast<uintptr_t>(records_host) & 15u) return fail(CHUB_ERR_ARG, "chub_step_host_packed: records must be 16-byte aligned");
+    return step_host_impl(e, nullptr, (const uint4 *) records_host, obs_host, reward_host, done_host, stream);
 }
 
 extern "C" int chub_reset_host(chub_engine *e, float *obs_host, void *stream) {
@@ -796,11 +845,12 @@ extern "C" int chub_rollout_capture(chub_engine *e, const float *actions_dev, in
         own = true;
     }
     CK(cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal));
+    unsigned long long tickets = 0;
     for (int j = 0; j < n_steps; ++j) {  // the step offset is baked per node; one tick per replay
         P.step_offset = j;
-        chub_launch_step(P, cap);
+        chub_launch_step(P, cap, &tickets);
     }
-    chub_launch_tick(e->step_index, n_steps, cap);
+    chub_launch_tick(e->step_index, n_steps, e->queue + 1, tickets * (unsigned long long) n_steps, cap);
     cudaError_t ce = cudaStreamEndCapture(cap, &e->graph);
     if (own) cudaStreamDestroy(cap);
     if (ce != cudaSuccess) return fail(CHUB_ERR_CUDA, std::string("capture: ") + cudaGetErrorString(ce));

@@ -6,7 +6,10 @@
 // HERE, next to the memory they live in, and only {64 on-bits, a[-2], a[-1]} = 16 bytes per hub cross the bus.
 // This is input marshalling, not stepping: nothing of the hub dynamics runs on the host.
 #include <immintrin.h>
+#include <pthread.h>
+#include <sched.h>
 #include <stddef.h>
+#include <stdlib.h>
 #include <stdint.h>
 #include <string.h>
 
@@ -176,6 +179,30 @@ extern "C" ChubPackPool *chub_pack_pool_create(int32_t n_threads) {
     ChubPackPool *p = new ChubPackPool();
     p->idle.store(n_threads);
     for (int i = 0; i < n_threads; ++i) p->workers.emplace_back([p] { p->run(); });
+    return p;
+}
+
+extern "C" ChubPackPool *chub_pack_pool_create_on(int32_t n_threads, const char *cpulist) {
+    ChubPackPool *p = chub_pack_pool_create(n_threads);
+#if defined(__linux__)
+    if (p && cpulist) {
+        cpu_set_t set;
+        CPU_ZERO(&set);
+        int n_set = 0;
+        for (const char *c = cpulist; *c;) {   // "a-b,c,d-e"
+            char *end;
+            long a = strtol(c, &end, 10);
+            if (end == c) break;
+            long b = a;
+            if (*end == '-') { c = end + 1; b = strtol(c, &end, 10); }
+            for (long k = a; k <= b && k < CPU_SETSIZE; ++k) { CPU_SET((int) k, &set); ++n_set; }
+            c = (*end == ',') ? end + 1 : end;
+            if (*end != ',') break;
+        }
+        if (n_set > 0)
+            for (auto &t : p->workers) pthread_setaffinity_np(t.native_handle(), sizeof set, &set);
+    }
+#endif
     return p;
 }
 

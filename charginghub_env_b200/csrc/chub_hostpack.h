@@ -11,6 +11,8 @@ typedef struct ChubPackPool ChubPackPool;
 // na_row: per-row na, or NULL -> na_all.  out: [n_rows] records {bits lo, bits hi, a[-2], a[-1]} (16 bytes each).
 void chub_pack_rows(const float *rows, int32_t stride, const int32_t *na_row, int32_t na_all, int64_t n_rows, void *out);
 ChubPackPool *chub_pack_pool_create(int32_t n_threads);
+// the same with the workers confined to a set of CPUs given as a sysfs cpulist ("0-15,32-47"); NULL = anywhere
+ChubPackPool *chub_pack_pool_create_on(int32_t n_threads, const char *cpulist);
 void chub_pack_pool_destroy(ChubPackPool *p);
 int32_t chub_pack_pool_threads(const ChubPackPool *p);
 int32_t chub_pack_pool_start(ChubPackPool *p, const float *rows, int32_t stride, const int32_t *na_row, int32_t na_all,

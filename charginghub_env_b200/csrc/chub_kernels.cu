@@ -11,6 +11,7 @@
 // touches the action matrix.  Charger assignment ("first k empty piles", CHS.hpp:417-451) is a
 // running count inside the single ascending pass; no list is built.
 #define CHUB_KERNEL_TU
+#include <algorithm>
 #include "chub_kernels.cuh"
 #include "../../include/chub_exo.h"
 
@@ -733,6 +734,21 @@ __device__ __noinline__ StationIO station_step_cp(const ChubParams &P, Scr<Q> S,
     return io;
 }
 
+// One hub tile (32 consecutive hubs, one per lane) through the whole step.
+template <int Q>
+__device__ __forceinline__ void step_tile(const ChubParams &P, Scr<Q> S, const float *tl_s, const int h);
+
+// The kernel is persistent: one block per SM, and inside it the warps that share a sub-core (warp w runs on SM sub-partition
+// w % 4) form a GROUP that pulls units of WARPS/4 consecutive tiles from a global ticket counter until the batch is used up.
+// Why groups and tickets: a hub's cost follows its time of day (quiet night: 10 k warp instructions per tile, every pile
+// occupied: 25 k, the resetting step: 32 k), so in a batch whose hubs are NOT all at the same time of day (staggered
+// resets, truncation) blocks differ 3.5x in duration and four block rounds per SM leave the last SMs a long tail (measured:
+// SMs 81 % busy); units a quarter of a block, handed out dynamically, even that out.  Why per sub-core: warps at different
+// times of day execute different parts of a 64 KB loop body, and mixing them on ONE sub-core's instruction cache costs
+// a quarter of the issue slots (measured: no_instruction stalls 2.7 % -> 24 %); a group keeps one sub-core on one unit, whose
+// tiles are neighbours in the batch and therefore, for any batch de-phased in groups of >= WARPS/4 warps, in step.
+// Ticket u of launch j of an epoch is atomicAdd(queue) - (*queue_base + j * stride); every group draws exactly one
+// ticket beyond the end, so a launch advances the counter by stride = units + groups and the tick kernel moves the base.
 template <int WARPS, int MINB, int Q>
 __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __grid_constant__ ChubParams P) {
     unsigned char *const smem = chub_smem;
@@ -742,14 +758,35 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
         reinterpret_cast<uint32_t *>(smem)[i] = reinterpret_cast<const uint32_t *>(kLogTab)[i];
     float *const tl_w = reinterpret_cast<float *>(smem + CHUB_LOG_N * 16);   // then the two curve-charging s2t(target) tables
     for (int i = threadIdx.x; i < 2000; i += WARPS * 32) tl_w[i] = __ldg(&P.s2t_lut[i]);
+    __shared__ unsigned long long ticket[2][4];
     __syncthreads();
     Scr<Q> S;
     S.base = (uint32_t) __cvta_generic_to_shared(chub_smem + CHUB_SMEM_TABLES + (threadIdx.x >> 5) * P.ws_bytes);
     S.lane = threadIdx.x & 31;
     asm volatile("" : "+r"(S.base), "+r"(S.lane));
 
+    if (P.queue == nullptr) {   // static mapping: block b owns tiles [b * WARPS, (b + 1) * WARPS) (ranged launches of the host pipeline)
+        step_tile<Q>(P, S, tl_s, P.h_begin + blockIdx.x * (WARPS * 32) + threadIdx.x);
+        return;
+    }
+    static_assert(WARPS % 4 == 0, "a group is the warps of one sub-core");
+    constexpr int GW = WARPS / 4;                    // warps per group = tiles per unit
+    const int warp = threadIdx.x >> 5, group = warp & 3, gw = warp >> 2;
+    const unsigned long long first = *P.queue_base + (unsigned long long) P.step_offset * (unsigned long long) P.queue_stride;
+    const long long n_units = ((long long) (P.h_end - P.h_begin) + GW * 32 - 1) / (GW * 32);
+    for (int it = 0;; ++it) {
+        if (gw == 0 && S.lane == 0) ticket[it & 1][group] = atomicAdd(P.queue, 1ull) - first;
+        asm volatile("bar.sync %0, %1;" ::"r"(group + 1), "r"(GW * 32) : "memory");   // the group's own barrier
+        const long long u = (long long) ticket[it & 1][group];
+        if (u >= n_units) break;
+        const long long h0 = (long long) P.h_begin + (u * GW + gw) * 32;
+        if (h0 < (long long) P.h_end) step_tile<Q>(P, S, tl_s, (int) h0 + S.lane);   // the last unit may be short of tiles
+    }
+}
+
+template <int Q>
+__device__ __forceinline__ void step_tile(const ChubParams &P, Scr<Q> S, const float *tl_s, const int h) {
     const unsigned full = 0xffffffffu;
-    const int h = P.h_begin + blockIdx.x * (WARPS * 32) + threadIdx.x;
     const bool active = h < P.h_end;
     const int ci = (active && P.cls) ? __ldg(&P.cls[h]) : 0;
     const ChubClass &c = P.classes[ci];
@@ -776,12 +813,6 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
         rng.k0 = key.x; rng.k1 = key.y; rng.lcg = a.x; rng.uctr = a.y;
         az = a.z; aw = a.w;
     }
-    if (active && (P.phase_sync & 4)) {   // optional: start the warp's pile rows on their way from HBM to L2
-        const uint4 *q = P.pile + chub_pile_index(h, 0, P.S0 + P.S1);
-        for (int i = 0; i < n0; ++i) asm volatile("prefetch.global.L2 [%0];" ::"l"(q + i * 32));
-        q += P.S0 * 32;
-        for (int i = 0; i < n1; ++i) asm volatile("prefetch.global.L2 [%0];" ::"l"(q + i * 32));
-    }
 
     // ---- the two EV stations, station 0 first (Aggregator_Simple.py:141-142); the whole warp takes part ----
     const int lane_ = S.lane;
@@ -791,7 +822,6 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
         const uint32_t abits = s ? (uint32_t) (bits >> n0) : (uint32_t) bits, occ_s = s ? occ.y : occ.x;
         const bool curve = active && !c.constant;
         StationOut o = {};
-        if (P.phase_sync & 1) __syncthreads();   // keep the block's warps in the same code region (instruction cache)
         const bool m_slow = curve && type == CHUB_SLOW, m_fast = curve && type == CHUB_FAST;
         if (__any_sync(full, m_fast)) station_step<CHUB_FAST, 0, Q>(P, S, tl_s, m_fast, h, slot0, n, t, line, abits, occ_s, rng, err, o);
         if (__any_sync(full, m_slow)) station_step<CHUB_SLOW, 0, Q>(P, S, tl_s, m_slow, h, slot0, n, t, line, abits, occ_s, rng, err, o);
@@ -808,7 +838,6 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
         S->park[s][2][lane_] = __float_as_uint(o.now); S->park[s][3][lane_] = o.occ;
         S->park[s][4][lane_] = (uint32_t) (o.line & 0xff) | ((uint32_t) (o.flow & 0xff) << 8) | ((uint32_t) o.incomplete << 16);
     }
-    if (P.phase_sync & 2) __syncthreads();
     if (!active) return;
     // what only the hub section needs is fetched or unpacked now: store mass, exogenous traces, the two analog actions
     HubVars v;
@@ -1024,7 +1053,10 @@ __global__ void chub_s2t_lut_kernel(float *out) {
 }
 void chub_launch_s2t_lut(float *out, cudaStream_t s) { chub_s2t_lut_kernel<<<(4000 + 127) / 128, 128, 0, s>>>(out); }
 
-__global__ void chub_tick_kernel(long long *step_index, int n) { *step_index += n; }
+__global__ void chub_tick_kernel(long long *step_index, int n, unsigned long long *queue_base, unsigned long long tickets) {
+    *step_index += n;
+    if (queue_base) *queue_base += tickets;   // the launches since the last tick drew this many tickets (see chub_step_kernel)
+}
 
 template <int Q>
 static int step_scratch_bytes(const ChubParams &p) {
@@ -1035,7 +1067,7 @@ static int step_scratch_bytes(const ChubParams &p) {
     return ws;
 }
 template <int WARPS, int MINB, int Q>
-static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s) {
+static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s, unsigned long long *tickets) {
     ChubParams p = p0;
     p.ws_bytes = step_scratch_bytes<Q>(p);
     const size_t smem = CHUB_SMEM_TABLES + (size_t) WARPS * p.ws_bytes;
@@ -1044,12 +1076,23 @@ static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s) {
     cudaError_t r = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
     if (r != cudaSuccess) return r;
     const int block = WARPS * 32;
-    kern<<<(p.h_end - p.h_begin + block - 1) / block, block, smem, s>>>(p);
+    const long long hubs = (long long) p.h_end - p.h_begin;
+    long long grid = (hubs + block - 1) / block;
+    if (p.queue) {   // persistent: one block per SM (at most one group per unit), groups draw units of WARPS/4 tiles
+        const long long unit = (WARPS / 4) * 32, units = (hubs + unit - 1) / unit;
+        const long long sms = (p.num_sms > 0 ? p.num_sms : 148) * MINB;
+        grid = std::min(sms, (units + 3) / 4);
+        p.queue_stride = (unsigned long long) (units + 4 * grid);
+        if (tickets) *tickets = p.queue_stride;
+    } else if (tickets) {
+        *tickets = 0;
+    }
+    kern<<<(unsigned) grid, block, smem, s>>>(p);
     return cudaSuccess;
 }
-// Launch shape.  One block per SM; the step's duration is (rounds of blocks over the SMs) x (warps per block) to
-// within a few per cent for 16..28 warps (measured), so the block size is chosen to waste the least of the last
-// round: 524,288 hubs are 3.95 rounds of 28-warp blocks but 4.6 of 24-warp ones.  CHUB_BLOCK overrides.
+// Launch shape.  One block per SM.  Large blocks run a tile cheaper than small ones (measured: 28 warps 1.00, 16 warps
+// 1.12, 8 warps 1.2, 4 warps 1.3 per tile), so the shape is the largest that still gives every SM a block's worth of
+// tiles; below that small blocks spread a small batch over the SMs.  CHUB_BLOCK overrides (warps * 100 + 10).
 // ---- scalar-load dispatch: the stations' evs_step(float) (CHS.hpp:1169-1186 slow, 1478-1495 fast) ----
 // The reference clamps the station's power target to [min_power, max_power] (catch_load, CHS.hpp:358-366), orders the
 // piles by urgency (a multimap keyed by -emergency: ties keep pile order, CHS.hpp:1375-1390) and switches cars on along
@@ -1288,39 +1331,33 @@ void chub_launch_stats_sums(const float4 *stats, int H, double *partial, double 
     chub_stats_final_kernel<<<1, 32, 0, s>>>(partial, sums);
 }
 
-cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s) {
+cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s, unsigned long long *tickets) {
     int shape = p.block;
     if (shape == 0) {
         const int ws = step_scratch_bytes<0>(p), sms = p.num_sms > 0 ? p.num_sms : 148;
+        const long long tiles = ((long long) (p.h_end - p.h_begin) + 31) / 32;
         const int NC = 6;
-        const int cand[NC] = {28, 24, 20, 16, 8, 4};                         // small blocks spread a small batch over the SMs
-        const double cost_per_warp[NC] = {1.00, 1.005, 1.085, 1.12, 1.2, 1.3};  // relative, from the measured sweeps
-        double best = 1e300;
+        const int cand[NC] = {28, 24, 20, 16, 8, 4};
+        shape = 410;
         for (int k = 0; k < NC; ++k) {
-            if (CHUB_SMEM_TABLES + cand[k] * ws + 1024 > 227 * 1024) continue;
-            const long long blocks = ((long long) (p.h_end - p.h_begin) + cand[k] * 32 - 1) / (cand[k] * 32);
-            const long long rounds = (blocks + sms - 1) / sms;
-            const double cost = (double) rounds * cand[k] * cost_per_warp[k];
-            if (cost < best) { best = cost; shape = cand[k] * 100 + 10; }
+            if (CHUB_SMEM_TABLES + cand[k] * ws + 1024 > 227 * 1024) continue;   // the warps' scratch must fit
+            if (tiles >= (long long) cand[k] * sms || cand[k] == 4) { shape = cand[k] * 100 + 10; break; }
         }
-        if (shape == 0) shape = 1220;
     }
     switch (shape) {  // warps per block * 100 + min blocks per SM * 10
-        case 1620: return launch_step_variant<16, 2, 0>(p, s);
-        case 1220: return launch_step_variant<12, 2, 0>(p, s);
-        case 830: return launch_step_variant<8, 3, 0>(p, s);
-        case 410: return launch_step_variant<4, 1, 0>(p, s);
-        case 810: return launch_step_variant<8, 1, 0>(p, s);
-        case 1610: return launch_step_variant<16, 1, 0>(p, s);
-        case 2010: return launch_step_variant<20, 1, 0>(p, s);
-        case 2410: return launch_step_variant<24, 1, 0>(p, s);
-        case 2810: return launch_step_variant<28, 1, 0>(p, s);
-        case 3210: return launch_step_variant<32, 1, 0>(p, s);
-        default: return launch_step_variant<12, 2, 0>(p, s);
+        case 410: return launch_step_variant<4, 1, 0>(p, s, tickets);
+        case 810: return launch_step_variant<8, 1, 0>(p, s, tickets);
+        case 1610: return launch_step_variant<16, 1, 0>(p, s, tickets);
+        case 2010: return launch_step_variant<20, 1, 0>(p, s, tickets);
+        case 2410: return launch_step_variant<24, 1, 0>(p, s, tickets);
+        case 2810: return launch_step_variant<28, 1, 0>(p, s, tickets);
+        default: return launch_step_variant<16, 1, 0>(p, s, tickets);
     }
 }
 void chub_launch_reset(const ChubParams &p, cudaStream_t s) {
     const int block = 128;
     chub_reset_kernel<<<(p.H + block - 1) / block, block, 0, s>>>(p);
 }
-void chub_launch_tick(long long *step_index, int n, cudaStream_t s) { chub_tick_kernel<<<1, 1, 0, s>>>(step_index, n); }
+void chub_launch_tick(long long *step_index, int n, unsigned long long *queue_base, unsigned long long tickets, cudaStream_t s) {
+    chub_tick_kernel<<<1, 1, 0, s>>>(step_index, n, queue_base, tickets);
+}

@@ -37,11 +37,14 @@ struct ChubParams {
     int h_begin, h_end;               // hub range of this launch (h_begin a multiple of 32); the whole batch by default
     int n_classes, action_stride, auto_reset, diagnostics;
     int trace_len, trace_per_hub;
-    int block, phase_sync;            // launch shape of the step kernel (see chub_launch_step); phase_sync: block barriers between code regions
+    int block, phase_sync;            // launch shape override of the step kernel (see chub_launch_step); phase_sync: unused
     int num_sms;                      // SMs of the device (launch-shape choice)
     int ws_bytes;                     // bytes of shared-memory scratch per warp (set by chub_launch_step)
     int step_offset;                  // added to *step_index (graph-captured rollouts bake 0..n-1)
     const long long *step_index;      // device: absolute step index of the state being left
+    unsigned long long *queue;        // device: ticket counter of the persistent step kernel; NULL = static block -> tile mapping
+    const unsigned long long *queue_base;   // device: the counter's value when the current epoch (since the last tick) began
+    unsigned long long queue_stride;  // tickets one launch draws (set by chub_launch_step)
     uint4 *pile;
     float *arrive;
     uint4 *hubA;
@@ -76,13 +79,13 @@ struct ChubParams {
     const uint8_t *reset_mask;        // reset kernel only
 };
 
-cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s);
+cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s, unsigned long long *tickets = nullptr);
 void chub_launch_reset(const ChubParams &p, cudaStream_t s);
 void chub_launch_situation(const ChubParams &p, float *out, cudaStream_t s);
 void chub_launch_report(const ChubParams &p, int h, double *out, cudaStream_t s);
 void chub_launch_dispatch(const ChubParams &p, unsigned long long *act_bits, cudaStream_t s);
 void chub_launch_s2t_lut(float *out, cudaStream_t s);
-void chub_launch_tick(long long *step_index, int n, cudaStream_t s);
+void chub_launch_tick(long long *step_index, int n, unsigned long long *queue_base, unsigned long long tickets, cudaStream_t s);
 #define CHUB_STATS_BLOCKS 296
 void chub_launch_stats_sums(const float4 *stats, int H, double *partial, double *sums, cudaStream_t s);
 void chub_launch_curve_sweep(int which, uint32_t first_bits, long long n, float *out, cudaStream_t s);

@@ -328,6 +328,24 @@ class HubEngine(object):
                                       _dptr(hb["done"]), ctypes.c_void_p(int(stream))))
         return hb["obs"], hb["reward"], hb["done"]
 
+    def pinned_records(self):
+        """A pinned uint32 [n_hubs, 4] array for step_host_packed (kept alive by the engine)."""
+        p = ctypes.c_void_p()
+        check(self.lib.chub_alloc_host(self.n_hubs * 16, ctypes.byref(p)))
+        a = np.ctypeslib.as_array((ctypes.c_uint32 * (self.n_hubs * 4)).from_address(p.value)).reshape(self.n_hubs, 4)
+        self.host_buffers()["ptrs"].append(p)
+        return a
+
+    def step_host_packed(self, records, stream=0):
+        """Host-buffer step on ready-made 16-byte records (uint32 [n_hubs, 4] host array: on-bits lo, hi, a[-2], a[-1] as
+        float bits -- pack_actions() makes them): records host->device, step, obs/reward/done back to the pinned arrays."""
+        hb = self.host_buffers()
+        if records.dtype != np.uint32 or not records.flags["C_CONTIGUOUS"] or records.shape != (self.n_hubs, 4):
+            raise ValueError("records must be a C-contiguous uint32 [%d, 4] array" % self.n_hubs)
+        check(self.lib.chub_step_host_packed(self.h, _dptr(records), _dptr(hb["obs"]), _dptr(hb["reward"]),
+                                             _dptr(hb["done"]), ctypes.c_void_p(int(stream))))
+        return hb["obs"], hb["reward"], hb["done"]
+
     def set_host_threads(self, n_threads, n_ranges=0):
         """Threads that threshold the action rows inside step_host (0: float rows cross PCIe unpacked) and the number of
         hub ranges of its pipeline (0: keep)."""

@@ -207,6 +207,12 @@ int chub_step_packed(chub_engine *e, const void *packed_dev, void *stream);
  * chub_pack_actions is the packing alone: [n_hubs][action_stride] host rows -> [n_hubs] host records. */
 int chub_step_host(chub_engine *e, const float *actions_host, float *obs_host, float *reward_host,
                    uint8_t *done_host, void *stream);
+/* chub_step_host for a HOST producer that already holds switch decisions: records_host = [n_hubs] 16-byte records of
+ * chub_step_packed in host memory (pinned for full overlap; 16-byte aligned).  Same pipeline -- records host->device,
+ * step kernel, results device->host, range by range -- minus the thresholding: 16 bytes per hub cross the host's memory
+ * system instead of 4 * action_stride, which is what bounds chub_step_host when several GPUs share one host. */
+int chub_step_host_packed(chub_engine *e, const void *records_host, float *obs_host, float *reward_host,
+                          uint8_t *done_host, void *stream);
 int chub_reset_host(chub_engine *e, float *obs_host, void *stream);
 int chub_set_host_threads(chub_engine *e, int32_t n_threads, int32_t n_ranges);
 int chub_pack_actions(chub_engine *e, const float *actions_host, void *packed_host);

@@ -13,6 +13,8 @@ ap.add_argument("--warm", type=int, default=40)
 ap.add_argument("--steps", type=int, default=3)
 ap.add_argument("--workload", default="config5")
 ap.add_argument("--control", default="piles", choices=["piles", "loads"])
+ap.add_argument("--phase", default="lockstep", choices=["lockstep", "spread", "spread-warps", "spread-blocks"],
+                help="spread: de-phase the batch first (bench.dephase) -- every launch then holds every time of day")
 a = ap.parse_args()
 tabs = load_tables()
 wl = bench.workload(a.workload, tabs)
@@ -25,6 +27,8 @@ eng.reset()
 if a.control == "loads":   # one power target per station: [load0 kW, load1 kW, a[-2], a[-1]]
     caps = torch.tensor([[40.0 * n for n in wl["classes"][0]["station_list"]]], device="cuda")
     acts = torch.cat([torch.rand((H, 2), device="cuda") ** 2 * caps, torch.rand((H, 2), device="cuda") * 2 - 1], dim=1).contiguous()
+if a.phase != "lockstep":
+    bench.dephase(eng, H, eng.step_loads if a.control == "loads" else eng.step, [acts], a.phase)
 for _ in range(a.warm + a.steps):
     (eng.step_loads if a.control == "loads" else eng.step)(acts)
 torch.cuda.synchronize()
