@@ -52,6 +52,8 @@ struct chub_engine {
     float *obs = nullptr, *reward = nullptr; uint8_t *done = nullptr; double *diag = nullptr; float *st_power = nullptr;
     long long *step_index = nullptr;
     unsigned long long *queue = nullptr;   // [0] ticket counter, [1] its value at the start of the epoch (chub_step_kernel)
+    unsigned char *lpt = nullptr;          // the step kernel's cost-binned unit lists
+    int lpt_cap = 0;
     int num_sms = 0;
     float *actions_stage = nullptr;  // device copy target of chub_step_host when the rows travel unpacked (host_threads == 0)
     uint4 *packed_stage = nullptr;   // device copy target of chub_step_host: one packed record per hub
@@ -117,7 +119,7 @@ static void engine_free(chub_engine *e) {
     if (e->comm_done) cudaEventDestroy(e->comm_done);
     void *ptrs[] = {e->pile, e->arrive, e->hubA, e->store, e->keys, e->occ, e->cls, e->stats, e->last_stats, e->err, e->qsoc,
                     e->d_classes, e->d_el, e->lut, e->s2t_lut, e->pv, e->wd, e->price_tr, e->obs, e->reward, e->done, e->diag,
-                    e->st_power, e->step_index, e->queue, e->actions_stage, e->exo_d, e->exo_i, e->pv_days, e->wd_days, e->act_bits, e->final_soc, e->packed_stage, e->report_dev,
+                    e->st_power, e->step_index, e->queue, e->lpt, e->actions_stage, e->exo_d, e->exo_i, e->pv_days, e->wd_days, e->act_bits, e->final_soc, e->packed_stage, e->report_dev,
                     e->stats_stage, e->stats_partial, e->stats_sums};
     for (void *p : ptrs)
         if (p) cudaFree(p);
@@ -158,6 +160,8 @@ extern "C" int chub_create(const chub_config *cfg, chub_engine **out) {
     A(dalloc(&e->qsoc, Hp * CHUB_FCEV_QCAP)); A(dalloc(&e->lut, (size_t) 96 * 1000)); A(dalloc(&e->s2t_lut, (size_t) 4000));
     A(dalloc(&e->obs, Hp * CHUB_OBS_DIM)); A(dalloc(&e->reward, Hp)); A(dalloc(&e->done, Hp));
     A(dalloc(&e->step_index, 1)); A(dalloc(&e->queue, 2));
+    e->lpt_cap = (e->Hpad / 32 + 3) / 4;   // units of >= 4 tiles (the smallest launch shape)
+    A(dalloc(&e->lpt, CHUB_LPT_BYTES(e->lpt_cap)));
     if (cfg->diagnostics) { A(dalloc(&e->diag, Hp * CHUB_D_COUNT)); A(dalloc(&e->st_power, Hp * 6)); }
     if (r != cudaSuccess) {
         engine_free(e);
@@ -509,6 +513,7 @@ static int fill_params(chub_engine *e, ChubParams &P) {
     P.trace_len = e->trace_len; P.trace_per_hub = e->trace_per_hub;
     P.step_offset = 0; P.step_index = e->step_index; P.num_sms = e->num_sms;
     P.queue = getenv("CHUB_STATIC_GRID") ? nullptr : e->queue; P.queue_base = e->queue + 1; P.queue_stride = 0;
+    P.lpt = e->lpt; P.lpt_cap = e->lpt_cap;
     {   // experiment knobs (defaults are the measured best)
         const char *b = getenv("CHUB_BLOCK"), *y = getenv("CHUB_PHASE_SYNC");
         P.block = b ? atoi(b) : 0;

@@ -534,9 +534,16 @@ __device__ __forceinline__ void hub_store(const ChubParams &P, int h, const HubV
 __device__ __forceinline__ void trace_at(const ChubParams &P, int h, long long k, int t, int t_read, double &pv, double &wd,
                                          double &pr) {
     const long long d = k - (long long) t;
-    const long long day = d >= 0 ? d / CHUB_DAY : -((CHUB_DAY - 1 - d) / CHUB_DAY);
-    long long m = (day * CHUB_DAY + (long long) t_read) % (long long) P.trace_len;
-    if (m < 0) m += P.trace_len;
+    uint32_t m;
+    if ((unsigned long long) d < 0x7fff0000ull) {   // every practical rollout: 32-bit arithmetic, division by a constant
+        m = ((uint32_t) d / (uint32_t) CHUB_DAY) * (uint32_t) CHUB_DAY + (uint32_t) t_read;
+        if (m >= (uint32_t) P.trace_len) m %= (uint32_t) P.trace_len;
+    } else {
+        const long long day = d >= 0 ? d / CHUB_DAY : -((CHUB_DAY - 1 - d) / CHUB_DAY);
+        long long mm = (day * CHUB_DAY + (long long) t_read) % (long long) P.trace_len;
+        if (mm < 0) mm += P.trace_len;
+        m = (uint32_t) mm;
+    }
     size_t i = (size_t) m;
     if (P.trace_per_hub) i = i * (size_t) P.Hpad + h;
     pv = __ldg(&P.pv[i]); wd = __ldg(&P.wd[i]); pr = __ldg(&P.price_tr[i]);
@@ -738,17 +745,27 @@ __device__ __noinline__ StationIO station_step_cp(const ChubParams &P, Scr<Q> S,
 template <int Q>
 __device__ __forceinline__ void step_tile(const ChubParams &P, Scr<Q> S, const float *tl_s, const int h);
 
-// The kernel is persistent: one block per SM, and inside it the warps that share a sub-core (warp w runs on SM sub-partition
-// w % 4) form a GROUP that pulls units of WARPS/4 consecutive tiles from a global ticket counter until the batch is used up.
-// Why groups and tickets: a hub's cost follows its time of day (quiet night: 10 k warp instructions per tile, every pile
-// occupied: 25 k, the resetting step: 32 k), so in a batch whose hubs are NOT all at the same time of day (staggered
-// resets, truncation) blocks differ 3.5x in duration and four block rounds per SM leave the last SMs a long tail (measured:
-// SMs 81 % busy); units a quarter of a block, handed out dynamically, even that out.  Why per sub-core: warps at different
-// times of day execute different parts of a 64 KB loop body, and mixing them on ONE sub-core's instruction cache costs
-// a quarter of the issue slots (measured: no_instruction stalls 2.7 % -> 24 %); a group keeps one sub-core on one unit, whose
-// tiles are neighbours in the batch and therefore, for any batch de-phased in groups of >= WARPS/4 warps, in step.
-// Ticket u of launch j of an epoch is atomicAdd(queue) - (*queue_base + j * stride); every group draws exactly one
-// ticket beyond the end, so a launch advances the counter by stride = units + groups and the tick kernel moves the base.
+// The kernel is persistent: one block per SM pulls UNITS of WARPS consecutive tiles (what a block of the static grid would
+// own) from a ticket counter until the batch is used up, heaviest units first.
+// Why: a hub's cost follows its time of day (quiet night: 10 k warp instructions per tile, every pile occupied: 25 k, the
+// resetting step: 32 k).  In a batch whose hubs are not all at the same time of day (staggered resets, truncation) units
+// differ 3.5x in duration, and with only four units per SM the order they are handed out in decides how long the last SMs
+// run alone (measured with the static grid: SMs 81 % busy).  Longest-first is the classic remedy; the cost of a unit is
+// what it took in the PREVIOUS launch (a day moves one step at a time), measured with clock64 and binned into
+// CHUB_LPT_BINS bins of 8192 cycles: a finished unit appends itself to its bin's list, the next launch walks the bins from
+// the top.  No sort, one atomic per unit.  A unit stays on ONE SM with all its warps: warps at different times of day run
+// different parts of a 64 KB loop body, and mixing them on one SM costs a quarter of the issue slots in instruction-cache
+// misses (measured: no_instruction stalls 2.7 % -> 24 %; handing quarter-units to the four sub-cores separately: the same).
+// Tickets: unit k of launch j of an epoch is atomicAdd(queue) - (*queue_base + j * stride); every block draws exactly one
+// ticket past the end, so a launch advances the counter by stride = units + blocks and the tick kernel moves the base.
+// The lists are double buffered by the parity of the absolute step; a list that does not hold exactly this launch's
+// units (first launch, other batch range or shape) is ignored and units go out in index order.
+#define CHUB_LPT_BINS 64
+struct LptList {            // one per parity, in global memory: head[0] = units the list was built for, then the bins
+    int n_units, done_blocks, pad[2];
+    int count[CHUB_LPT_BINS];
+    // int unit[CHUB_LPT_BINS][cap] follows
+};
 template <int WARPS, int MINB, int Q>
 __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __grid_constant__ ChubParams P) {
     unsigned char *const smem = chub_smem;
@@ -758,29 +775,88 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
         reinterpret_cast<uint32_t *>(smem)[i] = reinterpret_cast<const uint32_t *>(kLogTab)[i];
     float *const tl_w = reinterpret_cast<float *>(smem + CHUB_LOG_N * 16);   // then the two curve-charging s2t(target) tables
     for (int i = threadIdx.x; i < 2000; i += WARPS * 32) tl_w[i] = __ldg(&P.s2t_lut[i]);
-    __shared__ unsigned long long ticket[2][4];
+    __shared__ int s_unit;
+    __shared__ long long s_t0;
     __syncthreads();
     Scr<Q> S;
     S.base = (uint32_t) __cvta_generic_to_shared(chub_smem + CHUB_SMEM_TABLES + (threadIdx.x >> 5) * P.ws_bytes);
     S.lane = threadIdx.x & 31;
     asm volatile("" : "+r"(S.base), "+r"(S.lane));
 
-    if (P.queue == nullptr) {   // static mapping: block b owns tiles [b * WARPS, (b + 1) * WARPS) (ranged launches of the host pipeline)
-        step_tile<Q>(P, S, tl_s, P.h_begin + blockIdx.x * (WARPS * 32) + threadIdx.x);
-        return;
-    }
-    static_assert(WARPS % 4 == 0, "a group is the warps of one sub-core");
-    constexpr int GW = WARPS / 4;                    // warps per group = tiles per unit
-    const int warp = threadIdx.x >> 5, group = warp & 3, gw = warp >> 2;
-    const unsigned long long first = *P.queue_base + (unsigned long long) P.step_offset * (unsigned long long) P.queue_stride;
-    const long long n_units = ((long long) (P.h_end - P.h_begin) + GW * 32 - 1) / (GW * 32);
-    for (int it = 0;; ++it) {
-        if (gw == 0 && S.lane == 0) ticket[it & 1][group] = atomicAdd(P.queue, 1ull) - first;
-        asm volatile("bar.sync %0, %1;" ::"r"(group + 1), "r"(GW * 32) : "memory");   // the group's own barrier
-        const long long u = (long long) ticket[it & 1][group];
-        if (u >= n_units) break;
-        const long long h0 = (long long) P.h_begin + (u * GW + gw) * 32;
+    // Nothing of the queue's bookkeeping stays in registers across step_tile (they are the scarce resource there): warp 0
+    // re-derives it from the launch parameters at every draw, and the unit in flight waits in shared memory.
+    // Without a queue (ranged launches of the host pipeline, which run side by side on several streams) the mapping is
+    // static: block b does unit b and leaves.  One loop serves both, so that the tile code exists once.
+    if (threadIdx.x == 0) s_unit = -2;
+    for (;;) {
+        if (P.queue == nullptr) {
+            if (threadIdx.x == 0) s_unit = s_unit == -2 ? (int) blockIdx.x : -1;
+        } else if (threadIdx.x < 32) {   // warp 0: book the finished unit, draw a ticket, turn it into a unit
+            const int lane = threadIdx.x;
+            const int n_units = (int) (((long long) (P.h_end - P.h_begin) + WARPS * 32 - 1) / (WARPS * 32));
+            const int par = (int) ((*P.step_index + P.step_offset) & 1);
+            const size_t list_bytes = sizeof(LptList) + (size_t) CHUB_LPT_BINS * P.lpt_cap * sizeof(int);
+            const LptList *const rd = reinterpret_cast<const LptList *>(P.lpt + par * list_bytes);
+            LptList *const wr = reinterpret_cast<LptList *>(P.lpt + (par ^ 1) * list_bytes);
+            long long k = 0;
+            if (lane == 0) {
+                const int fin = s_unit;
+                if (fin >= 0) {
+                    int bin = (int) ((clock64() - s_t0) >> 13);
+                    bin = bin < 0 ? 0 : (bin >= CHUB_LPT_BINS ? CHUB_LPT_BINS - 1 : bin);
+                    const int at = atomicAdd(&wr->count[bin], 1);
+                    if (at < P.lpt_cap) reinterpret_cast<int *>(wr + 1)[(size_t) bin * P.lpt_cap + at] = fin;
+                }
+                const unsigned long long first = *P.queue_base + (unsigned long long) P.step_offset * P.queue_stride;
+                k = (long long) (atomicAdd(P.queue, 1ull) - first);
+            }
+            k = __shfl_sync(0xffffffffu, k, 0);
+            int u = k < n_units ? (int) k : -1;
+            if (k < n_units) {
+                // bins from the top: lane l looks after bins 63 - 2l and 62 - 2l
+                const int c_hi = rd->count[CHUB_LPT_BINS - 1 - 2 * lane], c_lo = rd->count[CHUB_LPT_BINS - 2 - 2 * lane];
+                int incl = c_hi + c_lo;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (lane >= d) incl += v;
+                }
+                const int total = __shfl_sync(0xffffffffu, incl, 31);
+                if (total == n_units && rd->n_units == n_units) {
+                    const int before = incl - c_hi - c_lo;
+                    const unsigned hit = __ballot_sync(0xffffffffu, (int) k < incl);
+                    const int owner = __ffs(hit) - 1;
+                    if (lane == owner) {
+                        const int r = (int) k - before;
+                        const int bin = r < c_hi ? CHUB_LPT_BINS - 1 - 2 * lane : CHUB_LPT_BINS - 2 - 2 * lane;
+                        u = reinterpret_cast<const int *>(rd + 1)[(size_t) bin * P.lpt_cap + (r < c_hi ? r : r - c_hi)];
+                    }
+                    u = __shfl_sync(0xffffffffu, u, owner);
+                }
+            }
+            if (lane == 0) { s_unit = u; s_t0 = clock64(); }
+        }
+        __syncthreads();
+        const int unit = s_unit;
+        if (unit < 0) break;
+        const long long h0 = (long long) P.h_begin + ((long long) unit * WARPS + (threadIdx.x >> 5)) * 32;
         if (h0 < (long long) P.h_end) step_tile<Q>(P, S, tl_s, (int) h0 + S.lane);   // the last unit may be short of tiles
+        __syncthreads();          // the unit's cost is that of its slowest warp; s_unit may be rewritten after this
+    }
+    // the last block out tags the list it helped write and clears the one everybody has finished reading
+    if (threadIdx.x == 0 && P.queue != nullptr) {
+        const int n_units = (int) (((long long) (P.h_end - P.h_begin) + WARPS * 32 - 1) / (WARPS * 32));
+        const int par = (int) ((*P.step_index + P.step_offset) & 1);
+        const size_t list_bytes = sizeof(LptList) + (size_t) CHUB_LPT_BINS * P.lpt_cap * sizeof(int);
+        LptList *const rd = reinterpret_cast<LptList *>(P.lpt + par * list_bytes);
+        LptList *const wr = reinterpret_cast<LptList *>(P.lpt + (par ^ 1) * list_bytes);
+        __threadfence();
+        if (atomicAdd(&wr->done_blocks, 1) == (int) gridDim.x - 1) {
+            wr->done_blocks = 0;
+            wr->n_units = n_units;
+            rd->n_units = -1;
+            for (int b = 0; b < CHUB_LPT_BINS; ++b) rd->count[b] = 0;
+        }
     }
 }
 
@@ -1078,12 +1154,13 @@ static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s, uns
     const int block = WARPS * 32;
     const long long hubs = (long long) p.h_end - p.h_begin;
     long long grid = (hubs + block - 1) / block;
-    if (p.queue) {   // persistent: one block per SM (at most one group per unit), groups draw units of WARPS/4 tiles
-        const long long unit = (WARPS / 4) * 32, units = (hubs + unit - 1) / unit;
-        const long long sms = (p.num_sms > 0 ? p.num_sms : 148) * MINB;
-        grid = std::min(sms, (units + 3) / 4);
-        p.queue_stride = (unsigned long long) (units + 4 * grid);
-        if (tickets) *tickets = p.queue_stride;
+    if (p.queue) {   // persistent: one block per SM draws units of one block's worth of tiles
+        const long long units = grid;
+        const long long sms = (long long) (p.num_sms > 0 ? p.num_sms : 148) * MINB;
+        grid = std::min(sms, units);
+        p.queue_stride = (unsigned long long) (units + grid);
+        if (units > p.lpt_cap) p.queue = nullptr, grid = units;   // more units than the lists hold: static grid
+        if (tickets) *tickets = p.queue ? p.queue_stride : 0;
     } else if (tickets) {
         *tickets = 0;
     }

@@ -45,6 +45,8 @@ struct ChubParams {
     unsigned long long *queue;        // device: ticket counter of the persistent step kernel; NULL = static block -> tile mapping
     const unsigned long long *queue_base;   // device: the counter's value when the current epoch (since the last tick) began
     unsigned long long queue_stride;  // tickets one launch draws (set by chub_launch_step)
+    unsigned char *lpt;               // device: two unit lists binned by measured cost (see chub_step_kernel)
+    int lpt_cap;                      // units a bin's list can hold
     uint4 *pile;
     float *arrive;
     uint4 *hubA;
@@ -87,6 +89,7 @@ void chub_launch_dispatch(const ChubParams &p, unsigned long long *act_bits, cud
 void chub_launch_s2t_lut(float *out, cudaStream_t s);
 void chub_launch_tick(long long *step_index, int n, unsigned long long *queue_base, unsigned long long tickets, cudaStream_t s);
 #define CHUB_STATS_BLOCKS 296
+#define CHUB_LPT_BYTES(cap) (2 * (272 + (size_t) 64 * (cap) * 4))   // two LptList + their 64 bins of `cap` ints
 void chub_launch_stats_sums(const float4 *stats, int H, double *partial, double *sums, cudaStream_t s);
 void chub_launch_curve_sweep(int which, uint32_t first_bits, long long n, float *out, cudaStream_t s);
 cudaError_t chub_upload_const(const ChubConst &c);

@@ -3,12 +3,12 @@ timeout 900 python -m pytest tests -m gpu -q -x --deselect tests/test_gpu_curves
 run() { name=$1; shift; timeout 300 env "$@" python bench.py --no-cpu --no-ppo --no-e2e --steps 96 $EXTRA > gpurun_out/b_$name.json 2> gpurun_out/b_$name.err; echo "$name rc=$?"; }
 EXTRA="--phase lockstep --steps 192" run lock_persist A=1
 EXTRA="--phase lockstep --steps 192" run lock_static CHUB_STATIC_GRID=1
-EXTRA="--phase spread" run spread7 A=1
-EXTRA="--phase spread-blocks" run spread28 A=1
-EXTRA="--phase spread-warps" run spread1 A=1
-EXTRA="--phase spread" run spread7_static CHUB_STATIC_GRID=1
-EXTRA="--phase spread" run spread7_w24 CHUB_BLOCK=2410
-EXTRA="--phase spread" run spread7_w20 CHUB_BLOCK=2010
+EXTRA="--phase spread" run spread28 A=1
+EXTRA="--phase spread" run spread28_static CHUB_STATIC_GRID=1
+EXTRA="--phase spread --steps 20" run spread28_k20 A=1
+EXTRA="--phase spread-quarters" run spread7 A=1
+EXTRA="--phase spread --workload config3" run c3_spread A=1
+EXTRA="--phase lockstep --workload config3 --steps 192" run c3_lock A=1
 python - <<'PY'
 import json, glob
 for f in sorted(glob.glob("gpurun_out/b_*.json")):

@@ -13,7 +13,7 @@ ap.add_argument("--warm", type=int, default=40)
 ap.add_argument("--steps", type=int, default=3)
 ap.add_argument("--workload", default="config5")
 ap.add_argument("--control", default="piles", choices=["piles", "loads"])
-ap.add_argument("--phase", default="lockstep", choices=["lockstep", "spread", "spread-warps", "spread-blocks"],
+ap.add_argument("--phase", default="lockstep", choices=["lockstep", "spread", "spread-warps", "spread-quarters"],
                 help="spread: de-phase the batch first (bench.dephase) -- every launch then holds every time of day")
 a = ap.parse_args()
 tabs = load_tables()
