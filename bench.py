@@ -75,8 +75,14 @@ def workload(name, tabs):
                                 fc_max_power=float(rs.choice([50, 100, 200])),
                                 fcev_permeate=float(rs.choice([0.005, 0.01, 0.02, 0.05]))))
         H = 262144
-        return dict(H=H, classes=classes, hub_class=rs.randint(0, ncls, H).astype(np.int32), auto_reset=True,
-                    stride=66, scaling="weak", desc="config3: 262,144 heterogeneous hubs (4..32 piles per station), auto-reset")
+        hub_class = rs.randint(0, ncls, H).astype(np.int32)
+        desc = "config3: 262,144 heterogeneous hubs (4..32 piles per station), auto-reset"
+        if not os.environ.get("CHUB_BENCH_UNSORTED"):
+            # hubs are independent and their order is the caller's choice: created class by class (sharding.order_by_class),
+            # a warp holds hubs of one class -- same pile counts, one parameter record -- instead of 32 different ones
+            hub_class = np.sort(hub_class)
+            desc += ", hubs created in class order"
+        return dict(H=H, classes=classes, hub_class=hub_class, auto_reset=True, stride=66, scaling="weak", desc=desc)
     raise SystemExit("unknown workload " + name)
 
 

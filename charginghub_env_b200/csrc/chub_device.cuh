@@ -77,7 +77,7 @@ struct HubRng {
 };
 
 __device__ __forceinline__ int rng_u1000(HubRng &r) {  // rand() % 1000, CHS.hpp:41
-    return (int) (chub_rand31(r.k0, r.k1, r.uctr++) % 1000u);
+    return (int) chub_urand(r.k0, r.k1, r.uctr++);   // already in [0, 1000): the % 1000 of CHS.hpp:41 is the identity on it
 }
 __device__ __forceinline__ float rng_u01(HubRng &r) {  // uniform_rand(0,1): tr*(1-0)+0
     float tr = (float) rng_u1000(r) / 999.0f;

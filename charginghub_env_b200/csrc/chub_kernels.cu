@@ -163,7 +163,7 @@ __device__ __forceinline__ void flat_car_step(const ChubParams &P, Scr<Q> S, con
         const int sl = (head + lane) & (LA_RING - 1);
         const float tt = __uint_as_float(S->la_t[SEG][sl]);
         const uint32_t w = S->la_w[SEG][sl];
-        const uint32_t id = S->la_id[SEG][sl], owner = id & 31u, i = id >> 5;
+        const uint32_t id = S->la_id[SEG][sl], owner = id & 31u;
         float soc, power;
         curve_step<TYPE, CP, SEG>(tt, soc, power);            // car_step, CHS.hpp:900-905 / 1065-1070
         const float tsoc = curve_s2t<TYPE, CP>(soc);
@@ -179,9 +179,9 @@ __device__ __forceinline__ void flat_car_step(const ChubParams &P, Scr<Q> S, con
             r = make_uint4(__float_as_uint(soc), __float_as_uint(tsoc), __float_as_uint(power),
                            ((w + (1u << 6)) & 0xfffu) | PW_CAR | PW_CHARGE | (urgent << 14) | ((uint32_t) cn << 15) |
                                (w & (0x3ffu << 20)));
-            (&S->pw[0][0])[i * 32u + owner] = __float_as_uint(power) | (urgent << 31);
+            (&S->pw[0][0])[id] = __float_as_uint(power) | (urgent << 31);   // id = pile * 32 + owner lane
         }
-        pile0[i * 32u + owner] = r;
+        pile0[id] = r;
     }
     __syncwarp();
 }

@@ -18,6 +18,18 @@ def shard_range(n_total, rank, world):
     return lo, lo + base + (1 if rank < extra else 0)
 
 
+def order_by_class(hub_class):
+    """Permutation that lists the hubs class by class (stable).  Hubs are independent, so a caller is free to CREATE its
+    batch in this order: a warp of the step kernel then holds 32 hubs of one class -- the same pile counts (no lane waits
+    for a neighbour's longer station), one parameter record, one electrolyser table -- instead of 32 different ones.
+    Returns (order, inverse): hub_class[order] is sorted; results[inverse] puts per-hub results back in the old order."""
+    hc = np.asarray(hub_class)
+    order = np.argsort(hc, kind="stable")
+    inverse = np.empty_like(order)
+    inverse[order] = np.arange(len(order))
+    return order, inverse
+
+
 def hub_streams(base_seed, hub_ids):
     """(key0, key1, minstd state) of each global hub id -- Python mirror of chub_hub_streams()."""
     M = (1 << 64) - 1

@@ -4,7 +4,8 @@
  *   U stream: libc rand(), used only as rand() % 1000 / 999.f   (CHS.hpp:35-44)
  *   E stream: std::default_random_engine e  == minstd_rand0     (CHS.hpp:25)
  * A batched engine needs one independent pair per hub.  This header fixes them:
- *   U: counter based, rand() := top 31 bits of a double PCG output hash of (key0, key1, counter);
+ *   U: counter based, rand() := chub_urand(key0, key1, counter), a PCG output hash of the counter reduced to [0, 1000)
+ *      (the reference only ever forms rand() % 1000);
  *   E: the same minstd_rand0 recurrence x <- 16807 x mod (2^31-1), one 31-bit state per hub.
  * It is plain C so the CUDA engine (device code), the C oracle and the reference shim (which
  * interposes rand() with chub_rand31) all consume bit-identical streams.
@@ -30,6 +31,16 @@ CHUB_HD uint32_t chub_pcg32(uint32_t v) {
 /* The value the reference would have obtained from rand(): uniform in [0, 2^31). */
 CHUB_HD uint32_t chub_rand31(uint32_t key0, uint32_t key1, uint32_t counter) {
     return chub_pcg32(chub_pcg32(counter ^ key0) + key1) >> 1;
+}
+
+/* The value the reference obtains from rand() IN THE U STREAM.  CHS.hpp:41 uses it only as rand() % 1000, so the stream is
+ * free to deliver that residue directly: one hash round of the counter, the second key folded in, and a multiply-shift
+ * range reduction to [0, 1000) -- half the instructions of chub_rand31(...) % 1000 on the device, where a busy hub draws
+ * forty of these per step.  The reference shim's rand() returns exactly this value, the oracle and the engine reduce it
+ * with the reference's own % 1000 (a no-op).  (The X stream of chub_exo.h keeps the full-range chub_rand31.) */
+CHUB_HD uint32_t chub_urand(uint32_t key0, uint32_t key1, uint32_t counter) {
+    uint32_t h = chub_pcg32(counter ^ key0) ^ key1;
+    return (uint32_t) (((uint64_t) h * 1000u) >> 32);
 }
 
 /* minstd_rand0 step; state stays in [1, 2^31-2]. */

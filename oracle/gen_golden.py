@@ -47,7 +47,10 @@ KEEP = ["pile_car", "pile_charge", "pile_urgent", "pile_stay", "pile_already", "
         "pile_power", "pile_arrive", "st_line", "st_flow_in", "st_car_number", "st_min_power", "st_charge_power",
         "st_max_power", "hub_t", "hub_uctr", "hub_lcg", "fcev_arrive", "fcev_qn", "hub_done", "store", "store_soc",
         "reward", "income", "hy_flow", "h2_power", "fc_power", "hy_use", "not_meet", "hy_to_use", "demand",
-        "h2_grid", "hy_act", "pv", "wd", "price", "obs"]
+        "h2_grid", "hy_act", "pv", "wd", "price", "obs",
+        # what the reference accumulates and reports at `done` (evcssp_manager.py:259-297; "charge is not complete" prints
+        # of CHS.hpp:916-921 / 1081-1086 counted from its stdout): the payload of the path's one collective
+        "cum_income", "cum_draw", "ep_return", "test_penalty", "deviation", "incomplete"]
 
 
 def main():

@@ -36,7 +36,7 @@ static unsigned long long g_u_calls = 0;
 extern "C" int rand(void) noexcept {
     ++g_u_calls;
     if (g_u_hooked) {
-        return (int) chub_rand31(g_u_key0, g_u_key1, g_u_ctr++);
+        return (int) chub_urand(g_u_key0, g_u_key1, g_u_ctr++);
     }
     static uint32_t s = 12345u;
     s = s * 1103515245u + 12345u;

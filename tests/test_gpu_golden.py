@@ -61,3 +61,15 @@ def test_engine_reproduces_reference_trace(path, tables):
         check(t + 1, obs, rew, done)
     assert eng.counters()["error_or"] == 0
     assert np.allclose(eng.class_table(0), z["el_table"])
+    if T == 96 and "cum_income" in z.files:
+        # the statistics frozen at done and the terminal store SOC against what the REFERENCE accumulated and printed
+        last = eng.tensor("last_stats").cpu().numpy()
+        for col, name in enumerate(("ep_return", "cum_income", "cum_draw")):
+            assert C.close(last[:, col], z[name][96], rtol=1e-6).all(), name
+        assert np.array_equal(last[:, 3], z["incomplete"][96].astype(np.float32))
+        fin = eng.tensor("final_soc").cpu().numpy()
+        assert C.close(fin, z["store_soc"][96], rtol=1e-6).all()
+        vlt = kw.get("hydro_store_vlt")
+        cap_kg = 0.089 * 200 * (5000.0 if vlt is None else vlt)              # hydro_sys.py:94-98, grams / 1000
+        pen = np.abs((fin.astype(np.float64) - kw["init_soc"]) * cap_kg / 0.2)   # VectorHubEnv's soc_penalty="abs"
+        assert C.close(pen, z["test_penalty"][96], rtol=1e-5, atol=1e-7 * cap_kg / 0.2).all()

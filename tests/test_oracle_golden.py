@@ -71,4 +71,10 @@ def test_oracle_reproduces_reference(path, tables):
         rows = z["actions"][t] if loads is None else np.concatenate([loads[t], z["actions"][t][:, -2:]], axis=1)
         orc.step(rows, z["pv"][t + 1], z["wd"][t + 1], z["price"][t + 1])
         check(t + 1)
+        if "cum_income" in z.files:   # the reference's own accumulators and its "charge is not complete" prints
+            for name in ("cum_income", "cum_draw", "ep_return", "deviation"):
+                assert np.allclose(z[name][t + 1], orc.get(name), rtol=1e-12, atol=1e-12), (name, t)
+            assert np.array_equal(z["incomplete"][t + 1], orc.get("st_incomplete").sum(axis=1)), ("incomplete", t)
+    if T == 96 and "cum_income" in z.files:
+        assert np.allclose(z["test_penalty"][96], orc.get("test_penalty"), rtol=1e-12, atol=0)
     assert (orc.get("hub_err") == 0).all()

@@ -26,7 +26,7 @@ for line in open(sass, errors="ignore"):
     if m:
         cur = (os.path.basename(m.group(1)), int(m.group(2)))
         continue
-    if re.match(r"\s+/\*[0-9a-f]{4}\*/", line):
+    if re.match(r"\s+/\*[0-9a-f]{4,}\*/", line):
         lab = "other " + cur[0]
         for f, a, b, l in REG:
             if f == cur[0] and a <= cur[1] <= b:
