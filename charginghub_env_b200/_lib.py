@@ -7,7 +7,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libchub.so")
+# CHUB_LIB selects another build of the same sources (libchub_checked.so, the self-checking one); never another backend
+LIB_PATH = os.environ.get("CHUB_LIB") or os.path.join(_HERE, "csrc", "libchub.so")
 
 MAX_PILES = 32
 OBS_DIM = 13
@@ -104,6 +105,7 @@ SYMBOLS = {
     "chub_reduce_stats": (ctypes.c_int, [_vp, _vp, _vp, _vp]),
     "chub_set_timing": (ctypes.c_int, [_vp, _i32]),
     "chub_step_times": (ctypes.c_int, [_vp, _vp, _i32, ctypes.POINTER(_i32)]),
+    "chub_checks": (ctypes.c_int, [_vp, ctypes.POINTER(_i32), ctypes.POINTER(_i64)]),
     "chub_debug_curve": (ctypes.c_int, [_vp, _i32, ctypes.c_uint32, _i64, _vp, _vp]),
     "chub_alloc_host": (ctypes.c_int, [_i64, ctypes.POINTER(_vp)]),
     "chub_free_host": (ctypes.c_int, [_vp]),

@@ -21,12 +21,16 @@ def up_to_date():
     return all(os.path.getmtime(os.path.join(CSRC, f)) <= t for f in SOURCES + HEADERS)
 
 
-def build(force=False, verbose=False):
-    if not force and up_to_date():
-        return OUT
+OUT_CHECKED = os.path.join(CSRC, "libchub_checked.so")   # the same sources with -DCHUB_CHECKS (include/chub.h chub_checks)
+
+
+def build(force=False, verbose=False, checked=True):
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + SOURCES + ["-o", OUT]
-    subprocess.check_call(cmd, cwd=CSRC)
+    if force or not up_to_date():
+        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + SOURCES + ["-o", OUT]
+        subprocess.check_call(cmd, cwd=CSRC)
+    if checked and (force or not os.path.exists(OUT_CHECKED) or os.path.getmtime(OUT_CHECKED) < os.path.getmtime(OUT)):
+        subprocess.check_call([nvcc] + NVCC_FLAGS + ["-DCHUB_CHECKS"] + SOURCES + ["-o", OUT_CHECKED], cwd=CSRC)
     return OUT
 
 

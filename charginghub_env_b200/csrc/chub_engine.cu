@@ -517,7 +517,7 @@ static int fill_params(chub_engine *e, ChubParams &P) {
     {   // experiment knobs (defaults are the measured best)
         const char *b = getenv("CHUB_BLOCK"), *y = getenv("CHUB_PHASE_SYNC");
         P.block = b ? atoi(b) : 0;
-        P.phase_sync = y ? atoi(y) : 0;
+        P.phase_sync = y ? atoi(y) : 0;   // experiment knob: bit 0 = hand units out in index order (ignore the cost lists)
     }
     P.pile = e->pile; P.arrive = e->arrive; P.hubA = e->hubA; P.store = e->store; P.keys = e->keys; P.occ = e->occ; P.cls = e->cls;
     P.stats = e->stats; P.last_stats = e->last_stats; P.err = e->err; P.qsoc = e->qsoc;
@@ -1164,6 +1164,20 @@ extern "C" int chub_step_times(chub_engine *e, float *ms_out, int32_t max_n, int
         CK(cudaEventElapsedTime(&ms_out[j], e->time_ev[2 * slot], e->time_ev[2 * slot + 1]));
     }
     *n_out = n;
+    return CHUB_OK;
+}
+
+// ---- self-checking build ----
+extern "C" int chub_checks(chub_engine *e, int32_t *compiled_in, int64_t *failures) {
+    if (!e) return fail(CHUB_ERR_ARG, "chub_checks: null engine");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    if (compiled_in) *compiled_in = chub_checks_compiled_in();
+    if (failures) {
+        unsigned long long n = 0;
+        CK(chub_read_check_failures(&n));
+        *failures = (int64_t) n;
+    }
     return CHUB_OK;
 }
 

@@ -23,6 +23,25 @@ cudaError_t chub_upload_const(const ChubConst &c) {
     return cudaMemcpyToSymbol(kC, &c, sizeof(ChubConst));
 }
 
+// Self-checking build (-DCHUB_CHECKS -> libchub_checked.so): compute-sanitizer is not available on the GPU pool this engine
+// is developed on, so the invariants it would watch -- every index into the per-warp shared-memory rings, the posted-power
+// rows, the warp's pile tile and the unit queue stays inside its array -- are asserted by the kernel itself and counted;
+// tests/test_gpu_checked_build.py runs the parity scenarios through that build and wants zero.  Compiled out otherwise.
+__device__ unsigned long long kCheckFails;
+#ifdef CHUB_CHECKS
+#define CHUB_CHECK(cond) do { if (!(cond)) atomicAdd(&kCheckFails, 1ull); } while (0)
+#else
+#define CHUB_CHECK(cond) do { } while (0)
+#endif
+cudaError_t chub_read_check_failures(unsigned long long *out) { return cudaMemcpyFromSymbol(out, kCheckFails, sizeof *out); }
+int chub_checks_compiled_in() {
+#ifdef CHUB_CHECKS
+    return 1;
+#else
+    return 0;
+#endif
+}
+
 // @region misc
 struct StationOut {
     float mn, mx, now;  // min_power, max_power, charge_power (CHS.hpp:1257-1259)
@@ -164,6 +183,7 @@ __device__ __forceinline__ void flat_car_step(const ChubParams &P, Scr<Q> S, con
         const float tt = __uint_as_float(S->la_t[SEG][sl]);
         const uint32_t w = S->la_w[SEG][sl];
         const uint32_t id = S->la_id[SEG][sl], owner = id & 31u;
+        CHUB_CHECK(count >= 1 && count <= 32 && (uint32_t) sl < LA_RING && id < 32u * (uint32_t) max(P.S0, P.S1));
         float soc, power;
         curve_step<TYPE, CP, SEG>(tt, soc, power);            // car_step, CHS.hpp:900-905 / 1065-1070
         const float tsoc = curve_s2t<TYPE, CP>(soc);
@@ -197,6 +217,7 @@ __device__ __forceinline__ void flat_add_car(Scr<Q> S, const float *tlut, uint4 
     const uint32_t *const sd = &S->la_t[0][0], *const sf = &S->la_w[0][0], *const sx = &S->la_id[0][0];
     for (int j = lane; j < total; j += 32) {
         const uint32_t x = sx[j], owner = x & 31u, i = (x >> 5) & 31u, tu = x >> 10;
+        CHUB_CHECK(total <= 2 * LA_RING && tu < 1000u);
         const float arrive = mk_soc_from<1>(sd[j]);
         const int late = late_time_from<1>(sf[j]);
         const float tsoc = curve_s2t<TYPE, CP>(arrive);
@@ -305,7 +326,9 @@ __device__ __forceinline__ void station_step(const ChubParams &P, Scr<Q> S, cons
         const uint32_t m0 = __ballot_sync(full, seg == 0), m1 = CP ? 0u : __ballot_sync(full, seg == 1);
         const int need = rows ? 32 : 1;              // the last occupied row also flushes the rings
         if ((m0 | m1) != 0u || need == 1) {          // otherwise nobody charges on this row: nothing to queue
+            CHUB_CHECK(cnt0 + __popc(m0) <= LA_RING && cnt1 + __popc(m1) <= LA_RING);
             if (seg >= 0) {
+                CHUB_CHECK(mine && i < n);
                 const int sl = seg * LA_RING + ((seg == 0 ? head0 + cnt0 + __popc(m0 & lt) : head1 + cnt1 + __popc(m1 & lt)) & (LA_RING - 1));
                 (&S->la_t[0][0])[sl] = __float_as_uint(tt);
                 (&S->la_w[0][0])[sl] = w;
@@ -367,6 +390,7 @@ __device__ __forceinline__ void station_step(const ChubParams &P, Scr<Q> S, cons
                 rng.lcg = wf.y;
                 const uint32_t i = (uint32_t) __ffs(rem) - 1u;
                 rem &= rem - 1u;
+                CHUB_CHECK(slot >= 0 && slot < 2 * LA_RING && i < (uint32_t) n);
                 (&S->la_t[0][0])[slot] = wd.x;
                 (&S->la_w[0][0])[slot] = wf.x;
                 (&S->la_id[0][0])[slot] = (uint32_t) lane | (i << 5) | (tu << 10);
@@ -385,6 +409,7 @@ __device__ __forceinline__ void station_step(const ChubParams &P, Scr<Q> S, cons
         const int i = __ffs(prow) - 1;
         const uint32_t vb = pwp[i * 32];
         const bool here = (present >> i) & 1u;
+        CHUB_CHECK(i < max(P.S0, P.S1) && (!here || (mine && i < n)));
         const float power = here ? __uint_as_float(vb & 0x7fffffffu) : 0.0f;
         mx += power;
         mn += (vb & PWB_URGENT) ? power : 0.0f;
@@ -712,14 +737,20 @@ __device__ __forceinline__ void load_actions(const ChubParams &P, float *stage, 
     if (staged) {
         const uint4 *g = reinterpret_cast<const uint4 *>(P.actions + (size_t) h0 * stride);
         uint4 *d = reinterpret_cast<uint4 *>(stage);
+        CHUB_CHECK(32 * stride <= stage_floats && h0 + 32 <= P.h_end);
         for (int c = lane; c < 8 * stride; c += 32) d[c] = __ldcs(g + c);
         __syncwarp();
         src = stage + lane * stride;
     }
     if (active) {
-        for (int j = 0; j < na; ++j) {
-            if (src[j] >= -0x1p-25f) bits |= 1ull << j;
-        }
+        // two 32-bit halves built from the top down (shift in one bit per entry): no 64-bit shifts, no per-entry bit index
+        uint32_t lo = 0u, hi = 0u;
+        const int n_lo = na < 32 ? na : 32;
+#pragma unroll 4
+        for (int j = na - 1; j >= 32; --j) hi = (hi << 1) | (src[j] >= -0x1p-25f ? 1u : 0u);
+#pragma unroll 4
+        for (int j = n_lo - 1; j >= 0; --j) lo = (lo << 1) | (src[j] >= -0x1p-25f ? 1u : 0u);
+        bits = (unsigned long long) lo | ((unsigned long long) hi << 32);
         a_m2 = src[na];      // action[-2] -> electrolyser set-point (the reference swaps the last two)
         a_m1 = src[na + 1];  // action[-1] -> fuel-cell set-point
     }
@@ -822,7 +853,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
                     if (lane >= d) incl += v;
                 }
                 const int total = __shfl_sync(0xffffffffu, incl, 31);
-                if (total == n_units && rd->n_units == n_units) {
+                if (total == n_units && rd->n_units == n_units && !(P.phase_sync & 1)) {
                     const int before = incl - c_hi - c_lo;
                     const unsigned hit = __ballot_sync(0xffffffffu, (int) k < incl);
                     const int owner = __ffs(hit) - 1;
@@ -839,6 +870,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
         __syncthreads();
         const int unit = s_unit;
         if (unit < 0) break;
+        CHUB_CHECK((long long) unit * WARPS * 32 < (long long) (P.h_end - P.h_begin));
         const long long h0 = (long long) P.h_begin + ((long long) unit * WARPS + (threadIdx.x >> 5)) * 32;
         if (h0 < (long long) P.h_end) step_tile<Q>(P, S, tl_s, (int) h0 + S.lane);   // the last unit may be short of tiles
         __syncthreads();          // the unit's cost is that of its slowest warp; s_unit may be rewritten after this

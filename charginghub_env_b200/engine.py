@@ -410,6 +410,12 @@ class HubEngine(object):
                                          _tensor_ptr(out, torch.float64, self.device), self._stream(stream)))
         return out
 
+    def checks(self):
+        """(compiled_in, failures) of the self-checking build (include/chub.h chub_checks)."""
+        c, n = ctypes.c_int32(0), ctypes.c_int64(0)
+        check(self.lib.chub_checks(self.h, ctypes.byref(c), ctypes.byref(n)))
+        return bool(c.value), int(n.value)
+
     def set_timing(self, on=True):
         check(self.lib.chub_set_timing(self.h, int(bool(on))))
 

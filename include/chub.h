@@ -289,6 +289,12 @@ int chub_step_times(chub_engine *e, float *ms_out, int32_t max_n, int32_t *n_out
  * reachable argument with it. */
 int chub_debug_curve(chub_engine *e, int32_t which, uint32_t first_bits, int64_t n, float *out_dev, void *stream);
 
+/* Self-checking build: libchub_checked.so is this library compiled with -DCHUB_CHECKS, which makes the kernels assert that
+ * every index into their shared-memory rings, posted-power rows, pile tiles and the unit queue stays inside its array
+ * (what compute-sanitizer's memcheck would watch; that tool is unavailable on the development pool).  compiled_in = 1
+ * in that build; failures = violations counted on this device since the library was loaded (0 is the only good value). */
+int chub_checks(chub_engine *e, int32_t *compiled_in, int64_t *failures);
+
 /* Absolute step index, number of step kernel launches so far, and sum of sticky error bits. */
 int chub_counters(chub_engine *e, int64_t *step_index, int64_t *launches, uint32_t *error_or);
 
