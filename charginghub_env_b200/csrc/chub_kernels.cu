@@ -797,6 +797,44 @@ struct LptList {            // one per parity, in global memory: head[0] = units
     int count[CHUB_LPT_BINS];
     // int unit[CHUB_LPT_BINS][cap] follows
 };
+// Warp 0 of a block draws a ticket and turns it into a unit (-1: the batch is used up).  All 32 lanes call it.
+template <int WARPS>
+__device__ __noinline__ int draw_unit(const ChubParams &P, int lane) {
+    const int n_units = (int) (((long long) (P.h_end - P.h_begin) + WARPS * 32 - 1) / (WARPS * 32));
+    const int par = (int) ((*P.step_index + P.step_offset) & 1);
+    const size_t list_bytes = sizeof(LptList) + (size_t) CHUB_LPT_BINS * P.lpt_cap * sizeof(int);
+    const LptList *const rd = reinterpret_cast<const LptList *>(P.lpt + par * list_bytes);
+    long long k = 0;
+    if (lane == 0) {
+        const unsigned long long first = *P.queue_base + (unsigned long long) P.step_offset * P.queue_stride;
+        k = (long long) (atomicAdd(P.queue, 1ull) - first);
+    }
+    k = __shfl_sync(0xffffffffu, k, 0);
+    if (k >= n_units) return -1;
+    int u = (int) k;
+    // bins from the top: lane l looks after bins 63 - 2l and 62 - 2l
+    const int c_hi = rd->count[CHUB_LPT_BINS - 1 - 2 * lane], c_lo = rd->count[CHUB_LPT_BINS - 2 - 2 * lane];
+    int incl = c_hi + c_lo;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += v;
+    }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    if (total == n_units && rd->n_units == n_units && !(P.phase_sync & 1)) {
+        const int before = incl - c_hi - c_lo;
+        const unsigned hit = __ballot_sync(0xffffffffu, (int) k < incl);
+        const int owner = __ffs(hit) - 1;
+        if (lane == owner) {
+            const int r = (int) k - before;
+            const int bin = r < c_hi ? CHUB_LPT_BINS - 1 - 2 * lane : CHUB_LPT_BINS - 2 - 2 * lane;
+            u = reinterpret_cast<const int *>(rd + 1)[(size_t) bin * P.lpt_cap + (r < c_hi ? r : r - c_hi)];
+        }
+        u = __shfl_sync(0xffffffffu, u, owner);
+    }
+    return u;
+}
+
 template <int WARPS, int MINB, int Q>
 __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __grid_constant__ ChubParams P) {
     unsigned char *const smem = chub_smem;
@@ -806,7 +844,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
         reinterpret_cast<uint32_t *>(smem)[i] = reinterpret_cast<const uint32_t *>(kLogTab)[i];
     float *const tl_w = reinterpret_cast<float *>(smem + CHUB_LOG_N * 16);   // then the two curve-charging s2t(target) tables
     for (int i = threadIdx.x; i < 2000; i += WARPS * 32) tl_w[i] = __ldg(&P.s2t_lut[i]);
-    __shared__ int s_unit;
+    __shared__ int s_unit[2];
     __shared__ long long s_t0;
     __syncthreads();
     Scr<Q> S;
@@ -814,66 +852,41 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     S.lane = threadIdx.x & 31;
     asm volatile("" : "+r"(S.base), "+r"(S.lane));
 
-    // Nothing of the queue's bookkeeping stays in registers across step_tile (they are the scarce resource there): warp 0
-    // re-derives it from the launch parameters at every draw, and the unit in flight waits in shared memory.
+    // Nothing of the queue's bookkeeping stays in registers across step_tile (they are the scarce resource there) but the
+    // loop count: warp 0 re-derives the rest from the launch parameters at every draw, and it draws the NEXT unit as soon as
+    // its own tile is done, so a unit boundary costs one barrier and (mostly) no round trip.
     // Without a queue (ranged launches of the host pipeline, which run side by side on several streams) the mapping is
     // static: block b does unit b and leaves.  One loop serves both, so that the tile code exists once.
-    if (threadIdx.x == 0) s_unit = -2;
-    for (;;) {
-        if (P.queue == nullptr) {
-            if (threadIdx.x == 0) s_unit = s_unit == -2 ? (int) blockIdx.x : -1;
-        } else if (threadIdx.x < 32) {   // warp 0: book the finished unit, draw a ticket, turn it into a unit
-            const int lane = threadIdx.x;
-            const int n_units = (int) (((long long) (P.h_end - P.h_begin) + WARPS * 32 - 1) / (WARPS * 32));
-            const int par = (int) ((*P.step_index + P.step_offset) & 1);
-            const size_t list_bytes = sizeof(LptList) + (size_t) CHUB_LPT_BINS * P.lpt_cap * sizeof(int);
-            const LptList *const rd = reinterpret_cast<const LptList *>(P.lpt + par * list_bytes);
-            LptList *const wr = reinterpret_cast<LptList *>(P.lpt + (par ^ 1) * list_bytes);
-            long long k = 0;
-            if (lane == 0) {
-                const int fin = s_unit;
-                if (fin >= 0) {
-                    int bin = (int) ((clock64() - s_t0) >> 13);
-                    bin = bin < 0 ? 0 : (bin >= CHUB_LPT_BINS ? CHUB_LPT_BINS - 1 : bin);
-                    const int at = atomicAdd(&wr->count[bin], 1);
-                    if (at < P.lpt_cap) reinterpret_cast<int *>(wr + 1)[(size_t) bin * P.lpt_cap + at] = fin;
-                }
-                const unsigned long long first = *P.queue_base + (unsigned long long) P.step_offset * P.queue_stride;
-                k = (long long) (atomicAdd(P.queue, 1ull) - first);
-            }
-            k = __shfl_sync(0xffffffffu, k, 0);
-            int u = k < n_units ? (int) k : -1;
-            if (k < n_units) {
-                // bins from the top: lane l looks after bins 63 - 2l and 62 - 2l
-                const int c_hi = rd->count[CHUB_LPT_BINS - 1 - 2 * lane], c_lo = rd->count[CHUB_LPT_BINS - 2 - 2 * lane];
-                int incl = c_hi + c_lo;
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const int v = __shfl_up_sync(0xffffffffu, incl, d);
-                    if (lane >= d) incl += v;
-                }
-                const int total = __shfl_sync(0xffffffffu, incl, 31);
-                if (total == n_units && rd->n_units == n_units && !(P.phase_sync & 1)) {
-                    const int before = incl - c_hi - c_lo;
-                    const unsigned hit = __ballot_sync(0xffffffffu, (int) k < incl);
-                    const int owner = __ffs(hit) - 1;
-                    if (lane == owner) {
-                        const int r = (int) k - before;
-                        const int bin = r < c_hi ? CHUB_LPT_BINS - 1 - 2 * lane : CHUB_LPT_BINS - 2 - 2 * lane;
-                        u = reinterpret_cast<const int *>(rd + 1)[(size_t) bin * P.lpt_cap + (r < c_hi ? r : r - c_hi)];
-                    }
-                    u = __shfl_sync(0xffffffffu, u, owner);
-                }
-            }
-            if (lane == 0) { s_unit = u; s_t0 = clock64(); }
-        }
-        __syncthreads();
-        const int unit = s_unit;
+    if (threadIdx.x < 32) {
+        const int u = P.queue ? draw_unit<WARPS>(P, threadIdx.x) : (int) blockIdx.x;
+        if (threadIdx.x == 0) s_unit[0] = u;
+    }
+    __syncthreads();
+    for (int it = 0;; ++it) {
+        const int unit = s_unit[it & 1];
         if (unit < 0) break;
         CHUB_CHECK((long long) unit * WARPS * 32 < (long long) (P.h_end - P.h_begin));
+        if (threadIdx.x == 0) s_t0 = clock64();
         const long long h0 = (long long) P.h_begin + ((long long) unit * WARPS + (threadIdx.x >> 5)) * 32;
         if (h0 < (long long) P.h_end) step_tile<Q>(P, S, tl_s, (int) h0 + S.lane);   // the last unit may be short of tiles
-        __syncthreads();          // the unit's cost is that of its slowest warp; s_unit may be rewritten after this
+        if (threadIdx.x < 32) {
+            // warp 0 draws the next unit when ITS tile is done, i.e. while the unit's stragglers are still at work: late
+            // enough that units still go to whichever SM is about to be free (drawing at the start of the unit would
+            // reserve two units per SM up front and cost the de-phased batch 14 %: measured), early enough to hide the
+            // round trip to the ticket counter and the bin walk
+            const int nxt = P.queue ? draw_unit<WARPS>(P, threadIdx.x) : -1;
+            if (threadIdx.x == 0) s_unit[(it + 1) & 1] = nxt;
+        }
+        __syncthreads();          // the unit's cost is that of its slowest warp
+        if (threadIdx.x == 0 && P.queue) {   // book it: into the bin of its cost, for the next launch to read
+            const int par = (int) ((*P.step_index + P.step_offset) & 1);
+            const size_t list_bytes = sizeof(LptList) + (size_t) CHUB_LPT_BINS * P.lpt_cap * sizeof(int);
+            LptList *const wr = reinterpret_cast<LptList *>(P.lpt + (par ^ 1) * list_bytes);
+            int bin = (int) ((clock64() - s_t0) >> 13);
+            bin = bin < 0 ? 0 : (bin >= CHUB_LPT_BINS ? CHUB_LPT_BINS - 1 : bin);
+            const int at = atomicAdd(&wr->count[bin], 1);
+            if (at < P.lpt_cap) reinterpret_cast<int *>(wr + 1)[(size_t) bin * P.lpt_cap + at] = s_unit[it & 1];
+        }
     }
     // the last block out tags the list it helped write and clears the one everybody has finished reading
     if (threadIdx.x == 0 && P.queue != nullptr) {
