@@ -16,6 +16,7 @@ EL_TABLE = 102
 FCEV_QCAP = 16
 DAY = 96
 REPORT_LEN = 29
+STATIC_MAX_HUBS = 1048576
 FAST, SLOW = 0, 1
 
 BUF_OBS, BUF_REWARD, BUF_DONE, BUF_STATS, BUF_LAST_STATS, BUF_ERROR, BUF_FINAL_SOC = range(7)
@@ -81,6 +82,7 @@ SYMBOLS = {
     "chub_step": (ctypes.c_int, [_vp, _vp, _vp]),
     "chub_step_into": (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "chub_step_loads": (ctypes.c_int, [_vp, _vp, _vp]),
+    "chub_step_loads_static": (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "chub_situation_width": (ctypes.c_int, [_vp, _vp, _vp]),
     "chub_situation": (ctypes.c_int, [_vp, _vp, _vp]),
     "chub_step_host": (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),

@@ -4,7 +4,7 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["chub_kernels.cu", "chub_engine.cu", "chub_hostpack.cpp"]
+SOURCES = ["chub_kernels.cu", "chub_engine.cu", "chub_noalloc.cu", "chub_hostpack.cpp"]
 HEADERS = ["chub_kernels.cuh", "chub_device.cuh", "chub_hostpack.h", "chub_fastmath.h", os.path.join("..", "..", "include", "chub.h"),
            os.path.join("..", "..", "include", "chub_rng.h")]
 OUT = os.path.join(CSRC, "libchub.so")

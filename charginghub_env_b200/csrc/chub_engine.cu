@@ -69,6 +69,8 @@ struct chub_engine {
     uint2 *exo_i = nullptr;
     float *final_soc = nullptr;
     unsigned long long *act_bits = nullptr;  // pile on-bits of the scalar-load step (chub_step_loads)
+    unsigned long long *static_bits = nullptr;   // the same in the library's file-scope array (chub_step_loads_static); not owned
+    cudaError_t static_bits_err = cudaSuccess;
     cudaStream_t host_streams[2 + CHUB_HOST_KSTREAMS] = {};  // chub_step_host pipeline: copy in, copy out, step kernels (round robin)
     cudaEvent_t host_events[2 * CHUB_PACK_MAX_RANGES + 2] = {};
     int trace_len = 0, trace_per_hub = 0;
@@ -152,6 +154,9 @@ extern "C" int chub_create(const chub_config *cfg, chub_engine **out) {
     e->Hpad = (cfg->n_hubs + 31) / 32 * 32;
     cudaDeviceGetAttribute(&e->num_sms, cudaDevAttrMultiProcessorCount, cfg->device);
     if (e->num_sms <= 0) e->num_sms = 148;
+    // set-up, this device current: the device address of chub_step_loads_static's scratch (asked once per device; a
+    // failure only disables that entry point)
+    e->static_bits_err = chub_static_act_bits(cfg->device, &e->static_bits);
     const size_t Hp = (size_t) e->Hpad;
     cudaError_t r = cudaSuccess;
     auto A = [&](cudaError_t x) { if (r == cudaSuccess) r = x; };
@@ -619,6 +624,37 @@ extern "C" int chub_step_loads(chub_engine *e, const float *loads_dev, void *str
     chub_launch_dispatch(P, e->act_bits, s);
     P.act_bits = e->act_bits;
     return run_step(e, P, s);
+}
+
+// chub_step_loads without any allocation: the dispatch kernel's output goes to the library's file-scope device array
+// (chub_noalloc.cu) instead of a buffer malloc'ed on first use.  Launches only -- no cudaMalloc / cudaFree, no event or
+// stream creation (the per-launch timers of chub_set_timing are not applied here), nothing from an allocating library.
+extern "C" int chub_step_loads_static(chub_engine *e, const float *loads_dev, float *obs_out_dev, float *reward_out_dev,
+                                      uint8_t *done_out_dev, void *stream) {
+    if (!e || !loads_dev) return fail(CHUB_ERR_ARG, "chub_step_loads_static: null argument");
+    if (e->H > CHUB_STATIC_MAX_HUBS)
+        return fail(CHUB_ERR_ARG, "chub_step_loads_static: the engine holds " + std::to_string(e->H) + " hubs, the static scratch "
+                                  "CHUB_STATIC_MAX_HUBS = " + std::to_string(CHUB_STATIC_MAX_HUBS) + "; use chub_step_loads");
+    if (e->static_bits_err != cudaSuccess || !e->static_bits)
+        return fail(CHUB_ERR_CUDA, std::string("chub_step_loads_static: the static scratch has no device address on this device: ") +
+                                   cudaGetErrorString(e->static_bits_err));
+    CK(cudaSetDevice(e->cfg.device));
+    ChubParams P;
+    int rc = fill_params(e, P);
+    if (rc) return rc;
+    P.actions = loads_dev;
+    if (obs_out_dev) P.obs = obs_out_dev;
+    if (reward_out_dev) P.reward = reward_out_dev;
+    if (done_out_dev) P.done = done_out_dev;
+    cudaStream_t s = (cudaStream_t) stream;
+    chub_launch_dispatch(P, e->static_bits, s);     // writes the word of every hub < n_hubs: nothing must start at zero
+    P.act_bits = e->static_bits;
+    unsigned long long tickets = 0;
+    CK(chub_launch_step(P, s, &tickets));
+    chub_launch_tick(e->step_index, 1, e->queue + 1, tickets, s);
+    CK(cudaGetLastError());
+    e->launches += 1;
+    return CHUB_OK;
 }
 
 extern "C" int chub_situation_width(chub_engine *e, int32_t *s0, int32_t *s1) {

@@ -93,5 +93,7 @@ void chub_launch_tick(long long *step_index, int n, unsigned long long *queue_ba
 void chub_launch_stats_sums(const float4 *stats, int H, double *partial, double *sums, cudaStream_t s);
 void chub_launch_curve_sweep(int which, uint32_t first_bits, long long n, float *out, cudaStream_t s);
 cudaError_t chub_upload_const(const ChubConst &c);
+// chub_noalloc.cu: device address of the file-scope scratch of chub_step_loads_static on the CURRENT device `device`
+cudaError_t chub_static_act_bits(int device, unsigned long long **ptr);
 cudaError_t chub_read_check_failures(unsigned long long *out);
 int chub_checks_compiled_in();

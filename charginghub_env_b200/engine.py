@@ -244,6 +244,22 @@ class HubEngine(object):
         check(self.lib.chub_step_loads(self.h, self._f32(loads), self._stream(stream)))
         return self.tensor("obs"), self.tensor("reward"), self.tensor("done")
 
+    def step_loads_static(self, loads, obs_out=None, reward_out=None, done_out=None, stream=None):
+        """step_loads without any allocation (include/chub.h chub_step_loads_static): the dispatch scratch is the library's
+        file-scope device array (at most _lib.STATIC_MAX_HUBS hubs; shared per device -- overlapping calls race).  Returns
+        nothing new: results are in the given tensors or, for None, in the engine's own obs / reward / done buffers."""
+        import torch
+        if tuple(loads.shape) != (self.n_hubs, 4):
+            raise ValueError("loads must be [%d, 4]" % self.n_hubs)
+        for t, shape, dt in ((obs_out, (self.n_hubs, _lib.OBS_DIM), torch.float32), (reward_out, (self.n_hubs,), torch.float32),
+                             (done_out, (self.n_hubs,), torch.uint8)):
+            if t is not None and (tuple(t.shape) != shape or t.dtype != dt or not t.is_contiguous()):
+                raise ValueError("output tensors must be contiguous %r %s" % (shape, dt))
+        check(self.lib.chub_step_loads_static(self.h, self._f32(loads), self._f32(obs_out) if obs_out is not None else None,
+                                              self._f32(reward_out) if reward_out is not None else None,
+                                              _tensor_ptr(done_out, torch.uint8, self.device) if done_out is not None else None,
+                                              self._stream(stream)))
+
     SITUATION_COLUMNS = ("car", "charge", "emergency", "assign", "power", "soc", "init_soc", "target_soc")
 
     def situation(self, out=None, stream=None):

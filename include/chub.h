@@ -191,6 +191,23 @@ int chub_step_into(chub_engine *e, const float *actions_dev, float *obs_out_dev,
  * electrolyser / fuel-cell actions in [-1,1] as in chub_step.  Targets must be finite. */
 int chub_step_loads(chub_engine *e, const float *loads_dev, void *stream);
 
+/* chub_step_loads for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * chub_step_loads keeps the dispatch kernel's output (one 64-bit word of pile on-bits per hub) in a buffer
+ * it cudaMalloc's on its first call; this variant keeps it in a file-scope device array of the library
+ * (csrc/chub_noalloc.cu) of CHUB_STATIC_MAX_HUBS words = 8 MiB, which every GPU that loads libchub.so holds until the
+ * process exits.  It calls no cudaMalloc / cudaFree, creates no stream or event, and calls into no allocating library;
+ * it launches the dispatch kernel, the step kernel and the tick on `stream` and returns.
+ * loads_dev: as chub_step_loads.  obs_out_dev / reward_out_dev / done_out_dev: as chub_step_into (NULL = the engine's
+ * own buffer).  Engines with more than CHUB_STATIC_MAX_HUBS hubs are refused with CHUB_ERR_ARG (use chub_step_loads).
+ * The array is shared by every engine on a device and by every call, and keeps the last call's contents; nothing in it
+ * has to start at zero (every hub's word is written before it is read, stream ordered), but calls that OVERLAP on the
+ * GPU -- two engines of one device on different streams, one engine driven from two streams -- race on it.  Its device
+ * address is resolved at chub_create (set-up), once per device.  chub_set_timing's per-launch timers do not cover it. */
+#define CHUB_STATIC_MAX_HUBS 1048576
+int chub_step_loads_static(chub_engine *e, const float *loads_dev, float *obs_out_dev, float *reward_out_dev,
+                           uint8_t *done_out_dev, void *stream);
+
 /* step(action) on packed actions: packed_dev = [n_hubs] 16-byte records {uint32 on-bits of piles 0..31, uint32 on-bits of
  * piles 32..63, float a[-2], float a[-1]}, pile j = entry j of the chub_step row (station 0's piles first); bit j is
  * what action_to_real (evcssp_manager.py:384-404) makes of row entry j: 1 iff a[j] >= -2^-25.  For producers that
