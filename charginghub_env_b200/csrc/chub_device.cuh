@@ -14,6 +14,33 @@
 
 #include "../../include/chub.h"
 #include "../../include/chub_rng.h"
+// fp64 constants of the curves and the canonical variates, appended to the constant-bank table of chub_fastmath.h (see there)
+#define CHUB_DK_CURVES(X)                                                                                              \
+    /* canon_d_of */                                                                                                  \
+    X(CAN_M, 2147483646.0) X(CAN_D, 4611686009837453312.0) X(CAN_RD, 1.0 / 4611686009837453312.0)                     \
+    /* slow_step SEG 0, slow_t2p */                                                                                   \
+    X(SC4, -0.0004112) X(SP4, -0.002056) X(SC3, 0.0023025) X(SP3, 0.00921) X(SC2, 0.03562 / 3) X(SP2, 0.03562)        \
+    X(SC1, 0.011895) X(SP1, 0.02379) X(SC0, 6.007)                                                                    \
+    /* slow_step SEG 1 */                                                                                             \
+    X(S_END, 3.67 * 4) X(SL_A, -4.041) X(SL_X0, 0.485) X(SL_B, 19.140115) X(SL_C, 11.943306312699628) X(SL_P, 21.1)   \
+    X(S_SCALE, 19.285746346634653) X(S_RSCALE, 1.0 / 19.285746346634653) X(S_SEG, 2.33 * 4)                           \
+    /* slow_s2t */                                                                                                    \
+    X(ST_BRK, 73.89239629561729) X(ST_B, 0.1295) X(ST_Q3, -0.001529) X(ST_Q2, 0.1871) X(ST_Q1, -10.15) X(ST_Q0, 213.1) \
+    X(ST_ADD, 0.1787983924863248) X(ST_SLOPE, 0.2012016075138625) X(ST_W, 26.10760370438271)                          \
+    X(ST_RW, 1.0 / 26.10760370438271)                                                                                 \
+    /* fast_step, fast_t2p */                                                                                         \
+    X(F_K, 0.053) X(F_A1, 0.7194 / 0.053) X(F_B1, 50.15) X(F_A, 0.7194) X(F_P0, 47.78) X(F_END, 51.2 / 15)            \
+    X(F_SEG, 28.7 / 15)                                                                                               \
+    X(FA4, 0.0002253) X(FI4, 0.0002253 / 5) X(FA3, 0.03572) X(FI3, -(0.03572 / 4)) X(FA2, 2.016) X(FI2, 2.016 / 3)    \
+    X(FA1, 48.76) X(FI1, -(48.76 / 2)) X(FA0, 457.7)                                                                  \
+    /* fast_s2t */                                                                                                    \
+    X(FS_N2, (double) -18.18f) X(FS_D1, (double) -23.9f) X(FS_N1, (double) 9.559f) X(FS_D0, (double) 56.48f)          \
+    X(FS_N0, (double) 48.99f) X(FS_DC, (double) 18.96f) X(FS_NC, (double) 29.09f)                                     \
+    /* hub section (chub_kernels.cu): hydrogen system, income, observation */                                         \
+    X(H_R5, 1.0 / 5.0) X(H_R210, 1.0 / 210.0) X(H_R92, 1.0 / 92.0) X(H_001, 0.01) X(H_R185, 1.0 / 18.5)               \
+    X(H_R70, 1.0 / 70.0) X(H_01, 0.1) X(H_R900, 1.0 / 900.0) X(H_MOL, 2.02) X(H_RMOL, 1.0 / 2.02) X(H_EA, 0.326)      \
+    X(H_EB, 1.476) X(H_R1000, 1.0 / 1000.0) X(H_08, 0.8) X(H_FC, 119.6) X(H_RFC, 1.0 / 119.6) X(H_M6, -6.0 / 1000.0)  \
+    X(H_I42, 0.42 / 4.0) X(H_I21, 0.21 / 4.0) X(H_P6, 6.0 / 1000.0) X(H_M10, -10.0 / 1000.0) X(H_R50, 1.0 / 50.0)
 #include "chub_fastmath.h"
 
 // ---------------------------------------------------------------------------------------------
@@ -93,10 +120,10 @@ __device__ __forceinline__ double canon_d(uint32_t &lcg) {
     double a = (double) (lcg - 1u);
     lcg = chub_minstd_next(lcg);
     double b = (double) (lcg - 1u);
-    double sum = a + b * 2147483646.0;
+    double sum = a + b * DK(CAN_M);
     // sum / D with D = (2^31-2)^2 rounded to double = 2^62 - 2^33: reciprocal estimate plus one fma residual
     // correction (Markstein) gives the correctly rounded quotient without the generic division routine
-    const double D = 4611686009837453312.0, rD = 1.0 / 4611686009837453312.0;
+    const double D = DK(CAN_D), rD = DK(CAN_RD);
     double q0 = sum * rD;
     double ret = fma(fma(-q0, D, sum), rD, q0);
     if (ret >= 1.0) ret = 0.99999999999999988898;
@@ -104,8 +131,8 @@ __device__ __forceinline__ double canon_d(uint32_t &lcg) {
 }
 // the same two, from states already drawn (the step kernel's add_car chain computes the states in parallel)
 __device__ __forceinline__ double canon_d_of(uint32_t s1, uint32_t s2) {
-    const double sum = (double) (s1 - 1u) + (double) (s2 - 1u) * 2147483646.0;
-    const double D = 4611686009837453312.0, rD = 1.0 / 4611686009837453312.0;
+    const double sum = (double) (s1 - 1u) + (double) (s2 - 1u) * DK(CAN_M);
+    const double D = DK(CAN_D), rD = DK(CAN_RD);
     const double q0 = sum * rD;
     double ret = fma(fma(-q0, D, sum), rD, q0);
     if (ret >= 1.0) ret = 0.99999999999999988898;
@@ -261,12 +288,11 @@ __device__ __forceinline__ float slow_s2t(float s) {
     // a s^2 + 0.1295 s with the square and the linear term rounded on their own, as the reference's pow(soc, 2) form
     // does: the shorter d * fma(a, d, 0.1295) differs from glibc on ONE reachable argument (61.03515625f), this form on
     // none (tests/test_gpu_curves.py walks all of them)
-    if (d <= 73.89239629561729) return (float) fma(kC.slow_stt1_a, d * d, 0.1295 * d);
+    if (d <= DK(ST_BRK)) return (float) fma(kC.slow_stt1_a, d * d, DK(ST_B) * d);
     if (d <= 100.0) {
-        double p = fma(fma(fma(fma(kC.slow_stt2_a, d, -0.001529), d, 0.1871), d, -10.15), d, 213.1);
-        float q = (float) (p + 0.1787983924863248);
-        return (float) ((double) q + chub_div_const(0.2012016075138625 * (d - 73.89239629561729), 26.10760370438271,
-                                                    1.0 / 26.10760370438271));
+        double p = fma(fma(fma(fma(kC.slow_stt2_a, d, DK(ST_Q3)), d, DK(ST_Q2)), d, DK(ST_Q1)), d, DK(ST_Q0));
+        float q = (float) (p + DK(ST_ADD));
+        return (float) ((double) q + chub_div_const(DK(ST_SLOPE) * (d - DK(ST_BRK)), DK(ST_W), DK(ST_RW)));
     }
     return 14.68f;
 }
@@ -283,21 +309,21 @@ __device__ __forceinline__ void slow_step(float t, float &soc, float &power) {
     const double y = (double) (t * 0.25f);  // charge_time / 4 is exact in fp32
     float ch;
     if (SEG == 0) {
-        ch = (float) (y * fma(fma(fma(fma(-0.0004112, y, 0.0023025), y, 0.03562 / 3), y, 0.011895), y, 6.007));
-        power = (float) fma(fma(fma(fma(-0.002056, y, 0.00921), y, 0.03562), y, 0.02379), y, 6.007);
-    } else if ((double) t <= 3.67 * 4) {
-        ch = (float) (-4.041 * y + 19.140115 * chub_log(fabs(y - 0.485), log_tab<1>()) + 11.943306312699628);
-        power = (float) chub_div(-4.041 * y + 21.1, y - 0.485);
+        ch = (float) (y * fma(fma(fma(fma(DK(SC4), y, DK(SC3)), y, DK(SC2)), y, DK(SC1)), y, DK(SC0)));
+        power = (float) fma(fma(fma(fma(DK(SP4), y, DK(SP3)), y, DK(SP2)), y, DK(SP1)), y, DK(SC0));
+    } else if ((double) t <= DK(S_END)) {
+        ch = (float) (DK(SL_A) * y + DK(SL_B) * chub_log(fabs(y - DK(SL_X0)), log_tab<1>()) + DK(SL_C));
+        power = (float) chub_div(DK(SL_A) * y + DK(SL_P), y - DK(SL_X0));
     } else {
         ch = kC.slow_c2_end;
         power = 0.0f;
     }
-    soc = (float) chub_div_const((double) (100.0f * ch), 19.285746346634653, 1.0 / 19.285746346634653);
+    soc = (float) chub_div_const((double) (100.0f * ch), DK(S_SCALE), DK(S_RSCALE));
 }
 __device__ __forceinline__ float slow_t2p(float t) {
     double y = (double) (t * 0.25f), td = (double) t;
-    if (td < 2.33 * 4) return (float) fma(fma(fma(fma(-0.002056, y, 0.00921), y, 0.03562), y, 0.02379), y, 6.007);
-    if (td < 3.67 * 4) return (float) chub_div(-4.041 * y + 21.1, y - 0.485);
+    if (td < DK(S_SEG)) return (float) fma(fma(fma(fma(DK(SP4), y, DK(SP3)), y, DK(SP2)), y, DK(SP1)), y, DK(SC0));
+    if (td < DK(S_END)) return (float) chub_div(DK(SL_A) * y + DK(SL_P), y - DK(SL_X0));
     return 0.0f;
 }
 
@@ -313,8 +339,8 @@ __device__ __forceinline__ float fast_s2t(float s) {
     double z = (double) zf, z2 = z * z;
     // p4*x and q3*x are fp32 products in the reference (float locals times a float argument)
     double p4z = (double) (-62.97f * zf), q3z = (double) (-50.12f * zf);
-    double num = fma(fma((double) -18.18f, z, (double) 9.559f), z, (double) 48.99f) * z2 + p4z + (double) 29.09f;
-    double den = fma(fma(z, 1.0, (double) -23.9f), z, (double) 56.48f) * z2 + q3z + (double) 18.96f;
+    double num = fma(fma(DK(FS_N2), z, DK(FS_N1)), z, DK(FS_N0)) * z2 + p4z + DK(FS_NC);
+    double den = fma(fma(z, 1.0, DK(FS_D1)), z, DK(FS_D0)) * z2 + q3z + DK(FS_DC);
     return (float) chub_div(num, den);
 }
 // a_part2 (CHS.hpp:688-690), the quartic power fit of the fast charger's second segment.  It falls to zero at 51.2
@@ -324,10 +350,10 @@ __device__ __forceinline__ float fast_s2t(float s) {
 // on every float32 argument of the segment (exhaustive: tests/test_gpu_curves.py).
 __device__ __forceinline__ float fast_a2(double x) {
     const double x2 = x * x, x3 = x2 * x, x4 = x2 * x2;
-    return (float) ((((0.0002253 * x4 - 0.03572 * x3) + 2.016 * x2) - 48.76 * x) + 457.7);
+    return (float) ((((DK(FA4) * x4 - DK(FA3) * x3) + DK(FA2) * x2) - DK(FA1) * x) + DK(FA0));
 }
 __device__ __forceinline__ float fast_aa2(double x) {
-    double p = x * fma(fma(fma(fma(0.0002253 / 5, x, -(0.03572 / 4)), x, 2.016 / 3), x, -(48.76 / 2)), x, 457.7);
+    double p = x * fma(fma(fma(fma(DK(FI4), x, DK(FI3)), x, DK(FI2)), x, DK(FI1)), x, DK(FA0));
     return (float) (p + (double) kC.fast_aa2_c);
 }
 // SEG 0: t < 28.7/15 (exponential part)   SEG 1: otherwise (polynomial part, or full past 51.2/15); t >= 1
@@ -337,11 +363,11 @@ template <int SEG>
 __device__ __forceinline__ void fast_step(float t, float &soc, float &power) {
     const double x = (double) (t * 15.0f);
     if (SEG == 0) {
-        const double ex = chub_exp(0.053 * x);
-        const float a1 = (float) ((0.7194 / 0.053) * ex + 50.15 * x - (double) kC.fast_aa1_c);
+        const double ex = chub_exp(DK(F_K) * x);
+        const float a1 = (float) (DK(F_A1) * ex + DK(F_B1) * x - (double) kC.fast_aa1_c);
         soc = a1 * kC.fast_scale;
-        power = (float) (0.7194 * ex + 47.78);
-    } else if ((double) t < 51.2 / 15) {
+        power = (float) (DK(F_A) * ex + DK(F_P0));
+    } else if ((double) t < DK(F_END)) {
         soc = fast_aa2(x) * kC.fast_scale;
         power = fast_a2(x);
     } else {
@@ -351,8 +377,8 @@ __device__ __forceinline__ void fast_step(float t, float &soc, float &power) {
 }
 __device__ __forceinline__ float fast_t2p(float t) {
     double x = (double) (t * 15.0f), td = (double) t;
-    if (td >= 0.0 && td < 28.7 / 15) return (float) (0.7194 * chub_exp(0.053 * x) + 47.78);
-    if (td >= 0.0 && td < 51.2 / 15) return fast_a2(x);
+    if (td >= 0.0 && td < DK(F_SEG)) return (float) (DK(F_A) * chub_exp(DK(F_K) * x) + DK(F_P0));
+    if (td >= 0.0 && td < DK(F_END)) return fast_a2(x);
     return 0.0f;
 }
 

@@ -24,6 +24,45 @@ typedef struct ChubLogEntry ChubLogEntry;
 #define CHUB_LOG_N 128
 #define CHUB_LOG_OFF 0x3fe6000000000000ull  // 0.6875: z = x * 2^-k lands in [0.6875, 1.375)
 
+// fp64 constants of the hot device code, read from the constant bank.  A double literal whose low word is not zero
+// costs the kernel TWO instructions (UMOV pairs into uniform registers) every time an expression uses it -- 8 % of all
+// instructions the step kernel issued in a busy hour, more than its fp64 arithmetic proper.  From a __constant__ table
+// two neighbouring doubles arrive in one LDCU.128, so the entries are listed in the order the code uses them.  Values are
+// written exactly as the expressions they replace were (the compiler folds them the same way), so results do not change;
+// the host build of these functions (tests/fastmath_check.cpp) sees the literals.
+#define CHUB_DK_LIST(X)                                                                                                \
+    /* chub_log */                                                                                                    \
+    X(LN2_HI, 0x1.62e42fefa3800p-1) X(LN2_LO, 0x1.ef35793c76730p-45)                                                  \
+    X(LG6, -1.0 / 6) X(LG5, 1.0 / 5) X(LG4, -1.0 / 4) X(LG3, 1.0 / 3)                                                 \
+    /* chub_exp */                                                                                                    \
+    X(INV_LN2, 0x1.71547652b82fep+0) X(EX13, 1.0 / 6227020800.0) X(EX12, 1.0 / 479001600.0) X(EX11, 1.0 / 39916800.0) \
+    X(EX10, 1.0 / 3628800.0) X(EX9, 1.0 / 362880.0) X(EX8, 1.0 / 40320.0) X(EX7, 1.0 / 5040.0) X(EX6, 1.0 / 720.0)    \
+    X(EX5, 1.0 / 120.0) X(EX4, 1.0 / 24.0) X(EX3, 1.0 / 6.0)                                                          \
+    CHUB_DK_CURVES(X)
+#ifndef CHUB_DK_CURVES
+#define CHUB_DK_CURVES(X)
+#endif
+struct ChubDK {
+#define CHUB_DK_FIELD(n, v) double n;
+    CHUB_DK_LIST(CHUB_DK_FIELD)
+#undef CHUB_DK_FIELD
+};
+#if defined(__CUDACC__)
+static __constant__ ChubDK kDK = {
+#define CHUB_DK_INIT(n, v) (v),
+    CHUB_DK_LIST(CHUB_DK_INIT)
+#undef CHUB_DK_INIT
+};
+#endif
+#if defined(__CUDA_ARCH__)
+#define DK(n) (kDK.n)
+#else
+#define CHUB_DK_LIT(n, v) static const double CHUB_DKV_##n = (v);
+CHUB_DK_LIST(CHUB_DK_LIT)
+#undef CHUB_DK_LIT
+#define DK(n) (CHUB_DKV_##n)
+#endif
+
 CHUB_FM uint64_t chub_d2u(double x) {
 #if defined(__CUDA_ARCH__)
     return (uint64_t) __double_as_longlong(x);
@@ -51,12 +90,12 @@ CHUB_FM double chub_log(double x, const ChubLogEntry *tab) {
     const ChubLogEntry e = tab[i];
     const double r = fma(z, e.invc, -1.0);
     const double kd = (double) k;
-    const double w = fma(kd, 0x1.62e42fefa3800p-1, e.logc);  // k*ln2_hi is exact for |k| < 2^11
+    const double w = fma(kd, DK(LN2_HI), e.logc);  // k*ln2_hi is exact for |k| < 2^11
     const double hi = w + r;
-    const double lo = (w - hi) + r + kd * 0x1.ef35793c76730p-45;
+    const double lo = (w - hi) + r + kd * DK(LN2_LO);
     const double r2 = r * r;
     // log1p(r) - r = r^2 (-1/2 + r/3 - r^2/4 + r^3/5 - r^4/6)
-    const double p = fma(fma(fma(fma(-1.0 / 6, r, 1.0 / 5), r, -1.0 / 4), r, 1.0 / 3), r, -0.5);
+    const double p = fma(fma(fma(fma(DK(LG6), r, DK(LG5)), r, DK(LG4)), r, DK(LG3)), r, -0.5);
     return hi + fma(r2, p, lo);
 }
 
@@ -68,20 +107,20 @@ CHUB_FM double chub_log_r2(double r2, const ChubLogEntry *tab) { return r2 == 1.
 // @region chub_exp
 // exp(a) for |a| < 700 (no overflow / underflow handling).
 CHUB_FM double chub_exp(double a) {
-    const double kd = rint(a * 0x1.71547652b82fep+0);  // a / ln2
-    double r = fma(-kd, 0x1.62e42fefa3800p-1, a);
-    r = fma(-kd, 0x1.ef35793c76730p-45, r);
-    double p = 1.0 / 6227020800.0;  // 1/13!
-    p = fma(p, r, 1.0 / 479001600.0);
-    p = fma(p, r, 1.0 / 39916800.0);
-    p = fma(p, r, 1.0 / 3628800.0);
-    p = fma(p, r, 1.0 / 362880.0);
-    p = fma(p, r, 1.0 / 40320.0);
-    p = fma(p, r, 1.0 / 5040.0);
-    p = fma(p, r, 1.0 / 720.0);
-    p = fma(p, r, 1.0 / 120.0);
-    p = fma(p, r, 1.0 / 24.0);
-    p = fma(p, r, 1.0 / 6.0);
+    const double kd = rint(a * DK(INV_LN2));  // a / ln2
+    double r = fma(-kd, DK(LN2_HI), a);
+    r = fma(-kd, DK(LN2_LO), r);
+    double p = DK(EX13);  // 1/13!
+    p = fma(p, r, DK(EX12));
+    p = fma(p, r, DK(EX11));
+    p = fma(p, r, DK(EX10));
+    p = fma(p, r, DK(EX9));
+    p = fma(p, r, DK(EX8));
+    p = fma(p, r, DK(EX7));
+    p = fma(p, r, DK(EX6));
+    p = fma(p, r, DK(EX5));
+    p = fma(p, r, DK(EX4));
+    p = fma(p, r, DK(EX3));
     p = fma(p, r, 0.5);
     p = fma(p, r, 1.0);
     p = fma(p, r, 1.0);

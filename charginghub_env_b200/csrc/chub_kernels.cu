@@ -433,6 +433,8 @@ __device__ __forceinline__ void station_step(const ChubParams &P, Scr<Q> S, cons
 
 // x / D for a literal D: exactly the IEEE quotient (Markstein correction), 3 instructions instead of ~25
 #define DIVC(x, D) chub_div_const((x), (D), 1.0 / (D))
+// the same with the reciprocal (and, where its low word is not zero, the divisor) from the constant-bank table
+#define DIVK(x, D, RD) chub_div_const((x), (D), DK(RD))
 
 // @region hydrogen helpers
 __device__ __forceinline__ double py_max(double a, double b) { return b > a ? b : a; }  // Python max(a, b)
@@ -441,16 +443,16 @@ __device__ __forceinline__ double py_min(double a, double b) { return b < a ? b 
 __device__ __forceinline__ double el_power(const ChubClass &c, double m) {  // Electrolyser.get_power, hydro_sys.py:38-48
     if (c.el_cells == 0.0) return 0.0;
     double v_H_mass = chub_div_const(m, c.el_cells, c.r_el_cells);
-    double v_H_mol = DIVC(v_H_mass, 2.02);
+    double v_H_mol = DIVK(v_H_mass, DK(H_MOL), H_RMOL);
     double v_H_L = v_H_mol * c.v_M;
     double v_H = v_H_L * 1000.0 * 60.0;
     double temp = chub_div_const(v_H * 2.0 * 96487.0, c.el_den, c.r_el_den);
-    double power = (temp * temp) * 0.326 + temp * 1.476;
-    return DIVC(c.el_cells * power, 1000.0);
+    double power = (temp * temp) * DK(H_EA) + temp * DK(H_EB);
+    return DIVK(c.el_cells * power, 1000.0, H_R1000);
 }
 __device__ __forceinline__ double cpr_power(const ChubClass &c, double m) {  // Compressor.generate_W, hydro_sys.py:74-82
-    double n = DIVC(m, 2.02);
-    return DIVC(DIVC(n * c.cpr_w12, 0.8), 1000.0);
+    double n = DIVK(m, DK(H_MOL), H_RMOL);
+    return DIVK(chub_div_const(n * c.cpr_w12, DK(H_08), 1.0 / 0.8), 1000.0, H_R1000);
 }
 
 // SAE J2601 table: initial pressure -> target pressure (hydro_sys.py:338-388)
@@ -467,11 +469,11 @@ __device__ __forceinline__ double j2601_target(double p) {
 __device__ __forceinline__ void fcev_need(float soc_f, double &minutes, double &grams) {
     double soc = (double) soc_f;
     if (soc < 0.5) soc = 0.5;
-    double p0 = (soc * 0.01) * 70.0;
+    double p0 = (soc * DK(H_001)) * 70.0;
     double tp = j2601_target(p0);
-    if (p0 < 5.0) minutes = DIVC(69.0 - p0, 18.5) + kC.topoff_time;
-    else minutes = DIVC(tp - p0, 18.5);
-    grams = kC.fcev_cap * DIVC(tp, 70.0) - kC.fcev_cap * DIVC(p0, 70.0);
+    if (p0 < 5.0) minutes = DIVK(69.0 - p0, 18.5, H_R185) + kC.topoff_time;
+    else minutes = DIVK(tp - p0, 18.5, H_R185);
+    grams = kC.fcev_cap * DIVK(tp, 70.0, H_R70) - kC.fcev_cap * DIVK(p0, 70.0, H_R70);
 }
 
 // HyFCEVStation.hvs_step with a backlog or several arrivals (hydro_sys.py:266-285); rare, kept
@@ -643,17 +645,17 @@ __device__ __forceinline__ void write_obs(const ChubParams &P, int h, const Chub
         o[k++] = (float) chub_div_const((double) s0.mn - c.half[0], c.half[0], c.r_half[0]);
         o[k++] = (float) chub_div_const((double) s0.now - c.half[0], c.half[0], c.r_half[0]);
         o[k++] = (float) chub_div_const((double) s0.mx - c.half[0], c.half[0], c.r_half[0]);
-        o[k++] = (float) DIVC((double) s0.line, 5.0);
+        o[k++] = (float) DIVK((double) s0.line, 5.0, H_R5);
     }
     if (c.n[1] > 0) {
         o[k++] = (float) chub_div_const((double) s1.mn - c.half[1], c.half[1], c.r_half[1]);
         o[k++] = (float) chub_div_const((double) s1.now - c.half[1], c.half[1], c.r_half[1]);
         o[k++] = (float) chub_div_const((double) s1.mx - c.half[1], c.half[1], c.r_half[1]);
-        o[k++] = (float) DIVC((double) s1.line, 5.0);
+        o[k++] = (float) DIVK((double) s1.line, 5.0, H_R5);
     }
     o[k++] = (float) store_soc;
-    o[k++] = (float) DIVC(pv, 210.0);
-    o[k++] = (float) DIVC(wd, 92.0);
+    o[k++] = (float) DIVK(pv, 210.0, H_R210);
+    o[k++] = (float) DIVK(wd, 92.0, H_R92);
     float *dst = P.obs + (size_t) h * CHUB_OBS_DIM;
 #pragma unroll
     for (int j = 0; j < CHUB_OBS_DIM; ++j) dst[j] = o[j];
@@ -1000,7 +1002,7 @@ __device__ __forceinline__ void step_tile(const ChubParams &P, Scr<Q> S, const f
         act = 0.01 * 100.0;  // hy_power_speed_list_input[-1]
         for (int ind = 0; ind < CHUB_EL_TABLE; ++ind) {
             if (__ldg(&tab[ind]) >= limit) {
-                if (ind > 0) act = 0.01 * (double) (ind - 1);  // ind == 0 picks input[-1] (Python index -1)
+                if (ind > 0) act = DK(H_001) * (double) (ind - 1);  // ind == 0 picks input[-1] (Python index -1)
                 break;
             }
         }
@@ -1026,17 +1028,17 @@ __device__ __forceinline__ void step_tile(const ChubParams &P, Scr<Q> S, const f
             demand = fcev_general(P, h, arrivals, v.qn, v.fline, v.rng, v.err);
         }
     }
-    const double must = py_max(0.0, c.cap_mass * 0.1 - v.store);
+    const double must = py_max(0.0, c.cap_mass * DK(H_01) - v.store);
     const double upper = py_max(c.cap_mass - v.store, 0.0);
     const double charge_temp = py_max(py_min(act * c.v_h_max * 900.0, upper), must);
-    double flow = DIVC(charge_temp, 900.0);
+    double flow = DIVK(charge_temp, 900.0, H_R900);
     flow = py_min(flow, c.v_h_max);
     const double ele_kw = el_power(c, flow);
     const double cpr_kw = cpr_power(c, flow);
     // HyStore.sty_step (hydro_sys.py:104-126)
     v.store += flow * 15.0 * 60.0;
     if (c.cap_mass - v.store < 0.0) v.err |= CHUB_HUBERR_STORE_ASSERT;
-    double lower = py_max(0.0, v.store - 0.1 * c.cap_mass);
+    double lower = py_max(0.0, v.store - DK(H_01) * c.cap_mass);
     const double hy_use = py_min(lower, demand);
     const double not_meet = demand - hy_use;
     v.store -= hy_use;
@@ -1065,7 +1067,7 @@ __device__ __forceinline__ void step_tile(const ChubParams &P, Scr<Q> S, const f
     if (fc > c.fc_cells) fc = c.fc_cells;
     else if (fc < 0.0) fc = 0.0;
     else if (fc > ev_sum) fc = ev_sum;
-    double hy_fc = DIVC(fc * 1500.0, 119.6);
+    double hy_fc = DIVK(fc * 1500.0, DK(H_FC), H_RFC);
     hy_fc = py_min(v.store, hy_fc);
     v.store -= hy_fc;
     const double fc_kw = py_max(0.0, fc);
@@ -1079,17 +1081,17 @@ __device__ __forceinline__ void step_tile(const ChubParams &P, Scr<Q> S, const f
         }
     }
     // ---- income and reward (evcssp_manager.py:234-269) ----
-    const double hy_loss = -6.0 / 1000.0 * hy_fc;
+    const double hy_loss = DK(H_M6) * hy_fc;
     const double p4 = pr_t * 0.25;
-    const double inc_fast = 0.42 / 4.0 * cp0 - p4 * l0;
-    const double inc_slow = 0.21 / 4.0 * cp1 - p4 * l1;
+    const double inc_fast = DK(H_I42) * cp0 - p4 * l0;
+    const double inc_slow = DK(H_I21) * cp1 - p4 * l1;
     const double inc_evs = inc_fast + inc_slow;
-    const double serve = 0.8 * (double) (s0.flow + s1.flow);
-    const double inc_hys = 6.0 / 1000.0 * hy_use;
-    const double nm_loss = -10.0 / 1000.0 * not_meet;
+    const double serve = DK(H_08) * (double) (s0.flow + s1.flow);
+    const double inc_hys = DK(H_P6) * hy_use;
+    const double nm_loss = DK(H_M10) * not_meet;
     const double hy_cost = -p4 * h2_grid;
     const double income = inc_hys + inc_evs + serve + hy_cost;
-    const double reward = DIVC(inc_hys + inc_evs + serve + hy_cost + 1.0 * hy_loss + nm_loss, 50.0);
+    const double reward = DIVK(inc_hys + inc_evs + serve + hy_cost + 1.0 * hy_loss + nm_loss, 50.0, H_R50);
     const bool done = v.t + 1 >= CHUB_DAY;
     const int t_left = v.t;
     v.t = (v.t + 1) % CHUB_DAY;
