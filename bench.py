@@ -77,11 +77,17 @@ def workload(name, tabs):
         H = 262144
         hub_class = rs.randint(0, ncls, H).astype(np.int32)
         desc = "config3: 262,144 heterogeneous hubs (4..32 piles per station), auto-reset"
-        if not os.environ.get("CHUB_BENCH_UNSORTED"):
-            # hubs are independent and their order is the caller's choice: created class by class (sharding.order_by_class),
-            # a warp holds hubs of one class -- same pile counts, one parameter record -- instead of 32 different ones
+        order = os.environ.get("CHUB_BENCH_ORDER", "size")
+        if order == "class":
             hub_class = np.sort(hub_class)
             desc += ", hubs created in class order"
+        elif order == "size":
+            # hubs are independent and their order is the caller's choice: created class by class, the classes by pile
+            # count (sharding.order_by_size), a warp holds hubs of one class -- same pile counts, one parameter record --
+            # and the warps of a block hubs of similar cost
+            from charginghub_env_b200 import sharding
+            hub_class = hub_class[sharding.order_by_size(classes, hub_class)[0]]
+            desc += ", hubs created class by class in order of pile count"
         return dict(H=H, classes=classes, hub_class=hub_class, auto_reset=True, stride=66, scaling="weak", desc=desc)
     raise SystemExit("unknown workload " + name)
 
@@ -291,7 +297,7 @@ def dephase(eng, H, step, pool, mode):
     group g - 1, all hubs stepping on in between, so that after 96 steps every launch holds all 96 times of day in equal
     shares.  Traces stay aligned with each hub's own time of day (include/chub.h chub_set_traces)."""
     import torch
-    unit = 32 * {"spread": 28, "spread-warps": 1, "spread-quarters": 7}[mode]   # 28 warps = one unit of the step kernel's queue
+    unit = {"spread": eng.unit_hubs(), "spread-warps": 32, "spread-quarters": eng.unit_hubs() // 4}[mode]   # one unit of the step kernel's queue
     grp = ((torch.arange(H, device="cuda") // unit) * 37) % 96
     for j in range(96):
         eng.reset(mask=(grp == j).to(torch.uint8), step_index=-1)
@@ -383,8 +389,8 @@ def main():
     phase = args.phase or ("spread" if wl["auto_reset"] else "lockstep")
     if phase != "lockstep" and not wl["auto_reset"]:
         raise SystemExit("--phase %s needs an auto-reset workload" % phase)
-    wl["desc"] += {"spread": "; de-phased: every launch holds all 96 times of day in equal shares (groups of 896 hubs reset one "
-                             "step apart during warm-up)",
+    wl["desc"] += {"spread": "; de-phased: every launch holds all 96 times of day in equal shares (groups of %d hubs reset one "
+                             "step apart during warm-up)" % eng.unit_hubs(),
                    "spread-warps": "; de-phased by single warps", "spread-quarters": "; de-phased by groups of 7 warps",
                    "lockstep": "; lock step (all hubs at the same time of day)" if wl["auto_reset"] else ""}[phase]
     eng.reset()

@@ -112,6 +112,7 @@ SYMBOLS = {
     "chub_alloc_host": (ctypes.c_int, [_i64, ctypes.POINTER(_vp)]),
     "chub_free_host": (ctypes.c_int, [_vp]),
     "chub_algorithmic_bytes": (_i64, [_vp, _i32]),
+    "chub_unit_hubs": (_i32, [_vp]),
 }
 
 _lib = None

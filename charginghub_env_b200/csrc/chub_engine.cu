@@ -323,6 +323,17 @@ extern "C" int64_t chub_algorithmic_bytes(chub_engine *e, int32_t k) {
     return 2 * (16 * n + 80) + 4 * (n + 2) + 57;
 }
 
+extern "C" int32_t chub_unit_hubs(chub_engine *e) {
+    if (!e || !e->have_classes) return -1;
+    ChubParams P;
+    memset(&P, 0, sizeof P);   // the shape depends on the batch size, the pile counts and the action stride only
+    P.H = e->H; P.Hpad = e->Hpad; P.S0 = e->S0; P.S1 = e->S1; P.h_begin = 0; P.h_end = e->H;
+    P.action_stride = e->cfg.action_stride; P.num_sms = e->num_sms;
+    const char *b = getenv("CHUB_BLOCK");
+    P.block = b ? atoi(b) : 0;
+    return (chub_step_shape(P) / 100) * 32;
+}
+
 // ---- static tables ----
 static float h_fast_aa1(float x, float c1) { return (float) ((0.7194 / 0.053) * std::exp(0.053 * x) + 50.15 * x - c1); }
 static double h_fast_anti(double x) {  // antiderivative of the quartic power fit, libm pow like the reference

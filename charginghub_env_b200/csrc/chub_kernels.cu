@@ -1455,7 +1455,7 @@ void chub_launch_stats_sums(const float4 *stats, int H, double *partial, double 
     chub_stats_final_kernel<<<1, 32, 0, s>>>(partial, sums);
 }
 
-cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s, unsigned long long *tickets) {
+int chub_step_shape(const ChubParams &p) {
     int shape = p.block;
     if (shape == 0) {
         const int ws = step_scratch_bytes<0>(p), sms = p.num_sms > 0 ? p.num_sms : 148;
@@ -1468,6 +1468,10 @@ cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s, unsigned long 
             if (tiles >= (long long) cand[k] * sms || cand[k] == 4) { shape = cand[k] * 100 + 10; break; }
         }
     }
+    return shape;
+}
+cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s, unsigned long long *tickets) {
+    const int shape = chub_step_shape(p);
     switch (shape) {  // warps per block * 100 + min blocks per SM * 10
         case 410: return launch_step_variant<4, 1, 0>(p, s, tickets);
         case 810: return launch_step_variant<8, 1, 0>(p, s, tickets);
@@ -1475,6 +1479,9 @@ cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s, unsigned long 
         case 2010: return launch_step_variant<20, 1, 0>(p, s, tickets);
         case 2410: return launch_step_variant<24, 1, 0>(p, s, tickets);
         case 2810: return launch_step_variant<28, 1, 0>(p, s, tickets);
+        case 1220: return launch_step_variant<12, 2, 0>(p, s, tickets);
+        case 1020: return launch_step_variant<10, 2, 0>(p, s, tickets);
+        case 1420: return launch_step_variant<14, 2, 0>(p, s, tickets);
         default: return launch_step_variant<16, 1, 0>(p, s, tickets);
     }
 }

@@ -82,6 +82,7 @@ struct ChubParams {
 };
 
 cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s, unsigned long long *tickets = nullptr);
+int chub_step_shape(const ChubParams &p);   // warps per block * 100 + blocks per SM * 10 of a launch with these parameters
 void chub_launch_reset(const ChubParams &p, cudaStream_t s);
 void chub_launch_situation(const ChubParams &p, float *out, cudaStream_t s);
 void chub_launch_report(const ChubParams &p, int h, double *out, cudaStream_t s);

@@ -154,6 +154,10 @@ class HubEngine(object):
     def algorithmic_bytes(self, k=0):
         return int(self.lib.chub_algorithmic_bytes(self.h, k))
 
+    def unit_hubs(self):
+        """Hubs per scheduling unit of a whole-batch step launch (chub_unit_hubs): hubs of one unit share an SM."""
+        return int(self.lib.chub_unit_hubs(self.h))
+
     def set_traces(self, pv, wd, price, per_hub=False):
         """pv (already x5), wd, price (table[t-1] + noise): [L] shared or [L, n_hubs] per hub."""
         a = [np.ascontiguousarray(x, np.float64) for x in (pv, wd, price)]

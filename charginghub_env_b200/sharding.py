@@ -30,6 +30,21 @@ def order_by_class(hub_class):
     return order, inverse
 
 
+def order_by_size(classes, hub_class):
+    """Like order_by_class, but the classes themselves are listed by size (piles of both stations, then of the first):
+    neighbouring warps -- the 16 to 28 tiles a block of the step kernel steps together -- then hold hubs of similar
+    cost, so no warp waits at the unit's end for a neighbour with four times its piles, the warps of a block stay in the
+    same part of the loop body, and the cost-ordered unit lists (chub_step_kernel) see units of one cost each.
+    `classes` are the constructor kwargs (station_list).  Returns (order, inverse) like order_by_class."""
+    hc = np.asarray(hub_class)
+    size = np.array([[sum(c["station_list"]), c["station_list"][0]] for c in classes], dtype=np.int64)
+    key = (size[hc, 0] * 4096 + size[hc, 1]) * (len(classes) + 1) + hc
+    order = np.argsort(key, kind="stable")
+    inverse = np.empty_like(order)
+    inverse[order] = np.arange(len(order))
+    return order, inverse
+
+
 def hub_streams(base_seed, hub_ids):
     """(key0, key1, minstd state) of each global hub id -- Python mirror of chub_hub_streams()."""
     M = (1 << 64) - 1

@@ -322,6 +322,12 @@ int chub_free_host(void *p);
 /* Algorithmic HBM bytes of one hub-step for class k: B(nf,ns) of SURVEY.md section 8d. */
 int64_t chub_algorithmic_bytes(chub_engine *e, int32_t k);
 
+/* Hubs per scheduling unit of a whole-batch step launch: the step kernel hands its persistent blocks units of this many
+ * consecutive hubs (one 32-hub tile per warp).  Hubs that share a unit are stepped side by side on one SM, so a caller
+ * that can choose the order of its hubs (which are independent: evcssp_manager.py:25-27 takes no neighbour) does best
+ * to keep hubs of similar size and phase together in runs of this length.  Informational; no reference counterpart. */
+int32_t chub_unit_hubs(chub_engine *e);
+
 #ifdef __cplusplus
 }
 #endif

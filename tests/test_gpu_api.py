@@ -393,6 +393,7 @@ def test_setters_invalidate_a_captured_rollout(tables):
 def test_per_launch_timers(tables):
     import torch
     eng, rs = _engine(4096, tables, seed=4)
+    assert eng.unit_hubs() % 32 == 0 and 128 <= eng.unit_hubs() <= 1024   # whole tiles, one per warp of a block
     acts = torch.from_numpy(rs.uniform(-1, 1, (4096, 47)).astype(np.float32)).cuda()
     eng.reset()
     eng.set_timing(True)

@@ -16,6 +16,19 @@ def test_shard_ranges_partition_the_batch():
         assert max(sizes) - min(sizes) <= 1
 
 
+def test_hub_orders_are_permutations_that_group_classes_and_sizes():
+    rs = np.random.RandomState(5)
+    classes = [dict(station_list=[int(rs.randint(4, 33)), int(rs.randint(4, 33))]) for _ in range(40)]
+    hc = rs.randint(0, 40, 5000)
+    for order, inverse in (sharding.order_by_class(hc), sharding.order_by_size(classes, hc)):
+        assert sorted(order.tolist()) == list(range(5000))
+        assert (hc[order][inverse] == hc).all()
+        runs = 1 + int((np.diff(hc[order]) != 0).sum())
+        assert runs == len(set(hc.tolist()))                      # every class is one contiguous run
+    size = np.array([sum(c["station_list"]) for c in classes])[hc[sharding.order_by_size(classes, hc)[0]]]
+    assert (np.diff(size) >= 0).all()                             # and the runs come in order of pile count
+
+
 def test_python_stream_mirror_equals_c_header():
     """sharding.hub_streams (used to seed explicit streams) == chub_hub_streams() in include/chub_rng.h."""
     ids = np.array([0, 1, 2, 4095, 4096, 1048575, 4194303], np.int64)
