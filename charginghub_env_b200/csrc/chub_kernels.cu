@@ -1458,14 +1458,23 @@ void chub_launch_stats_sums(const float4 *stats, int H, double *partial, double 
 int chub_step_shape(const ChubParams &p) {
     int shape = p.block;
     if (shape == 0) {
+        // One block per SM; a block of W warps steps units of W tiles, one tile per warp, unit after unit.  Large blocks
+        // run a tile cheaper than small ones (measured cost per tile: 28 warps 1.00, 16 warps 1.12, 8 warps 1.2, 4 warps
+        // 1.3), but what decides for a batch that is not many times the machine is how its units divide among the SMs:
+        // 4,096 tiles are ONE round of 28-warp units on 147 SMs, but two rounds -- the second almost empty -- of 24-warp
+        // units.  So: the shape with the least estimated time = rounds x tiles in flight per SM x cost per tile.
         const int ws = step_scratch_bytes<0>(p), sms = p.num_sms > 0 ? p.num_sms : 148;
         const long long tiles = ((long long) (p.h_end - p.h_begin) + 31) / 32;
         const int NC = 6;
         const int cand[NC] = {28, 24, 20, 16, 8, 4};
+        const double cost[NC] = {1.00, 1.04, 1.08, 1.12, 1.2, 1.3};
+        double best = 0.0;
         shape = 410;
         for (int k = 0; k < NC; ++k) {
             if (CHUB_SMEM_TABLES + cand[k] * ws + 1024 > 227 * 1024) continue;   // the warps' scratch must fit
-            if (tiles >= (long long) cand[k] * sms || cand[k] == 4) { shape = cand[k] * 100 + 10; break; }
+            const long long units = (tiles + cand[k] - 1) / cand[k], rounds = (units + sms - 1) / sms;
+            const double est = (double) rounds * cand[k] * cost[k];
+            if (best == 0.0 || est < best) { best = est; shape = cand[k] * 100 + 10; }
         }
     }
     return shape;
