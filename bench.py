@@ -1,7 +1,7 @@
 """bench.py -- hub-env-steps/s of the batched step path on N B200s (one process per GPU).
 
-A "step" is ONE launch of the fused hub step kernel over this rank's shard of hubs (plus the one-thread tick kernel that
-advances the trace index).  Workloads (BASELINE.json configs):
+A "step" is ONE launch of the fused hub step kernel over this rank's shard of hubs (its last block out advances the
+trace index; only the ranged launches of the host pipeline still end with a one-thread tick kernel).  Workloads (BASELINE.json configs):
   config5 (default): 524,288 default hubs per GPU (4,194,304 at 8 GPUs, weak scaling), shared synthetic year traces,
                      auto-reset on, actions from a rotating pool of pre-drawn matrices
   config2          : 4,096 identical default hubs (the bit-exact parity configuration; far too small to fill a B200)
@@ -288,8 +288,8 @@ def ppo_loop(args, eng, H, S, rank, world, local, barrier, n_segments):
     return {"value": H * world * K / (ms_max * 1e-3), "unit": UNIT, "steps": K, "ms_per_step": ms_max / K, "segment": T,
             "graph_replays": n_segments, "algorithmic_bytes_per_hub_step": bytes_loop,
             "what": "configs[4]: %d-step segments, torch policy (linear + tanh) on DLPack views, obs/reward/done written "
-                    "into the rollout buffers by chub_step_into, one CUDA graph per segment; per step 1 step kernel + "
-                    "1 tick (ours) + 1 GEMM + 1 tanh (torch)" % T}
+                    "into the rollout buffers by chub_step_into, one CUDA graph per segment; per step 1 step kernel "
+                    "(ours) + 1 GEMM + 1 tanh (torch)" % T}
 
 
 def dephase(eng, H, step, pool, mode):
@@ -424,7 +424,7 @@ def main():
                 "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": world, "steps": res["steps"],
                 "warmup": args.segment * 2, "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": wl["scaling"],
                 "vs_baseline": None, "dtype": "f32 state / f64 arithmetic", "data": "synthetic",
-                "config": dict(config_dict(wl, H, world), loop=res["what"]), "e2e": None, "gpu_launches": res["steps"] * 2,
+                "config": dict(config_dict(wl, H, world), loop=res["what"]), "e2e": None, "gpu_launches": res["steps"],
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
                              "peak_source": peak_src, "kernel": "whole loop step (policy + chub_step_kernel + stores)"},
                 "hub_error_bits": int(eng.counters()["error_or"])}))
@@ -609,7 +609,7 @@ def main():
             "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": wl["scaling"], "vs_baseline": None,
             "dtype": "f32 state / f64 arithmetic", "data": "synthetic", "config": cfg, "clocks": clocks,
             "e2e": e2e, "e2e_packed": e2e_packed, "ppo_loop": ppo,
-            "gpu_launches": int(launches) * (3 if args.control == "loads" else 2)
+            "gpu_launches": int(launches) * (2 if args.control == "loads" else 1)
                             + (int(e2e["steps"]) * (host_chunks + 1) * 2 if e2e else 0),
             "roofline": roof, "hub_error_bits": int(err),
             "reference_env_steps_per_s": reference_env_rate(),

@@ -562,12 +562,15 @@ static int run_step(chub_engine *e, const ChubParams &P, cudaStream_t s) {
         }
     }
     unsigned long long tickets = 0;
-    CK(chub_launch_step(P, s, &tickets));
+    bool ticked = false;
+    ChubParams Q = P;
+    Q.self_tick = 1;   // the kernel's last block advances the step index: one launch per step, no tick kernel behind it
+    CK(chub_launch_step(Q, s, &tickets, &ticked));
     if (slot >= 0) {
         CK(cudaEventRecord(e->time_ev[2 * slot + 1], s));
         e->timed += 1;
     }
-    chub_launch_tick(e->step_index, 1, e->queue + 1, tickets, s);
+    if (!ticked) chub_launch_tick(e->step_index, 1, e->queue + 1, tickets, s);
     CK(cudaGetLastError());
     e->launches += 1;
     return CHUB_OK;
@@ -661,8 +664,10 @@ extern "C" int chub_step_loads_static(chub_engine *e, const float *loads_dev, fl
     chub_launch_dispatch(P, e->static_bits, s);     // writes the word of every hub < n_hubs: nothing must start at zero
     P.act_bits = e->static_bits;
     unsigned long long tickets = 0;
-    CK(chub_launch_step(P, s, &tickets));
-    chub_launch_tick(e->step_index, 1, e->queue + 1, tickets, s);
+    bool ticked = false;
+    P.self_tick = 1;
+    CK(chub_launch_step(P, s, &tickets, &ticked));
+    if (!ticked) chub_launch_tick(e->step_index, 1, e->queue + 1, tickets, s);
     CK(cudaGetLastError());
     e->launches += 1;
     return CHUB_OK;
@@ -898,11 +903,15 @@ extern "C" int chub_rollout_capture(chub_engine *e, const float *actions_dev, in
     }
     CK(cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal));
     unsigned long long tickets = 0;
-    for (int j = 0; j < n_steps; ++j) {  // the step offset is baked per node; one tick per replay
-        P.step_offset = j;
-        chub_launch_step(P, cap, &tickets);
+    bool ticked = false;
+    P.self_tick = 1;
+    for (int j = 0; j < n_steps; ++j) {
+        // persistent launches advance the step index themselves; for static grids the step offset is baked per node
+        // and one tick closes the replay
+        P.step_offset = ticked ? 0 : j;
+        chub_launch_step(P, cap, &tickets, &ticked);
     }
-    chub_launch_tick(e->step_index, n_steps, e->queue + 1, tickets * (unsigned long long) n_steps, cap);
+    if (!ticked) chub_launch_tick(e->step_index, n_steps, e->queue + 1, tickets * (unsigned long long) n_steps, cap);
     cudaError_t ce = cudaStreamEndCapture(cap, &e->graph);
     if (own) cudaStreamDestroy(cap);
     if (ce != cudaSuccess) return fail(CHUB_ERR_CUDA, std::string("capture: ") + cudaGetErrorString(ce));

@@ -903,6 +903,10 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
             wr->n_units = n_units;
             rd->n_units = -1;
             for (int b = 0; b < CHUB_LPT_BINS; ++b) rd->count[b] = 0;
+            if (P.self_tick) {   // every block has read the step index for the last time: advance it, and the queue's epoch
+                *const_cast<long long *>(P.step_index) = *P.step_index + 1;
+                *const_cast<unsigned long long *>(P.queue_base) = *P.queue_base + P.queue_stride;
+            }
         }
     }
 }
@@ -1190,7 +1194,7 @@ static int step_scratch_bytes(const ChubParams &p) {
     return ws;
 }
 template <int WARPS, int MINB, int Q>
-static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s, unsigned long long *tickets) {
+static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s, unsigned long long *tickets, bool *self_ticked) {
     ChubParams p = p0;
     p.ws_bytes = step_scratch_bytes<Q>(p);
     const size_t smem = CHUB_SMEM_TABLES + (size_t) WARPS * p.ws_bytes;
@@ -1211,6 +1215,8 @@ static cudaError_t launch_step_variant(const ChubParams &p0, cudaStream_t s, uns
     } else if (tickets) {
         *tickets = 0;
     }
+    if (!p.queue) p.self_tick = 0;   // a static grid does not know its last block
+    if (self_ticked) *self_ticked = p.self_tick != 0;
     kern<<<(unsigned) grid, block, smem, s>>>(p);
     return cudaSuccess;
 }
@@ -1479,19 +1485,16 @@ int chub_step_shape(const ChubParams &p) {
     }
     return shape;
 }
-cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s, unsigned long long *tickets) {
+cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s, unsigned long long *tickets, bool *self_ticked) {
     const int shape = chub_step_shape(p);
     switch (shape) {  // warps per block * 100 + min blocks per SM * 10
-        case 410: return launch_step_variant<4, 1, 0>(p, s, tickets);
-        case 810: return launch_step_variant<8, 1, 0>(p, s, tickets);
-        case 1610: return launch_step_variant<16, 1, 0>(p, s, tickets);
-        case 2010: return launch_step_variant<20, 1, 0>(p, s, tickets);
-        case 2410: return launch_step_variant<24, 1, 0>(p, s, tickets);
-        case 2810: return launch_step_variant<28, 1, 0>(p, s, tickets);
-        case 1220: return launch_step_variant<12, 2, 0>(p, s, tickets);
-        case 1020: return launch_step_variant<10, 2, 0>(p, s, tickets);
-        case 1420: return launch_step_variant<14, 2, 0>(p, s, tickets);
-        default: return launch_step_variant<16, 1, 0>(p, s, tickets);
+        case 410: return launch_step_variant<4, 1, 0>(p, s, tickets, self_ticked);
+        case 810: return launch_step_variant<8, 1, 0>(p, s, tickets, self_ticked);
+        case 1610: return launch_step_variant<16, 1, 0>(p, s, tickets, self_ticked);
+        case 2010: return launch_step_variant<20, 1, 0>(p, s, tickets, self_ticked);
+        case 2410: return launch_step_variant<24, 1, 0>(p, s, tickets, self_ticked);
+        case 2810: return launch_step_variant<28, 1, 0>(p, s, tickets, self_ticked);
+        default: return launch_step_variant<16, 1, 0>(p, s, tickets, self_ticked);
     }
 }
 void chub_launch_reset(const ChubParams &p, cudaStream_t s) {

@@ -41,6 +41,7 @@ struct ChubParams {
     int num_sms;                      // SMs of the device (launch-shape choice)
     int ws_bytes;                     // bytes of shared-memory scratch per warp (set by chub_launch_step)
     int step_offset;                  // added to *step_index (graph-captured rollouts bake 0..n-1)
+    int self_tick;                    // the step kernel's last block advances *step_index (and the queue's epoch) itself: no tick launch
     const long long *step_index;      // device: absolute step index of the state being left
     unsigned long long *queue;        // device: ticket counter of the persistent step kernel; NULL = static block -> tile mapping
     const unsigned long long *queue_base;   // device: the counter's value when the current epoch (since the last tick) began
@@ -81,7 +82,9 @@ struct ChubParams {
     const uint8_t *reset_mask;        // reset kernel only
 };
 
-cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s, unsigned long long *tickets = nullptr);
+// tickets: what a later tick has to add to the queue's epoch base; self_ticked: the launch advances the step index itself
+// (asked for with p.self_tick, granted when the launch is a persistent one: its last block out is known)
+cudaError_t chub_launch_step(const ChubParams &p, cudaStream_t s, unsigned long long *tickets = nullptr, bool *self_ticked = nullptr);
 int chub_step_shape(const ChubParams &p);   // warps per block * 100 + blocks per SM * 10 of a launch with these parameters
 void chub_launch_reset(const ChubParams &p, cudaStream_t s);
 void chub_launch_situation(const ChubParams &p, float *out, cudaStream_t s);
