@@ -184,40 +184,9 @@ __device__ __noinline__ uint2 draw_mk_soc(uint32_t lcg) {
     de = fminf(fmaxf(de, 1.0f), 10.0f);
     return make_uint2(__float_as_uint((float) (75.0 - 5.0 * (double) de)), lcg);
 }
-// The serial part of the two polar normals, alone: walk the minstd stream to the attempt that is accepted and
-// return {state that attempt started from, state after it}.  The variate itself is a pure function of the
-// start state and can be evaluated later, by any lane (mk_soc_from / late_time_from).
-__device__ __noinline__ uint2 walk_polar_d(uint32_t lcg) {
-    uint32_t s0;
-    for (;;) {
-        s0 = lcg;
-        const uint32_t s2 = chub_minstd_jump(s0, CHUB_MINSTD_A2), s4 = chub_minstd_jump(s0, CHUB_MINSTD_A4);
-        lcg = s4;
-        const float xa = fmaf((float) (s2 - 1u), 9.31322575e-10f, -1.0f), ya = fmaf((float) (s4 - 1u), 9.31322575e-10f, -1.0f);
-        const float r2a = fmaf(xa, xa, ya * ya);
-        bool ok = r2a < 1.0f;
-        if (fabsf(r2a - 1.0f) < 4e-6f || r2a < 4e-6f) {   // too close to call in fp32: decide like the reference
-            const double xe = 2.0 * canon_d_of(chub_minstd_next(s0), s2) - 1.0;
-            const double ye = 2.0 * canon_d_of(chub_minstd_jump(s0, CHUB_MINSTD_A3), s4) - 1.0;
-            const double r2e = xe * xe + ye * ye;
-            ok = !(r2e > 1.0 || r2e == 0.0);
-        }
-        if (ok) break;
-    }
-    return make_uint2(s0, lcg);
-}
-__device__ __noinline__ uint2 walk_polar_f(uint32_t lcg) {
-    uint32_t s0;
-    for (;;) {
-        s0 = lcg;
-        const uint32_t s1 = chub_minstd_next(s0), s2 = chub_minstd_jump(s0, CHUB_MINSTD_A2);
-        lcg = s2;
-        const float x = 2.0f * canon_f_of(s1) - 1.0f, y = 2.0f * canon_f_of(s2) - 1.0f;
-        const float r2 = x * x + y * y;
-        if (!(r2 > 1.0f || r2 == 0.0f)) break;
-    }
-    return make_uint2(s0, lcg);
-}
+// The serial part of the two polar normals of add_car -- walking the minstd stream to the attempt that is accepted -- lives
+// in the step kernel (chub_kernels.cu, add_car: one loop trip per attempt of either kind); the variate itself is a pure
+// function of the state its accepted attempt started from and is evaluated later, by any lane (mk_soc_from / late_time_from).
 // mk_soc (CHS.hpp:804-814) from the start state of its accepted attempt
 template <int LT>
 __device__ __forceinline__ float mk_soc_from(uint32_t s0) {

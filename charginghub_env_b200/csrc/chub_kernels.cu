@@ -383,17 +383,52 @@ __device__ __forceinline__ void station_step(const ChubParams &P, Scr<Q> S, cons
             }
             const int total = __shfl_sync(full, incl, 31);
             int slot = incl - q;
-            for (int k = 0; k < q; ++k, ++slot) {
-                const uint2 wd = walk_polar_d(rng.lcg);           // E
-                const uint32_t tu = (uint32_t) rng_u1000(rng);    // U  (target = u/999*20+80)
-                const uint2 wf = walk_polar_f(wd.y);              // E
-                rng.lcg = wf.y;
-                const uint32_t i = (uint32_t) __ffs(rem) - 1u;
-                rem &= rem - 1u;
-                CHUB_CHECK(slot >= 0 && slot < 2 * LA_RING && i < (uint32_t) n);
-                (&S->la_t[0][0])[slot] = wd.x;
-                (&S->la_w[0][0])[slot] = wf.x;
-                (&S->la_id[0][0])[slot] = (uint32_t) lane | (i << 5) | (tu << 10);
+            // One loop trip = one polar ATTEMPT of whichever kind the lane is at -- the double attempt of mk_soc (four
+            // draws: x from the pair's second state, y from the fourth) or the float attempt of mk_late_time (two draws) --
+            // through one body: the two differ in their jump multipliers and in the band test only.  A lane's trip count
+            // is the SUM of its attempts (10.2 +- 1.7 for four cars) instead of the warp waiting, car by car and normal by
+            // normal, for the lane with the most rejections (2.5 trips per normal with a dozen lanes at work).
+            {
+                int left = q;
+                uint32_t st = rng.lcg, sd = 0u, tu = 0u;
+                bool mode_f = false;
+                while (left > 0) {
+                    const uint32_t sx = chub_minstd_jump(st, mode_f ? 16807u : CHUB_MINSTD_A2);
+                    const uint32_t sy = chub_minstd_jump(st, mode_f ? CHUB_MINSTD_A2 : CHUB_MINSTD_A4);
+                    // 2 * canonical - 1 of generate_canonical<float,24> (bits/random.tcc: (s - 1) / 2^31, clamped below 1):
+                    // one rounding, like the reference's 2.0f * ret - 1.0f (the scalings by powers of two are exact).  For
+                    // the double attempt the same expression on the pair's high states estimates x^2 + y^2 to 1e-6 (draw_mk_soc, chub_device.cuh).
+                    const float x = fmaf(fminf((float) (sx - 1u), 2147483520.0f), 0x1p-30f, -1.0f);
+                    const float y = fmaf(fminf((float) (sy - 1u), 2147483520.0f), 0x1p-30f, -1.0f);
+                    const float r2 = x * x + y * y;
+                    bool ok = !(r2 > 1.0f || r2 == 0.0f);
+                    if (!mode_f && (fabsf(r2 - 1.0f) < 4e-6f || r2 < 4e-6f)) {   // too close to call in fp32: like the reference
+                        const double xe = 2.0 * canon_d_of(chub_minstd_next(st), sx) - 1.0;
+                        const double ye = 2.0 * canon_d_of(chub_minstd_jump(st, CHUB_MINSTD_A3), sy) - 1.0;
+                        const double r2e = xe * xe + ye * ye;
+                        ok = !(r2e > 1.0 || r2e == 0.0);
+                    }
+                    const uint32_t s0 = st;
+                    st = sy;
+                    if (ok) {
+                        if (!mode_f) {
+                            sd = s0;                                  // E: mk_soc's accepted attempt starts here
+                            tu = (uint32_t) rng_u1000(rng);           // U  (target = u/999*20+80)
+                            mode_f = true;
+                        } else {                                      // E: mk_late_time's accepted attempt starts at s0
+                            const uint32_t i = (uint32_t) __ffs(rem) - 1u;
+                            rem &= rem - 1u;
+                            CHUB_CHECK(slot >= 0 && slot < 2 * LA_RING && i < (uint32_t) n);
+                            (&S->la_t[0][0])[slot] = sd;
+                            (&S->la_w[0][0])[slot] = s0;
+                            (&S->la_id[0][0])[slot] = (uint32_t) lane | (i << 5) | (tu << 10);
+                            slot += 1;
+                            left -= 1;
+                            mode_f = false;
+                        }
+                    }
+                }
+                rng.lcg = st;
             }
             __syncwarp();
             flat_add_car<TYPE, CP, Q>(S, tlut, pile0, P.arrive + tile0, total);
