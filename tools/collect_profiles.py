@@ -61,6 +61,6 @@ if captures:
     if len(lock) == 2:
         for c in lock:
             c["phase"] = "lockstep-" + ("busy" if "42" in c["what"] else "quiet")
-    json.dump({"source": "ncu --set full --clock-control none, one launch each (tools/gpu_r02j.sh); dram__bytes_read.sum + "
+    json.dump({"source": "ncu --set full --clock-control none, one launch each (tools/gpu_r02k.sh); dram__bytes_read.sum + "
                          "dram__bytes_write.sum", "captures": captures}, open(os.path.join(dst, "r02_traffic.json"), "w"), indent=1)
 print("\n".join(sorted(f for f in os.listdir(dst) if f.startswith(pre))))
