@@ -631,7 +631,7 @@ def main():
             "dtype": "f32 state / f64 arithmetic", "data": "synthetic", "config": cfg, "clocks": clocks,
             "e2e": e2e, "e2e_packed": e2e_packed, "ppo_loop": ppo,
             "gpu_launches": int(launches) * (2 if args.control == "loads" else 1)
-                            + (int(e2e["steps"]) * (host_chunks + 1) * 2 if e2e else 0),
+                            + (int(e2e["steps"]) * (host_chunks + 1) * 2 * 2 if e2e else 0),   # e2e + e2e_packed, two windows each
             "roofline": roof, "measurement": measurement, "hub_error_bits": int(err),
             "reference_env_steps_per_s": reference_env_rate(),
         }
