@@ -668,8 +668,11 @@ __device__ __forceinline__ void exo_reset(const ChubParams &P, ExoState &g, uint
 }
 
 // observation, evcssp_manager.py:318-342 (state_norm) over make_state's real_state
+// obs_row: where the 13 values go instead of the hub's row of P.obs (the step kernel parks them in shared memory and the warp
+// then writes its 32 rows -- one contiguous block of the row-major matrix -- with coalesced stores); NULL = straight to P.obs
 __device__ __forceinline__ void write_obs(const ChubParams &P, int h, const ChubClass &c, int t, const StationOut &s0,
-                                          const StationOut &s1, double store_soc, double pv, double wd, double pr) {
+                                          const StationOut &s1, double store_soc, double pv, double wd, double pr,
+                                          float *obs_row = nullptr) {
     float o[CHUB_OBS_DIM];
 #pragma unroll
     for (int j = 0; j < CHUB_OBS_DIM; ++j) o[j] = 0.0f;
@@ -691,7 +694,7 @@ __device__ __forceinline__ void write_obs(const ChubParams &P, int h, const Chub
     o[k++] = (float) store_soc;
     o[k++] = (float) DIVK(pv, 210.0, H_R210);
     o[k++] = (float) DIVK(wd, 92.0, H_R92);
-    float *dst = P.obs + (size_t) h * CHUB_OBS_DIM;
+    float *dst = obs_row ? obs_row : P.obs + (size_t) h * CHUB_OBS_DIM;
 #pragma unroll
     for (int j = 0; j < CHUB_OBS_DIM; ++j) dst[j] = o[j];
 }
@@ -700,7 +703,7 @@ __device__ __forceinline__ void write_obs(const ChubParams &P, int h, const Chub
 // (evs_reset), hydrogen store, FCEV queue, episode statistics, first observation of the new episode.
 // Out of line on purpose: the step kernel calls it once per hub per 96 steps (fused auto-reset).
 // @region hub_reset_full
-__device__ __noinline__ void hub_reset_full(const ChubParams &P, int h, long long k_obs) {
+__device__ __noinline__ void hub_reset_full(const ChubParams &P, int h, long long k_obs, float *obs_row = nullptr) {
     const int ci = P.cls ? __ldg(&P.cls[h]) : 0;
     const ChubClass &c = P.classes[ci];
     HubVars v;
@@ -725,7 +728,7 @@ __device__ __noinline__ void hub_reset_full(const ChubParams &P, int h, long lon
     } else {
         trace_at(P, h, k_obs, 0, 0, pv, wd, pr);
     }
-    write_obs(P, h, c, 0, s0, s1, c.init_soc, pv, wd, pr);
+    write_obs(P, h, c, 0, s0, s1, c.init_soc, pv, wd, pr, obs_row);
     if (P.diag) {
         const size_t s = (size_t) P.Hpad;
         float *q = P.st_power + h;
@@ -812,6 +815,8 @@ __device__ __noinline__ StationIO station_step_cp(const ChubParams &P, Scr<Q> S,
 // One hub tile (32 consecutive hubs, one per lane) through the whole step.
 template <int Q>
 __device__ __forceinline__ void step_tile(const ChubParams &P, Scr<Q> S, const float *tl_s, const int h);
+template <int Q>
+__device__ __forceinline__ void flush_obs(const ChubParams &P, Scr<Q> S, int h0);
 
 // The kernel is persistent: one block per SM pulls UNITS of WARPS consecutive tiles (what a block of the static grid would
 // own) from a ticket counter until the batch is used up, heaviest units first.
@@ -905,7 +910,10 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
         CHUB_CHECK((long long) unit * WARPS * 32 < (long long) (P.h_end - P.h_begin));
         if (threadIdx.x == 0) s_t0 = clock64();
         const long long h0 = (long long) P.h_begin + ((long long) unit * WARPS + (threadIdx.x >> 5)) * 32;
-        if (h0 < (long long) P.h_end) step_tile<Q>(P, S, tl_s, (int) h0 + S.lane);   // the last unit may be short of tiles
+        if (h0 < (long long) P.h_end) {   // the last unit may be short of tiles
+            step_tile<Q>(P, S, tl_s, (int) h0 + S.lane);
+            flush_obs<Q>(P, S, (int) h0);
+        }
         if (threadIdx.x < 32) {
             // warp 0 draws the next unit when ITS tile is done, i.e. while the unit's stragglers are still at work: late
             // enough that units still go to whichever SM is about to be free (drawing at the start of the unit would
@@ -1000,7 +1008,6 @@ __device__ __forceinline__ void step_tile(const ChubParams &P, Scr<Q> S, const f
         S->park[s][2][lane_] = __float_as_uint(o.now); S->park[s][3][lane_] = o.occ;
         S->park[s][4][lane_] = (uint32_t) (o.line & 0xff) | ((uint32_t) (o.flow & 0xff) << 8) | ((uint32_t) o.incomplete << 16);
     }
-    if (!active) return;
     // what only the hub section needs is fetched or unpacked now: store mass, exogenous traces, the two analog actions
     HubVars v;
     v.rng = rng; v.err = err;
@@ -1015,12 +1022,14 @@ __device__ __forceinline__ void step_tile(const ChubParams &P, Scr<Q> S, const f
         s1.now = __uint_as_float(S->park[1][2][lane_]); s1.occ = S->park[1][3][lane_];
         s1.line = p1 & 0xff; s1.flow = (int) (signed char) ((p1 >> 8) & 0xff); s1.incomplete = p1 >> 16; s1.number = __popc(s1.occ);
     }
+    const float a_m2 = S->am[0][lane_], a_m1 = S->am[1][lane_];
+    __syncwarp();   // every lane has read what the stations parked: the scratch now takes the observation rows
+    if (!active) return;
     v.store = P.store[h];
     const long long k = *P.step_index + P.step_offset;
     double pv_t, wd_t, pr_t;
     if (P.exo_mode) exo_current(P, h, pv_t, wd_t, pr_t);
     else trace_at(P, h, k, v.t, v.t, pv_t, wd_t, pr_t);
-    const float a_m2 = S->am[0][lane_], a_m1 = S->am[1][lane_];
     v.line0 = s0.line; v.line1 = s1.line;
     v.flow0 = s0.flow; v.flow1 = s1.flow;
     v.occ0 = s0.occ; v.occ1 = s1.occ;
@@ -1174,11 +1183,29 @@ __device__ __forceinline__ void step_tile(const ChubParams &P, Scr<Q> S, const f
     } else if (!(done && P.auto_reset)) {
         trace_at(P, h, k, t_left, t_left + 1, pv_n, wd_n, pr_n);
     }
+    // the observation row waits in the (now idle) station scratch: lane l's 13 values at float 13 l (odd pitch: no conflicts)
+    float *const obs_row = reinterpret_cast<float *>(&S->park[0][0][0]) + lane_ * CHUB_OBS_DIM;
     if (done && P.auto_reset) {  // fused auto-reset: the returned obs is the first one of the next episode
-        hub_reset_full(P, h, k + 1);
+        hub_reset_full(P, h, k + 1, obs_row);
     } else {
-        write_obs(P, h, c, v.t, s0, s1, store_soc, pv_n, wd_n, pr_n);
+        write_obs(P, h, c, v.t, s0, s1, store_soc, pv_n, wd_n, pr_n, obs_row);
     }
+}
+
+// second half of step_tile, by the whole warp: the 32 observation rows parked in shared memory are one contiguous block of
+// the row-major [H][13] matrix -- 13 coalesced 128-byte stores instead of 13 x 32 scattered ones
+template <int Q>
+__device__ __forceinline__ void flush_obs(const ChubParams &P, Scr<Q> S, int h0) {
+    __syncwarp();
+    const int rows = min(32, P.h_end - h0);
+    const float *src = reinterpret_cast<const float *>(&S->park[0][0][0]);
+    float *dst = P.obs + (size_t) h0 * CHUB_OBS_DIM;
+#pragma unroll
+    for (int k = 0; k < CHUB_OBS_DIM; ++k) {
+        const int e = k * 32 + S.lane;
+        if (e < rows * CHUB_OBS_DIM) dst[e] = src[e];
+    }
+    __syncwarp();
 }
 
 // @region other kernels
