@@ -833,6 +833,10 @@ __device__ __forceinline__ void flush_obs(const ChubParams &P, Scr<Q> S, int h0)
 // ticket past the end, so a launch advances the counter by stride = units + blocks and the tick kernel moves the base.
 // The lists are double buffered by the parity of the absolute step; a list that does not hold exactly this launch's
 // units (first launch, other batch range or shape) is ignored and units go out in index order.
+// the absolute step index of this launch (*P.step_index + P.step_offset), read from global memory ONCE per block: every tile
+// needs it for its trace slots and every unit draw for the parity of the cost lists, and a dependent trip to L2 each time
+// is what the car-independent part of a step is made of (tools/empty_tile_cost.py)
+__shared__ long long g_step_k;
 #define CHUB_LPT_BINS 64
 struct LptList {            // one per parity, in global memory: head[0] = units the list was built for, then the bins
     int n_units, done_blocks, pad[2];
@@ -843,7 +847,7 @@ struct LptList {            // one per parity, in global memory: head[0] = units
 template <int WARPS>
 __device__ __noinline__ int draw_unit(const ChubParams &P, int lane) {
     const int n_units = (int) (((long long) (P.h_end - P.h_begin) + WARPS * 32 - 1) / (WARPS * 32));
-    const int par = (int) ((*P.step_index + P.step_offset) & 1);
+    const int par = (int) (g_step_k & 1);
     const size_t list_bytes = sizeof(LptList) + (size_t) CHUB_LPT_BINS * P.lpt_cap * sizeof(int);
     const LptList *const rd = reinterpret_cast<const LptList *>(P.lpt + par * list_bytes);
     long long k = 0;
@@ -888,6 +892,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     for (int i = threadIdx.x; i < 2000; i += WARPS * 32) tl_w[i] = __ldg(&P.s2t_lut[i]);
     __shared__ int s_unit[2];
     __shared__ long long s_t0;
+    if (threadIdx.x == 0) g_step_k = *P.step_index + P.step_offset;
     __syncthreads();
     Scr<Q> S;
     S.base = (uint32_t) __cvta_generic_to_shared(chub_smem + CHUB_SMEM_TABLES + (threadIdx.x >> 5) * P.ws_bytes);
@@ -924,7 +929,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
         }
         __syncthreads();          // the unit's cost is that of its slowest warp
         if (threadIdx.x == 0 && P.queue) {   // book it: into the bin of its cost, for the next launch to read
-            const int par = (int) ((*P.step_index + P.step_offset) & 1);
+            const int par = (int) (g_step_k & 1);
             const size_t list_bytes = sizeof(LptList) + (size_t) CHUB_LPT_BINS * P.lpt_cap * sizeof(int);
             LptList *const wr = reinterpret_cast<LptList *>(P.lpt + (par ^ 1) * list_bytes);
             int bin = (int) ((clock64() - s_t0) >> 13);
@@ -936,7 +941,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) chub_step_kernel(const __gri
     // the last block out tags the list it helped write and clears the one everybody has finished reading
     if (threadIdx.x == 0 && P.queue != nullptr) {
         const int n_units = (int) (((long long) (P.h_end - P.h_begin) + WARPS * 32 - 1) / (WARPS * 32));
-        const int par = (int) ((*P.step_index + P.step_offset) & 1);
+        const int par = (int) (g_step_k & 1);
         const size_t list_bytes = sizeof(LptList) + (size_t) CHUB_LPT_BINS * P.lpt_cap * sizeof(int);
         LptList *const rd = reinterpret_cast<LptList *>(P.lpt + par * list_bytes);
         LptList *const wr = reinterpret_cast<LptList *>(P.lpt + (par ^ 1) * list_bytes);
@@ -982,6 +987,9 @@ __device__ __forceinline__ void step_tile(const ChubParams &P, Scr<Q> S, const f
         occ = P.occ[h];
         rng.k0 = key.x; rng.k1 = key.y; rng.lcg = a.x; rng.uctr = a.y;
         az = a.z; aw = a.w;
+        // what the hub section will ask for after the stations: on its way to L2 now (no registers held)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(P.store + h));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(P.stats + 2 * h));
     }
 
     // ---- the two EV stations, station 0 first (Aggregator_Simple.py:141-142); the whole warp takes part ----
@@ -1026,7 +1034,7 @@ __device__ __forceinline__ void step_tile(const ChubParams &P, Scr<Q> S, const f
     __syncwarp();   // every lane has read what the stations parked: the scratch now takes the observation rows
     if (!active) return;
     v.store = P.store[h];
-    const long long k = *P.step_index + P.step_offset;
+    const long long k = g_step_k;
     double pv_t, wd_t, pr_t;
     if (P.exo_mode) exo_current(P, h, pv_t, wd_t, pr_t);
     else trace_at(P, h, k, v.t, v.t, pv_t, wd_t, pr_t);
