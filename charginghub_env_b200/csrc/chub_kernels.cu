@@ -673,9 +673,9 @@ __device__ __forceinline__ void exo_reset(const ChubParams &P, ExoState &g, uint
 __device__ __forceinline__ void write_obs(const ChubParams &P, int h, const ChubClass &c, int t, const StationOut &s0,
                                           const StationOut &s1, double store_soc, double pv, double wd, double pr,
                                           float *obs_row = nullptr) {
-    float o[CHUB_OBS_DIM];
-#pragma unroll
-    for (int j = 0; j < CHUB_OBS_DIM; ++j) o[j] = 0.0f;
+    // written where it goes as it is computed (a local array indexed by a run-time count lives in local memory: 26 more
+    // trips through the load/store unit per hub-step)
+    float *const o = obs_row ? obs_row : P.obs + (size_t) h * CHUB_OBS_DIM;
     int k = 0;
     o[k++] = (float) kC.time_sin[t];
     o[k++] = (float) chub_div_const(pr - kC.price_mean, kC.price_std, kC.r_price_std);
@@ -694,9 +694,7 @@ __device__ __forceinline__ void write_obs(const ChubParams &P, int h, const Chub
     o[k++] = (float) store_soc;
     o[k++] = (float) DIVK(pv, 210.0, H_R210);
     o[k++] = (float) DIVK(wd, 92.0, H_R92);
-    float *dst = obs_row ? obs_row : P.obs + (size_t) h * CHUB_OBS_DIM;
-#pragma unroll
-    for (int j = 0; j < CHUB_OBS_DIM; ++j) dst[j] = o[j];
+    for (; k < CHUB_OBS_DIM; ++k) o[k] = 0.0f;
 }
 
 // EvcsspManagerEnv_v6.reset (evcssp_manager.py:304-316) of one hub, from and to HBM: both stations
