@@ -197,7 +197,8 @@ int chub_step_loads(chub_engine *e, const float *loads_dev, void *stream);
  * it cudaMalloc's on its first call; this variant keeps it in a file-scope device array of the library
  * (csrc/chub_noalloc.cu) of CHUB_STATIC_MAX_HUBS words = 8 MiB, which every GPU that loads libchub.so holds until the
  * process exits.  It calls no cudaMalloc / cudaFree, creates no stream or event, and calls into no allocating library;
- * it launches the dispatch kernel, the step kernel and the tick on `stream` and returns.
+ * it launches the dispatch kernel and the step kernel (which advances the step index itself; behind a static grid a
+ * one-thread tick kernel follows) on `stream` and returns.
  * loads_dev: as chub_step_loads.  obs_out_dev / reward_out_dev / done_out_dev: as chub_step_into (NULL = the engine's
  * own buffer).  Engines with more than CHUB_STATIC_MAX_HUBS hubs are refused with CHUB_ERR_ARG (use chub_step_loads).
  * The array is shared by every engine on a device and by every call, and keeps the last call's contents; nothing in it
