@@ -365,6 +365,14 @@ __device__ __forceinline__ void station_step(const ChubParams &P, Scr<Q> S, cons
         }
     }
 
+    // The arrival SOC of a new car goes to a row of its own (`arrive`), 4 bytes into a sector nobody has read: a partial
+    // write to a sector that is not in L2 ends as a read-modify-write at the memory.  The rows that will take new cars are
+    // known now; lane r asks for row r's 128-byte line, and by the time the walk is done the stores find it in L2.
+    {
+        const uint32_t arows = __reduce_or_sync(full, add_mask);
+        if ((arows >> lane) & 1u) asm volatile("prefetch.global.L2 [%0];" ::"l"(P.arrive + tile0 + (size_t) lane * 32));
+    }
+
 // @region add_car (per-lane stream walk)
     // ---- add_car for the newly assigned piles, ascending (CHS.hpp:864-877 / 1029-1042).  Per car the E stream serves
     // mk_soc then mk_late_time and the U stream the target draw in between.  Which attempt of each polar normal is
